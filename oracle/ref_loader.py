@@ -1,0 +1,76 @@
+"""Load the UNMODIFIED reference function for pinning the oracle (TEST INFRASTRUCTURE).
+
+`import app` is impossible (streamlit/yfinance/xgboost/plotly are absent and
+app.py:17 runs `st.set_page_config` at import), so the FunctionDef named
+`garch_monte_carlo` (app.py:586-657) is taken out of the parsed module and
+executed in a namespace holding only what it uses: np, pd, Optional, Dict.
+
+/root/reference exists only in the build container: nothing that runs on the GPU
+box may call this.  `make_golden.py` uses it to write tests/golden/ref_*.npz.
+"""
+from __future__ import annotations
+
+import ast
+import os
+from typing import Dict, Optional
+
+import numpy as np
+
+DEFAULT_REFERENCE = os.environ.get("MC_REFERENCE", "/root/reference/app.py")
+
+
+def reference_available(path: str = DEFAULT_REFERENCE) -> bool:
+    return os.path.isfile(path)
+
+
+def load_reference_function(path: str = DEFAULT_REFERENCE, np_module=np):
+    import pandas as pd
+    with open(path, "r") as fh:
+        tree = ast.parse(fh.read(), filename=path)
+    node = next(n for n in tree.body
+                if isinstance(n, ast.FunctionDef) and n.name == "garch_monte_carlo")
+    module = ast.Module(body=[node], type_ignores=[])
+    ns = {"np": np_module, "pd": pd, "Optional": Optional, "Dict": Dict}
+    exec(compile(module, path, "exec"), ns)
+    return ns["garch_monte_carlo"]
+
+
+class _ChoiceProxy:
+    """Stands in for `np.random` inside the reference so that a supplied matrix of
+    shocks (or pool indices) is what `np.random.choice` (app.py:620) returns."""
+
+    def __init__(self, shocks=None, indices=None):
+        self._shocks, self._indices, self._t = shocks, indices, 0
+
+    def choice(self, pool, size=None):
+        t, self._t = self._t, self._t + 1
+        if self._shocks is not None:
+            return np.asarray(self._shocks[t], dtype=np.float64)
+        return np.asarray(pool)[np.asarray(self._indices[t])]
+
+
+class _NumpyProxy:
+    def __init__(self, random):
+        self.random = random
+
+    def __getattr__(self, name):
+        return getattr(np, name)
+
+
+def run_reference_injected(df, n_sims, n_days, s0, *, shocks=None, indices=None,
+                           path: str = DEFAULT_REFERENCE):
+    """Run the unmodified reference with its RNG replaced by a supplied matrix."""
+    fn = load_reference_function(path, _NumpyProxy(_ChoiceProxy(shocks, indices)))
+    return fn(df, n_sims, n_days, s0)
+
+
+def synthetic_frame(n_rows: int = 1250, seed: int = 0, heavy_tail: bool = False):
+    """SURVEY 8c synthetic input: log_ret ~ N(0, 0.02^2) (or scaled Student-t4),
+    rvol_20 = 0.02*sqrt(252)."""
+    import pandas as pd
+    rs = np.random.RandomState(seed)
+    if heavy_tail:
+        r = rs.standard_t(4, n_rows) * 0.02 / np.sqrt(2.0)
+    else:
+        r = rs.normal(0.0, 0.02, n_rows)
+    return pd.DataFrame({"log_ret": r, "rvol_20": np.full(n_rows, 0.02 * np.sqrt(252))})
