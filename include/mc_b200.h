@@ -1,0 +1,186 @@
+/*
+ * mc_b200.h -- C ABI of the B200-native Monte Carlo path simulator.
+ *
+ * This is the drop-in boundary for the one hot path of raasawin/montecarlo:
+ * the routine `garch_monte_carlo(df, n_sims, n_days, current_price,
+ * progress_callback=None)` (reference app.py:586-657, sole call site
+ * app.py:1240).  The reference has no FFI of its own -- its boundary is that
+ * plain Python function -- so the entry points below are what a ctypes binding
+ * for it needs: one call that takes the bootstrap pool and the scalar model
+ * parameters and returns every reduction the function's result dict holds
+ * (app.py:647-657), plus a staged variant that lets the host interleave one
+ * small collective per stage when paths are sharded over several GPUs.
+ *
+ * Conventions: plain C, no C++ types or exceptions cross the boundary.  Every
+ * function returns 0 on success, a negative mc_status otherwise;
+ * mc_last_error(h) gives the message.  All `d_` pointers are DEVICE pointers
+ * owned by the caller (PyTorch tensors' data_ptr()), `h_` pointers are host
+ * memory.  Kernels are enqueued on the caller's CUDA stream (passed as void*,
+ * a cudaStream_t); only mc_fetch_result / mc_run synchronise.  A handle is
+ * bound to one device and guarded by a mutex: concurrent calls on different
+ * handles are safe (the Streamlit app runs sessions in threads, app.py:1392).
+ */
+#ifndef MC_B200_H
+#define MC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MC_ABI_VERSION 1u
+#define MC_MAX_PCTS 16u       /* terminal percentiles per call (reference uses 9, app.py:639) */
+#define MC_MAX_PATH_PCTS 8u   /* fan-chart percentiles (reference uses 5, app.py:644) */
+#define MC_MAX_ASSETS 32u
+
+typedef enum mc_status {
+    MC_OK = 0,
+    MC_ERR_INVALID = -1,     /* bad argument / unsupported combination */
+    MC_ERR_CUDA = -2,        /* a CUDA runtime call failed */
+    MC_ERR_VERSION = -3,     /* mc_params.struct_size / version mismatch */
+    MC_ERR_STATE = -4        /* stage functions called out of order */
+} mc_status;
+
+/* where the per-step shock comes from */
+typedef enum mc_shock {
+    MC_SHOCK_BOOTSTRAP = 0,  /* Philox word -> index into the pool: replaces np.random.choice(std_returns) app.py:620 */
+    MC_SHOCK_NORMAL = 1,     /* Philox -> Box-Muller N(0,1) in registers (north_star extension) */
+    MC_SHOCK_INJECTED = 2    /* read z[t, path] from d_shocks (parity testing) */
+} mc_shock;
+
+/* how the per-step variance evolves */
+typedef enum mc_var_model {
+    MC_VAR_GARCH = 0,        /* var' = omega + alpha r^2 + beta var   app.py:632-633 */
+    MC_VAR_CONST = 1         /* constant variance var0 (GBM) */
+} mc_var_model;
+
+typedef enum mc_dtype { MC_F32 = 0, MC_F64 = 1 } mc_dtype;
+
+enum {
+    MC_FLAG_STORE_PATHS = 1u,   /* write paths[(T+1), ld] time-major like app.py:612-613 */
+    MC_FLAG_FAN_CHART = 2u,     /* per-step percentiles (app.py:643-645); needs STORE_PATHS */
+    MC_FLAG_NO_TERMINAL_SELECT = 4u  /* skip percentiles / tail (moments + histogram only) */
+};
+
+/*
+ * One simulation request.  Everything the reference hard-codes or derives
+ * before its loop (app.py:601-609) arrives here as a number.
+ */
+typedef struct mc_params {
+    uint32_t struct_size;       /* sizeof(mc_params) */
+    uint32_t version;           /* MC_ABI_VERSION */
+    uint64_t n_paths;           /* paths simulated by THIS call (this rank's shard) */
+    uint64_t path_offset;       /* global id of local path 0: Philox counter = global id */
+    uint64_t n_paths_global;    /* paths over all ranks (order statistics are global) */
+    uint64_t paths_ld;          /* row stride (elements) of d_paths, >= n_paths; 0 = n_paths */
+    uint32_t n_steps;           /* n_days */
+    uint32_t n_assets;          /* 1, or d <= MC_MAX_ASSETS for the portfolio mode */
+    int32_t shock;              /* mc_shock */
+    int32_t var_model;          /* mc_var_model */
+    int32_t dtype;              /* mc_dtype of terminal / paths / pool / shocks buffers */
+    uint32_t flags;
+    uint64_t seed;              /* Philox key */
+    double s0;                  /* current_price            app.py:613 */
+    double var0;                /* initial per-step variance app.py:606 (GBM: sigma^2 dt) */
+    double omega, alpha, beta;  /* app.py:601-603 */
+    double drift;               /* log-space drift per step (reference: 0; GBM: (mu - sigma^2/2) dt) */
+    uint32_t pool_len;          /* H = len(std_returns)      app.py:609 */
+    uint32_t hist_bins;         /* 0 = no histogram */
+    double hist_lo, hist_hi;    /* np.histogram range; lo >= hi means (min, max) of the data */
+    uint32_t n_pcts;            /* terminal percentiles, ascending, in percent */
+    uint32_t n_path_pcts;
+    double pcts[MC_MAX_PCTS];
+    double path_pcts[MC_MAX_PATH_PCTS];
+    double tail_pct;            /* CVaR level in percent (reference: 5, app.py:656); <0 = none */
+} mc_params;
+
+/* Portfolio description (n_assets > 1); host arrays, copied at launch. */
+typedef struct mc_portfolio {
+    const double* h_chol;       /* [d*d] row-major lower-triangular Cholesky factor of the correlation */
+    const double* h_sigma_step; /* [d] sigma_i * sqrt(dt) */
+    const double* h_drift_step; /* [d] (mu_i - sigma_i^2/2) dt */
+    const double* h_s0;         /* [d] initial prices */
+    const double* h_weights;    /* [d] portfolio weights */
+} mc_portfolio;
+
+/* Everything scalar the reference's result dict holds (app.py:647-657). */
+typedef struct mc_result {
+    uint64_t n;                 /* paths reduced (global) */
+    uint64_t n_above;           /* #(final > s0)                    -> prob_profit  app.py:654 */
+    double mean;                /* mean(final)                      -> expected_return app.py:652 */
+    double std;                 /* std(final), ddof=0               -> expected_vol app.py:653 */
+    double min, max;
+    double pct[MC_MAX_PCTS];    /* np.percentile(final, p), method='linear'  app.py:638-640 */
+    double pct_lo[MC_MAX_PCTS]; /* the two order statistics each percentile interpolates */
+    double pct_hi[MC_MAX_PCTS];
+    uint64_t tail_count;        /* #(final <= percentile(tail_pct)) */
+    double tail_sum;            /* their sum                        -> cvar_95 app.py:656 */
+    double hist_lo, hist_hi;    /* range actually used */
+    float sim_ms;               /* device time of the simulation kernel(s), CUDA events */
+    float total_ms;             /* device time of the whole call */
+    uint32_t launches;          /* kernels launched by this call */
+    uint32_t reserved;
+} mc_result;
+
+typedef struct mc_handle mc_handle;
+
+int mc_abi_version(void);
+int mc_create(int device_ordinal, mc_handle** out);
+int mc_destroy(mc_handle* h);
+const char* mc_last_error(const mc_handle* h);   /* h may be NULL: last create() error */
+
+/*
+ * Whole job on one GPU (replaces the body of garch_monte_carlo, app.py:612-656).
+ *   d_pool     : [pool_len] std_returns (dtype), MC_SHOCK_BOOTSTRAP only
+ *   d_shocks   : [n_steps (* n_assets), ld] injected shocks, MC_SHOCK_INJECTED only
+ *   d_paths    : [(n_steps+1), paths_ld] or NULL          (MC_FLAG_STORE_PATHS)
+ *   d_terminal : [n_paths] final prices (always written)
+ *   h_result   : scalars;  h_hist: uint64[hist_bins] or NULL;
+ *   h_fan      : double[n_path_pcts * (n_steps+1)] or NULL (MC_FLAG_FAN_CHART)
+ * Synchronises `stream` before returning.
+ */
+int mc_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf,
+           const void* d_pool, const void* d_shocks, void* d_paths, void* d_terminal,
+           mc_result* h_result, uint64_t* h_hist, double* h_fan, void* stream);
+
+/*
+ * Staged variant for path-sharded multi-GPU runs.  Each stage writes
+ * a packed buffer of 8-byte words; the host all-gathers it over ranks (NCCL) and
+ * hands the gathered [n_ranks][words] buffer to the next stage.  With n_ranks=1
+ * the "gathered" buffer is the stage buffer itself.
+ *
+ *   mc_stage_begin(...)                 simulate + local moments + first digit histogram
+ *   loop: words = mc_stage_words(h)     size of the buffer the next call writes/expects
+ *         mc_stage_next(h, d_gathered, n_ranks, d_out, &done)
+ *   mc_fetch_result(...)                D2H of the merged result, synchronises
+ */
+int mc_stage_begin(mc_handle* h, const mc_params* p, const mc_portfolio* pf,
+                   const void* d_pool, const void* d_shocks, void* d_paths, void* d_terminal,
+                   void* d_stage_out, uint64_t stage_capacity_words, void* stream);
+int64_t mc_stage_words(const mc_handle* h);
+int64_t mc_stage_max_words(const mc_params* p);
+int mc_stage_next(mc_handle* h, const void* d_gathered, uint32_t n_ranks,
+                  void* d_stage_out, int* done, void* stream);
+int mc_fetch_result(mc_handle* h, mc_result* h_result, uint64_t* h_hist, double* h_fan,
+                    void* stream);
+
+/*
+ * Building blocks exposed for tests and for the callers either side of the path.
+ */
+/* z[t, i] (dtype) for paths path_offset.. : the shocks the simulator would draw */
+int mc_debug_shocks(mc_handle* h, const mc_params* p, const void* d_pool, void* d_out, void* stream);
+/* raw Philox-4x32-10 words: out[4*i..4*i+3] for counters ctr[4*i..], one key */
+int mc_debug_philox(mc_handle* h, const uint32_t* d_ctr, uint32_t n, uint32_t key0, uint32_t key1,
+                    uint32_t* d_out, void* stream);
+/* np.percentile(x[r, :], pcts, method='linear') for r in rows of a [rows, ld] matrix */
+int mc_percentiles(mc_handle* h, const void* d_x, int32_t dtype, uint64_t rows, uint64_t n,
+                   uint64_t ld, const double* pcts, uint32_t n_pcts, double* h_out, void* stream);
+/* np.histogram(x, bins, range=(lo, hi)) on float64-cast values */
+int mc_histogram(mc_handle* h, const void* d_x, int32_t dtype, uint64_t n, uint32_t bins,
+                 double lo, double hi, uint64_t* h_counts, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MC_B200_H */

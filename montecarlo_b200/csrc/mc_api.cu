@@ -1,0 +1,526 @@
+// mc_api.cu -- the C ABI of include/mc_b200.h: handle, workspace and the stage machine.
+//
+// The stage machine is what lets one code path serve both the single-GPU call
+// (mc_run: every "gathered" buffer is the local stage buffer) and the path-sharded
+// multi-GPU run (the host all-gathers each stage buffer over ranks between calls).
+// Stages:   0 .. P-1 : digit histograms of radix pass k (stage 0 also carries the moments)
+//           P        : tail (count, sum) + fixed-bin histogram counts
+// with P = number of radix passes (3 for fp32 keys, 7 for fp64), or 0 when no
+// percentile is requested.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+
+#include "mc_select.cuh"
+#include "mc_sim.cuh"
+
+using namespace mc;
+
+namespace {
+thread_local std::string g_create_error;
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        cudaError_t e = cudaMalloc(&p, n * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+template <typename T>
+struct PinnedBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        cudaError_t e = cudaMallocHost(&p, n * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+}  // namespace
+
+struct mc_handle {
+    int device = 0;
+    DeviceInfo dev{};
+    std::mutex mu;
+    std::string err;
+
+    DevBuf<BlockPartial> partials;
+    DevBuf<DeviceResult> res;
+    DevBuf<SelectPlan> plans;           // [2]: terminal, fan
+    DevBuf<RowState> states_t, states_f;
+    DevBuf<double> pct_t;               // [3 * MC_MAX_PCTS]
+    DevBuf<double> fan;                 // [rows * n_path_pcts]
+    DevBuf<double> tail_scratch;        // [2 * 1024]
+    DevBuf<double> edges;
+    DevBuf<unsigned long long> hist_total;
+    DevBuf<unsigned long long> stage;   // internal stage buffer (mc_run, mc_percentiles)
+    PinnedBuf<unsigned char> h_stage;   // pinned staging for the D2H of results
+    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+
+    // state of the run in flight
+    bool active = false;
+    mc_params p{};
+    SelectProblem prob_t{}, prob_f{};
+    bool has_t = false, has_f = false;
+    int n_sel = 0;          // radix passes to run
+    int call_idx = 0;
+    int tail_idx = -1;
+    size_t next_words = 0;  // words of the stage buffer most recently written
+    unsigned launches = 0;
+    void* d_terminal = nullptr;
+};
+
+namespace {
+
+int fail(mc_handle* h, int code, const std::string& msg) {
+    if (h) h->err = msg; else g_create_error = msg;
+    return code;
+}
+int cuda_fail(mc_handle* h, cudaError_t e, const char* where) {
+    return fail(h, MC_ERR_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
+}
+#define MC_CUDA(h, call)                                                  \
+    do {                                                                  \
+        cudaError_t e__ = (call);                                         \
+        if (e__ != cudaSuccess) return cuda_fail((h), e__, #call);        \
+    } while (0)
+
+size_t hist_words(const SelectProblem& sp, int pass) {
+    const size_t nb = (size_t)1 << sp.plan.pass_bits[pass];
+    const size_t g_cap = pass == 0 ? 1 : (size_t)sp.plan.n_targets;
+    return (sp.rows * g_cap * nb + 1) / 2;
+}
+
+// words of hist stage `pass` and the offsets of its parts
+struct StageLayout { size_t off_t, off_f, words; };
+StageLayout layout_hist_stage(const mc_handle* h, int pass) {
+    StageLayout L{};
+    size_t w = pass == 0 ? STAGE0_HEADER : 0;
+    L.off_t = w;
+    // the stage-0 histogram of the terminal values is always produced (it is fused into the sim kernel)
+    if (pass == 0) w += DIGIT0_BINS / 2;
+    else if (h->has_t) w += hist_words(h->prob_t, pass);
+    L.off_f = w;
+    if (h->has_f) w += hist_words(h->prob_f, pass);
+    L.words = w;
+    return L;
+}
+size_t final_stage_words(const mc_params& p) { return 2 + (size_t)p.hist_bins; }
+
+int validate(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void* d_pool, const void* d_shocks,
+             void* d_paths, void* d_terminal) {
+    if (!p) return fail(h, MC_ERR_INVALID, "params is NULL");
+    if (p->struct_size != sizeof(mc_params) || p->version != MC_ABI_VERSION)
+        return fail(h, MC_ERR_VERSION, "mc_params struct_size/version mismatch");
+    if (p->n_paths_global == 0 || p->n_paths > p->n_paths_global)
+        return fail(h, MC_ERR_INVALID, "n_paths_global must be >= n_paths and > 0");
+    if (p->n_paths >= (1ull << 32)) return fail(h, MC_ERR_INVALID, "n_paths per call must be < 2^32");
+    if (p->n_steps == 0 || p->n_steps > 1000000u) return fail(h, MC_ERR_INVALID, "n_steps out of range");
+    if (p->dtype != MC_F32 && p->dtype != MC_F64) return fail(h, MC_ERR_INVALID, "bad dtype");
+    if (p->shock < 0 || p->shock > MC_SHOCK_INJECTED) return fail(h, MC_ERR_INVALID, "bad shock mode");
+    if (p->var_model != MC_VAR_GARCH && p->var_model != MC_VAR_CONST) return fail(h, MC_ERR_INVALID, "bad var model");
+    if (p->n_assets < 1 || p->n_assets > MC_MAX_ASSETS) return fail(h, MC_ERR_INVALID, "n_assets out of range");
+    if (p->n_assets > 1 && (!pf || !pf->h_chol || !pf->h_sigma_step || !pf->h_drift_step || !pf->h_s0 || !pf->h_weights))
+        return fail(h, MC_ERR_INVALID, "portfolio description missing");
+    if (p->n_assets > 1 && (p->shock == MC_SHOCK_BOOTSTRAP || p->var_model != MC_VAR_CONST))
+        return fail(h, MC_ERR_INVALID, "portfolio mode supports normal/injected shocks with constant variance");
+    if (p->shock == MC_SHOCK_BOOTSTRAP && (!d_pool || p->pool_len == 0))
+        return fail(h, MC_ERR_INVALID, "bootstrap needs a pool");
+    if (p->shock == MC_SHOCK_INJECTED && !d_shocks) return fail(h, MC_ERR_INVALID, "injected shocks missing");
+    if (!d_terminal && p->n_paths) return fail(h, MC_ERR_INVALID, "d_terminal is NULL");
+    if ((p->flags & MC_FLAG_STORE_PATHS) && !d_paths && p->n_paths) return fail(h, MC_ERR_INVALID, "d_paths is NULL");
+    if ((p->flags & MC_FLAG_FAN_CHART) && !(p->flags & MC_FLAG_STORE_PATHS))
+        return fail(h, MC_ERR_INVALID, "fan chart needs stored paths");
+    if (p->paths_ld && p->paths_ld < p->n_paths) return fail(h, MC_ERR_INVALID, "paths_ld < n_paths");
+    if (p->n_pcts > MC_MAX_PCTS || p->n_path_pcts > MC_MAX_PATH_PCTS) return fail(h, MC_ERR_INVALID, "too many percentiles");
+    if (p->hist_bins > (1u << 16)) return fail(h, MC_ERR_INVALID, "hist_bins > 65536");
+    if (!(p->var0 >= 0.0) || !(p->s0 == p->s0)) return fail(h, MC_ERR_INVALID, "var0 must be >= 0");
+    return MC_OK;
+}
+
+int upload_plan(mc_handle* h, SelectProblem& sp, int slot, cudaStream_t s) {
+    sp.d_plan = h->plans.p + slot;
+    // pageable host -> device async copy is staged by the runtime before returning
+    MC_CUDA(h, cudaMemcpyAsync(sp.d_plan, &sp.plan, sizeof(SelectPlan), cudaMemcpyHostToDevice, s));
+    return MC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mc_abi_version(void) { return (int)MC_ABI_VERSION; }
+
+const char* mc_last_error(const mc_handle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int mc_create(int device_ordinal, mc_handle** out) {
+    if (!out) return fail(nullptr, MC_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaGetDeviceCount");
+    if (device_ordinal < 0 || device_ordinal >= count) return fail(nullptr, MC_ERR_INVALID, "no such CUDA device");
+    mc_handle* h = new (std::nothrow) mc_handle();
+    if (!h) return fail(nullptr, MC_ERR_INVALID, "out of host memory");
+    h->device = device_ordinal;
+    cudaDeviceProp prop{};
+    if ((e = cudaSetDevice(device_ordinal)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, device_ordinal)) != cudaSuccess) {
+        delete h;
+        return cuda_fail(nullptr, e, "cudaGetDeviceProperties");
+    }
+    if (prop.major < 10) {
+        delete h;
+        return fail(nullptr, MC_ERR_INVALID, "this library is built for sm_100a (Blackwell) only");
+    }
+    h->dev.sm_count = prop.multiProcessorCount;
+    h->dev.max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+    bool ok = h->partials.reserve(MAX_SIM_GRID) == cudaSuccess && h->res.reserve(1) == cudaSuccess &&
+              h->plans.reserve(2) == cudaSuccess && h->states_t.reserve(1) == cudaSuccess &&
+              h->pct_t.reserve(3 * MC_MAX_PCTS) == cudaSuccess && h->tail_scratch.reserve(2 * 1024) == cudaSuccess;
+    for (int i = 0; i < 3 && ok; ++i) ok = cudaEventCreate(&h->ev[i]) == cudaSuccess;
+    if (!ok) {
+        e = cudaGetLastError();
+        mc_destroy(h);
+        return cuda_fail(nullptr, e, "workspace allocation");
+    }
+    *out = h;
+    return MC_OK;
+}
+
+int mc_destroy(mc_handle* h) {
+    if (!h) return MC_OK;
+    cudaSetDevice(h->device);
+    h->partials.release(); h->res.release(); h->plans.release(); h->states_t.release(); h->states_f.release();
+    h->pct_t.release(); h->fan.release(); h->tail_scratch.release(); h->edges.release(); h->hist_total.release();
+    h->stage.release(); h->h_stage.release();
+    for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
+    delete h;
+    return MC_OK;
+}
+
+int64_t mc_stage_max_words(const mc_params* p) {
+    if (!p) return -1;
+    const size_t rows_f = (p->flags & MC_FLAG_FAN_CHART) ? (size_t)p->n_steps + 1 : 0;
+    const size_t nt_t = 2 * (size_t)p->n_pcts, nt_f = 2 * (size_t)p->n_path_pcts;
+    size_t w0 = STAGE0_HEADER + DIGIT0_BINS / 2 + rows_f * DIGIT0_BINS / 2;
+    size_t wk = nt_t * DIGIT_BINS / 2 + rows_f * nt_f * DIGIT_BINS / 2;
+    size_t wf = 2 + (size_t)p->hist_bins;
+    size_t m = w0 > wk ? w0 : wk;
+    return (int64_t)(m > wf ? m : wf);
+}
+
+int64_t mc_stage_words(const mc_handle* h) { return h ? (int64_t)h->next_words : -1; }
+
+static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void* d_pool,
+                              const void* d_shocks, void* d_paths, void* d_terminal, void* d_stage_out,
+                              uint64_t cap_words, cudaStream_t s) {
+    int rc = validate(h, p, pf, d_pool, d_shocks, d_paths, d_terminal);
+    if (rc) return rc;
+    MC_CUDA(h, cudaSetDevice(h->device));
+    h->active = false;
+    h->p = *p;
+    h->launches = 0;
+    h->call_idx = 0;
+    h->d_terminal = d_terminal;
+    h->has_t = p->n_pcts > 0 && !(p->flags & MC_FLAG_NO_TERMINAL_SELECT);
+    h->has_f = (p->flags & MC_FLAG_FAN_CHART) && p->n_path_pcts > 0;
+    h->tail_idx = -1;
+    if (h->has_t) {
+        if (!build_select_plan(p->pcts, (int)p->n_pcts, p->n_paths_global, p->dtype, &h->prob_t.plan))
+            return fail(h, MC_ERR_INVALID, "percentiles must be ascending and within [0, 100]");
+        h->prob_t.x = d_terminal; h->prob_t.dtype = p->dtype; h->prob_t.rows = 1; h->prob_t.n = p->n_paths;
+        h->prob_t.ld = p->n_paths; h->prob_t.d_states = h->states_t.p;
+        if ((rc = upload_plan(h, h->prob_t, 0, s))) return rc;
+        if (p->tail_pct >= 0.0) {
+            for (unsigned k = 0; k < p->n_pcts; ++k) if (p->pcts[k] == p->tail_pct) h->tail_idx = (int)k;
+            if (h->tail_idx < 0) return fail(h, MC_ERR_INVALID, "tail_pct must be one of pcts");
+        }
+    }
+    if (h->has_f) {
+        if (!build_select_plan(p->path_pcts, (int)p->n_path_pcts, p->n_paths_global, p->dtype, &h->prob_f.plan))
+            return fail(h, MC_ERR_INVALID, "path percentiles must be ascending and within [0, 100]");
+        const size_t rows = (size_t)p->n_steps + 1;
+        if (rows > 65535) return fail(h, MC_ERR_INVALID, "fan chart supports at most 65534 steps");
+        MC_CUDA(h, h->states_f.reserve(rows));
+        MC_CUDA(h, h->fan.reserve(rows * p->n_path_pcts));
+        h->prob_f.x = d_paths; h->prob_f.dtype = p->dtype; h->prob_f.rows = rows; h->prob_f.n = p->n_paths;
+        h->prob_f.ld = p->paths_ld ? p->paths_ld : p->n_paths; h->prob_f.d_states = h->states_f.p;
+        if ((rc = upload_plan(h, h->prob_f, 1, s))) return rc;
+    }
+    h->n_sel = (h->has_t || h->has_f) ? (h->has_t ? h->prob_t.plan.n_passes : h->prob_f.plan.n_passes) : 0;
+    if (p->hist_bins) {
+        MC_CUDA(h, h->edges.reserve((size_t)p->hist_bins + 1));
+        MC_CUDA(h, h->hist_total.reserve(p->hist_bins));
+    }
+    const StageLayout L = layout_hist_stage(h, 0);
+    if (!d_stage_out || cap_words < (uint64_t)mc_stage_max_words(p))
+        return fail(h, MC_ERR_INVALID, "stage buffer smaller than mc_stage_max_words()");
+    unsigned long long* out = static_cast<unsigned long long*>(d_stage_out);
+
+    MC_CUDA(h, cudaEventRecord(h->ev[0], s));
+    MC_CUDA(h, cudaMemsetAsync(out, 0, L.words * sizeof(unsigned long long), s));
+    SimBuffers b{};
+    b.d_pool = d_pool; b.d_shocks = d_shocks; b.d_paths = d_paths; b.d_terminal = d_terminal;
+    b.d_partials = h->partials.p;
+    b.d_hist0 = reinterpret_cast<unsigned int*>(out + L.off_t);
+    int grid = 0;
+    MC_CUDA(h, launch_simulation(*p, pf, b, h->dev, &grid, s));
+    MC_CUDA(h, cudaEventRecord(h->ev[1], s));
+    MC_CUDA(h, launch_reduce_partials(h->partials.p, grid, out, s));
+    h->launches += 2;
+    if (h->has_f) {
+        MC_CUDA(h, launch_select_hist(h->prob_f, 0, reinterpret_cast<unsigned int*>(out + L.off_f), h->dev.sm_count, s));
+        h->launches += 1;
+    }
+    h->next_words = L.words;
+    h->active = true;
+    return MC_OK;
+}
+
+static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ranks, void* d_stage_out, int* done,
+                             cudaStream_t s) {
+    if (!h->active) return fail(h, MC_ERR_STATE, "mc_stage_next without mc_stage_begin");
+    if (!d_gathered || !d_stage_out || n_ranks == 0 || !done) return fail(h, MC_ERR_INVALID, "bad stage arguments");
+    MC_CUDA(h, cudaSetDevice(h->device));
+    const unsigned long long* g = static_cast<const unsigned long long*>(d_gathered);
+    unsigned long long* out = static_cast<unsigned long long*>(d_stage_out);
+    const mc_params& p = h->p;
+    const size_t stride = h->next_words;      // words per rank in `gathered`
+    const int c = h->call_idx++;
+    *done = 0;
+
+    if (c == (h->n_sel > 0 ? h->n_sel : 1)) {      // gathered = final stage
+        MC_CUDA(h, launch_merge_final(g, n_ranks, stride, p.hist_bins, h->res.p, h->hist_total.p, s));
+        h->launches += 1;
+        MC_CUDA(h, cudaEventRecord(h->ev[2], s));
+        *done = 1;
+        h->active = false;
+        return MC_OK;
+    }
+    if (c == 0) {
+        MC_CUDA(h, launch_merge_moments(g, n_ranks, stride, p.s0, h->res.p, s));
+        h->launches += 1;
+    }
+    if (c < h->n_sel) {
+        const StageLayout L = layout_hist_stage(h, c);
+        if (h->has_t) {
+            MC_CUDA(h, launch_select_scan(h->prob_t, c, reinterpret_cast<const unsigned int*>(g + L.off_t), n_ranks,
+                                          stride * 2, s));
+            h->launches += 1;
+        }
+        if (h->has_f) {
+            MC_CUDA(h, launch_select_scan(h->prob_f, c, reinterpret_cast<const unsigned int*>(g + L.off_f), n_ranks,
+                                          stride * 2, s));
+            h->launches += 1;
+        }
+        if (c + 1 < h->n_sel) {
+            const StageLayout N = layout_hist_stage(h, c + 1);
+            if (h->has_t) {
+                MC_CUDA(h, launch_select_hist(h->prob_t, c + 1, reinterpret_cast<unsigned int*>(out + N.off_t),
+                                              h->dev.sm_count, s));
+                h->launches += 1;
+            }
+            if (h->has_f) {
+                MC_CUDA(h, launch_select_hist(h->prob_f, c + 1, reinterpret_cast<unsigned int*>(out + N.off_f),
+                                              h->dev.sm_count, s));
+                h->launches += 1;
+            }
+            h->next_words = N.words;
+            return MC_OK;
+        }
+        // last radix pass done: keys are exact -> percentiles
+        if (h->has_t) {
+            double* pct = h->pct_t.p;
+            MC_CUDA(h, launch_select_finish(h->prob_t, pct, pct + MC_MAX_PCTS, pct + 2 * MC_MAX_PCTS, s));
+            MC_CUDA(h, launch_publish_percentiles(pct, pct + MC_MAX_PCTS, pct + 2 * MC_MAX_PCTS, (int)p.n_pcts,
+                                                  h->tail_idx, h->res.p, s));
+            h->launches += 2;
+        }
+        if (h->has_f) {
+            MC_CUDA(h, launch_select_finish(h->prob_f, h->fan.p, nullptr, nullptr, s));
+            h->launches += 1;
+        }
+    }
+    // emit the final stage: [tail count, tail sum, histogram counts...]
+    MC_CUDA(h, cudaMemsetAsync(out, 0, 2 * sizeof(unsigned long long), s));
+    if (h->has_t && h->tail_idx >= 0) {
+        MC_CUDA(h, launch_tail(h->d_terminal, p.dtype, p.n_paths, h->res.p, h->tail_scratch.p, out, h->dev.sm_count, s));
+        h->launches += 2;
+    }
+    if (p.hist_bins) {
+        MC_CUDA(h, launch_value_hist(h->d_terminal, p.dtype, p.n_paths, p.hist_bins, p.hist_lo, p.hist_hi, h->res.p,
+                                     h->edges.p, out + 2, h->dev.sm_count, s));
+        h->launches += 2;
+    }
+    h->next_words = final_stage_words(p);
+    return MC_OK;
+}
+
+static int fetch_locked(mc_handle* h, mc_result* r, uint64_t* h_hist, double* h_fan, cudaStream_t s) {
+    if (h->active) return fail(h, MC_ERR_STATE, "stages not finished");
+    if (!r) return fail(h, MC_ERR_INVALID, "h_result is NULL");
+    MC_CUDA(h, cudaSetDevice(h->device));
+    const mc_params& p = h->p;
+    const size_t fan_n = h->has_f ? ((size_t)p.n_steps + 1) * p.n_path_pcts : 0;
+    const size_t bytes = sizeof(DeviceResult) + (size_t)p.hist_bins * 8 + fan_n * 8;
+    MC_CUDA(h, h->h_stage.reserve(bytes));
+    unsigned char* hp = h->h_stage.p;
+    MC_CUDA(h, cudaMemcpyAsync(hp, h->res.p, sizeof(DeviceResult), cudaMemcpyDeviceToHost, s));
+    if (p.hist_bins && h_hist)
+        MC_CUDA(h, cudaMemcpyAsync(hp + sizeof(DeviceResult), h->hist_total.p, (size_t)p.hist_bins * 8, cudaMemcpyDeviceToHost, s));
+    if (fan_n && h_fan)
+        MC_CUDA(h, cudaMemcpyAsync(hp + sizeof(DeviceResult) + (size_t)p.hist_bins * 8, h->fan.p, fan_n * 8, cudaMemcpyDeviceToHost, s));
+    MC_CUDA(h, cudaStreamSynchronize(s));
+    DeviceResult d;
+    memcpy(&d, hp, sizeof(d));
+    memset(r, 0, sizeof(*r));
+    r->n = d.n; r->n_above = d.n_above; r->mean = d.mean; r->std = d.std; r->min = d.vmin; r->max = d.vmax;
+    if (h->has_t) {
+        memcpy(r->pct, d.pct, sizeof(d.pct));
+        memcpy(r->pct_lo, d.pct_lo, sizeof(d.pct_lo));
+        memcpy(r->pct_hi, d.pct_hi, sizeof(d.pct_hi));
+    }
+    r->tail_count = d.tail_count; r->tail_sum = d.tail_sum;
+    r->hist_lo = d.hist_lo; r->hist_hi = d.hist_hi;
+    if (p.hist_bins && h_hist) memcpy(h_hist, hp + sizeof(DeviceResult), (size_t)p.hist_bins * 8);
+    if (fan_n && h_fan) {
+        // device layout [row][pct] -> caller layout [pct][row] (path_percentiles['p5'] is a vector over time)
+        const double* src = reinterpret_cast<const double*>(hp + sizeof(DeviceResult) + (size_t)p.hist_bins * 8);
+        const size_t rows = (size_t)p.n_steps + 1;
+        for (size_t rr = 0; rr < rows; ++rr)
+            for (unsigned k = 0; k < p.n_path_pcts; ++k) h_fan[k * rows + rr] = src[rr * p.n_path_pcts + k];
+    }
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]) == cudaSuccess) r->sim_ms = ms;
+    if (cudaEventElapsedTime(&ms, h->ev[0], h->ev[2]) == cudaSuccess) r->total_ms = ms;
+    r->launches = h->launches;
+    return MC_OK;
+}
+
+int mc_stage_begin(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void* d_pool, const void* d_shocks,
+                   void* d_paths, void* d_terminal, void* d_stage_out, uint64_t cap_words, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return stage_begin_locked(h, p, pf, d_pool, d_shocks, d_paths, d_terminal, d_stage_out, cap_words,
+                              static_cast<cudaStream_t>(stream));
+}
+
+int mc_stage_next(mc_handle* h, const void* d_gathered, uint32_t n_ranks, void* d_stage_out, int* done, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return stage_next_locked(h, d_gathered, n_ranks, d_stage_out, done, static_cast<cudaStream_t>(stream));
+}
+
+int mc_fetch_result(mc_handle* h, mc_result* r, uint64_t* h_hist, double* h_fan, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return fetch_locked(h, r, h_hist, h_fan, static_cast<cudaStream_t>(stream));
+}
+
+int mc_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void* d_pool, const void* d_shocks,
+           void* d_paths, void* d_terminal, mc_result* h_result, uint64_t* h_hist, double* h_fan, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (!p) return fail(h, MC_ERR_INVALID, "params is NULL");
+    if (p->struct_size != sizeof(mc_params)) return fail(h, MC_ERR_VERSION, "mc_params struct_size mismatch");
+    if (p->n_paths != p->n_paths_global || p->path_offset + p->n_paths < p->n_paths)
+        return fail(h, MC_ERR_INVALID, "mc_run is single-rank: n_paths must equal n_paths_global");
+    MC_CUDA(h, cudaSetDevice(h->device));
+    const size_t cap = (size_t)mc_stage_max_words(p);
+    MC_CUDA(h, h->stage.reserve(cap));
+    int rc = stage_begin_locked(h, p, pf, d_pool, d_shocks, d_paths, d_terminal, h->stage.p, cap, s);
+    if (rc) return rc;
+    int done = 0;
+    while (!done) {
+        rc = stage_next_locked(h, h->stage.p, 1, h->stage.p, &done, s);
+        if (rc) return rc;
+    }
+    return fetch_locked(h, h_result, h_hist, h_fan, s);
+}
+
+int mc_debug_shocks(mc_handle* h, const mc_params* p, const void* d_pool, void* d_out, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (!p || p->struct_size != sizeof(mc_params)) return fail(h, MC_ERR_VERSION, "mc_params mismatch");
+    if (p->shock == MC_SHOCK_BOOTSTRAP && !d_pool) return fail(h, MC_ERR_INVALID, "pool missing");
+    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_CUDA(h, launch_debug_shocks(*p, d_pool, d_out, static_cast<cudaStream_t>(stream)));
+    return MC_OK;
+}
+
+int mc_debug_philox(mc_handle* h, const uint32_t* d_ctr, uint32_t n, uint32_t key0, uint32_t key1, uint32_t* d_out,
+                    void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_CUDA(h, launch_debug_philox(d_ctr, n, key0, key1, d_out, static_cast<cudaStream_t>(stream)));
+    return MC_OK;
+}
+
+int mc_percentiles(mc_handle* h, const void* d_x, int32_t dtype, uint64_t rows, uint64_t n, uint64_t ld,
+                   const double* pcts, uint32_t n_pcts, double* h_out, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (!d_x || !pcts || !h_out || rows == 0 || n == 0 || n_pcts == 0 || rows > 65535 || ld < n)
+        return fail(h, MC_ERR_INVALID, "bad mc_percentiles arguments");
+    MC_CUDA(h, cudaSetDevice(h->device));
+    SelectProblem sp{};
+    if (!build_select_plan(pcts, (int)n_pcts, n, dtype, &sp.plan))
+        return fail(h, MC_ERR_INVALID, "percentiles must be ascending and within [0, 100]");
+    sp.x = d_x; sp.dtype = dtype; sp.rows = rows; sp.n = n; sp.ld = ld;
+    MC_CUDA(h, h->states_f.reserve(rows));
+    MC_CUDA(h, h->fan.reserve(rows * n_pcts));
+    sp.d_states = h->states_f.p;
+    int rc = upload_plan(h, sp, 1, s);
+    if (rc) return rc;
+    size_t cap = 0;
+    for (int k = 0; k < sp.plan.n_passes; ++k) { const size_t w = hist_words(sp, k); if (w > cap) cap = w; }
+    MC_CUDA(h, h->stage.reserve(cap));
+    unsigned int* hist = reinterpret_cast<unsigned int*>(h->stage.p);
+    for (int k = 0; k < sp.plan.n_passes; ++k) {
+        MC_CUDA(h, launch_select_hist(sp, k, hist, h->dev.sm_count, s));
+        MC_CUDA(h, launch_select_scan(sp, k, hist, 1, 0, s));
+    }
+    MC_CUDA(h, launch_select_finish(sp, h->fan.p, nullptr, nullptr, s));
+    MC_CUDA(h, cudaMemcpyAsync(h_out, h->fan.p, rows * n_pcts * sizeof(double), cudaMemcpyDeviceToHost, s));
+    MC_CUDA(h, cudaStreamSynchronize(s));
+    return MC_OK;
+}
+
+int mc_histogram(mc_handle* h, const void* d_x, int32_t dtype, uint64_t n, uint32_t bins, double lo, double hi,
+                 uint64_t* h_counts, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (!d_x || !h_counts || bins == 0 || bins > (1u << 16) || !(lo < hi))
+        return fail(h, MC_ERR_INVALID, "bad mc_histogram arguments (explicit lo < hi required)");
+    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_CUDA(h, h->edges.reserve((size_t)bins + 1));
+    MC_CUDA(h, h->hist_total.reserve(bins));
+    MC_CUDA(h, launch_value_hist(d_x, dtype, n, bins, lo, hi, h->res.p, h->edges.p, h->hist_total.p, h->dev.sm_count, s));
+    MC_CUDA(h, cudaMemcpyAsync(h_counts, h->hist_total.p, (size_t)bins * 8, cudaMemcpyDeviceToHost, s));
+    MC_CUDA(h, cudaStreamSynchronize(s));
+    return MC_OK;
+}
+
+}  // extern "C"

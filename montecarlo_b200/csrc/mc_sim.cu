@@ -1,0 +1,597 @@
+// mc_sim.cu -- path-stepping kernels for sm_100a.
+//
+// Replaces the reference's time loop (app.py:618-633), which streams three
+// [N] float64 arrays through memory per step (shocks, paths[t], variances[t]).
+// Here one thread owns one path: its log-price and variance live in registers
+// for all T steps, shocks are generated in registers (mc_rng.cuh), and the only
+// HBM traffic is the terminal value (4 B per PATH, not per step) unless the
+// caller asks for the full time-major paths matrix (app.py:612 layout), in which
+// case each step adds one coalesced store per path.
+//
+// The terminal reductions of app.py:636-656 start here too: each thread
+// accumulates moments about s0 in fp64, and the first radix digit of the terminal
+// value's order-preserving key is histogrammed in shared memory so the later
+// exact percentile selection (mc_select.cu) does not need a pass of its own.
+//
+// Units: the fp32 kernels accumulate the log-price in log2 units (the host
+// pre-multiplies drift, omega and var0 by log2(e) or its square; GARCH is
+// homogeneous so the recursion is unchanged) so that price = s0 * ex2(y) is a
+// single MUFU.EX2.  The fp64 kernels work in natural units with exp().
+#include "mc_rng.cuh"
+#include "mc_sim.cuh"
+
+namespace mc {
+
+template <typename Real>
+struct SimArgs {
+    unsigned long long n_paths, path_offset, ld_paths, ld_shocks;
+    uint32_t n_steps, pool_len;
+    int pool_log2_copies;          // -1: pool stays in global memory
+    RoundKeys rk;
+    const Real* pool;
+    const Real* shocks;
+    Real* paths;
+    Real* terminal;
+    Real s0, var0, omega, alpha, beta, drift;   // kernel units
+    double center;
+    BlockPartial* partials;
+    unsigned int* hist0;
+};
+
+__device__ __forceinline__ float exp_units(float y) { return fast_ex2(y); }
+__device__ __forceinline__ double exp_units(double y) { return exp(y); }
+__device__ __forceinline__ float sqrt_units(float v) { return fast_sqrt(v); }
+__device__ __forceinline__ double sqrt_units(double v) { return sqrt(v); }
+__device__ __forceinline__ float fma_units(float a, float b, float c) { return fmaf(a, b, c); }
+__device__ __forceinline__ double fma_units(double a, double b, double c) { return fma(a, b, c); }
+
+// ------------------------------------------------------------------ block reduction
+__device__ __forceinline__ double shfl_down_f64(double v, int d) { return __shfl_down_sync(0xffffffffu, v, d); }
+__device__ __forceinline__ unsigned long long shfl_down_u64(unsigned long long v, int d) {
+    return __shfl_down_sync(0xffffffffu, v, d);
+}
+
+__device__ __forceinline__ void combine(BlockPartial& a, const BlockPartial& b) {
+    a.sum_d += b.sum_d;
+    a.sum_d2 += b.sum_d2;
+    a.vmin = fmin(a.vmin, b.vmin);
+    a.vmax = fmax(a.vmax, b.vmax);
+    a.n += b.n;
+    a.n_above += b.n_above;
+}
+
+__device__ __forceinline__ BlockPartial warp_reduce(BlockPartial p) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        BlockPartial o;
+        o.sum_d = shfl_down_f64(p.sum_d, d);
+        o.sum_d2 = shfl_down_f64(p.sum_d2, d);
+        o.vmin = shfl_down_f64(p.vmin, d);
+        o.vmax = shfl_down_f64(p.vmax, d);
+        o.n = shfl_down_u64(p.n, d);
+        o.n_above = shfl_down_u64(p.n_above, d);
+        combine(p, o);
+    }
+    return p;
+}
+
+// all threads of the block must call; result valid in thread 0
+__device__ __forceinline__ BlockPartial block_reduce(BlockPartial p, BlockPartial* s_warp /*[32]*/) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n_warps = (blockDim.x + 31) >> 5;
+    p = warp_reduce(p);
+    if (lane == 0) s_warp[warp] = p;
+    __syncthreads();
+    if (warp == 0) {
+        BlockPartial q;
+        if (lane < n_warps) q = s_warp[lane];
+        else { q.sum_d = 0; q.sum_d2 = 0; q.vmin = INFINITY; q.vmax = -INFINITY; q.n = 0; q.n_above = 0; }
+        p = warp_reduce(q);
+    }
+    return p;
+}
+
+__device__ __forceinline__ BlockPartial empty_partial() {
+    BlockPartial p;
+    p.sum_d = 0.0; p.sum_d2 = 0.0; p.vmin = INFINITY; p.vmax = -INFINITY; p.n = 0; p.n_above = 0;
+    return p;
+}
+
+template <typename Real>
+__device__ __forceinline__ void account(BlockPartial& acc, unsigned int* s_hist, Real value, Real s0,
+                                        double center) {
+    const double d = (double)value - center;
+    acc.sum_d += d;
+    acc.sum_d2 = fma(d, d, acc.sum_d2);
+    acc.vmin = fmin(acc.vmin, (double)value);
+    acc.vmax = fmax(acc.vmax, (double)value);
+    acc.n += 1;
+    acc.n_above += (value > s0) ? 1ull : 0ull;       // app.py:654
+    const auto key = key_of(value);
+    atomicAdd(&s_hist[(unsigned int)(key >> (KeyT<Real>::bits - DIGIT0_BITS))], 1u);
+}
+
+__device__ __forceinline__ void finish_block(BlockPartial acc, unsigned int* s_hist, BlockPartial* s_warp,
+                                             BlockPartial* partials, unsigned int* hist0) {
+    acc = block_reduce(acc, s_warp);
+    if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+    __syncthreads();
+    for (int i = threadIdx.x; i < DIGIT0_BINS; i += blockDim.x) {
+        const unsigned int c = s_hist[i];
+        if (c) atomicAdd(&hist0[i], c);
+    }
+}
+
+// ------------------------------------------------------------------ shock sources
+template <typename Real, int SHOCK>
+__device__ __forceinline__ void draw4(const SimArgs<Real>& a, const Real* s_pool, unsigned long long i,
+                                      uint32_t c0, uint32_t c1, uint32_t call, uint32_t t, Real (&z)[4]) {
+    if (SHOCK == MC_SHOCK_INJECTED) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            z[k] = (t + k < a.n_steps) ? a.shocks[(unsigned long long)(t + k) * a.ld_shocks + i] : Real(0);
+        return;
+    }
+    const u32x4 w = philox4x32_10(c0, c1, call, 0u, a.rk);
+    if (SHOCK == MC_SHOCK_NORMAL) {
+        normals4<Real>(w, z);
+    } else {
+        const uint32_t u[4] = {w.x, w.y, w.z, w.w};
+        if (a.pool_log2_copies >= 0) {
+            // replicated pool: lane l reads copy (l mod copies), so with 32 copies every
+            // lane stays in its own bank no matter which index it drew
+            const uint32_t copies_mask = (1u << a.pool_log2_copies) - 1u;
+            const uint32_t sub = threadIdx.x & copies_mask;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                z[k] = s_pool[(bootstrap_index(u[k], a.pool_len) << a.pool_log2_copies) + sub];
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) z[k] = __ldg(&a.pool[bootstrap_index(u[k], a.pool_len)]);
+        }
+    }
+}
+
+// one step of app.py:623-633 in log space; y excludes the deterministic drift
+template <typename Real, int VAR>
+__device__ __forceinline__ void step(const SimArgs<Real>& a, Real z, Real sig, Real& y, Real& v) {
+    if (VAR == MC_VAR_CONST) {
+        y = fma_units(sig, z, y);
+    } else {
+        const Real r = z * sqrt_units(v);                         // app.py:623-626
+        y += r;                                                   // app.py:629
+        v = fma_units(a.alpha, r * r, fma_units(a.beta, v, a.omega));   // app.py:632-633
+    }
+}
+
+template <typename Real, int SHOCK, int VAR, bool STORE, int MAXB>
+__global__ void __launch_bounds__(MAXB) sim_kernel(const __grid_constant__ SimArgs<Real> a) {
+    extern __shared__ __align__(16) unsigned char smem_dyn[];
+    __shared__ unsigned int s_hist[DIGIT0_BINS];
+    __shared__ BlockPartial s_warp[32];
+    Real* s_pool = reinterpret_cast<Real*>(smem_dyn);
+
+    for (int i = threadIdx.x; i < DIGIT0_BINS; i += blockDim.x) s_hist[i] = 0u;
+    if (SHOCK == MC_SHOCK_BOOTSTRAP && a.pool_log2_copies >= 0) {
+        const uint32_t total = a.pool_len << a.pool_log2_copies;
+        for (uint32_t i = threadIdx.x; i < total; i += blockDim.x) s_pool[i] = a.pool[i >> a.pool_log2_copies];
+    }
+    __syncthreads();
+
+    BlockPartial acc = empty_partial();
+    const Real sig = (VAR == MC_VAR_CONST) ? sqrt_units(a.var0) : Real(0);
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    const uint32_t n_full = a.n_steps >> 2;
+
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n_paths;
+         i += stride) {
+        const unsigned long long gid = a.path_offset + i;
+        const uint32_t c0 = (uint32_t)gid, c1 = (uint32_t)(gid >> 32);
+        Real y = Real(0), v = a.var0;
+        if (STORE) a.paths[i] = a.s0;                              // app.py:613
+
+        constexpr bool FUSED_SUM = (SHOCK == MC_SHOCK_NORMAL && VAR == MC_VAR_CONST && !STORE &&
+                                    sizeof(Real) == 4);
+        uint32_t t = 0;
+        if (FUSED_SUM) {
+            // constant sigma and nothing stored: y_T = sig * sum z.  The Box-Muller radius
+            // constant and sigma are applied once after the loop; each normal costs one FFMA.
+            float s = 0.0f;
+#pragma unroll 2
+            for (uint32_t j = 0; j < n_full; ++j) {
+                const u32x4 w = philox4x32_10(c0, c1, j, 0u, a.rk);
+                const float r0 = bm_rho(w.x), th0 = bm_theta(w.y);
+                const float r1 = bm_rho(w.z), th1 = bm_theta(w.w);
+                s = fmaf(r0, fast_cos(th0), s);
+                s = fmaf(r0, fast_sin(th0), s);
+                s = fmaf(r1, fast_cos(th1), s);
+                s = fmaf(r1, fast_sin(th1), s);
+            }
+            y = (Real)(sig * BM_RADIUS_SCALE_F * s);
+            t = n_full << 2;
+        } else {
+#pragma unroll 2
+            for (uint32_t j = 0; j < n_full; ++j) {
+                Real z[4];
+                draw4<Real, SHOCK>(a, s_pool, i, c0, c1, j, t, z);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    step<Real, VAR>(a, z[k], sig, y, v);
+                    if (STORE)
+                        a.paths[(unsigned long long)(t + k + 1) * a.ld_paths + i] =
+                            a.s0 * exp_units(fma_units((Real)(t + k + 1), a.drift, y));
+                }
+                t += 4;
+            }
+        }
+        if (t < a.n_steps) {   // ragged tail: n_steps not a multiple of 4
+            Real z[4];
+            draw4<Real, SHOCK>(a, s_pool, i, c0, c1, n_full, t, z);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                if (t + k < a.n_steps) {
+                    step<Real, VAR>(a, z[k], sig, y, v);
+                    if (STORE)
+                        a.paths[(unsigned long long)(t + k + 1) * a.ld_paths + i] =
+                            a.s0 * exp_units(fma_units((Real)(t + k + 1), a.drift, y));
+                }
+            }
+        }
+        const Real final_price = a.s0 * exp_units(fma_units((Real)a.n_steps, a.drift, y));
+        a.terminal[i] = final_price;                               // app.py:636
+        account<Real>(acc, s_hist, final_price, a.s0, a.center);
+    }
+    finish_block(acc, s_hist, s_warp, a.partials, a.hist0);
+}
+
+// ------------------------------------------------------------------ correlated portfolio
+// Mode P (north_star extension; nothing like it in the reference): d assets driven by
+// y = L z with L the Cholesky factor of the correlation matrix.  L (pre-scaled by
+// sigma_i sqrt(dt)) arrives as a kernel PARAMETER, i.e. in the constant bank, so the
+// 136 FFMAs of the d=16 triangular product read it as an instruction operand and the
+// kernel keeps no mutable global state (concurrent handles cannot race).
+template <typename Real, int D>
+struct PortArgs {
+    unsigned long long n_paths, path_offset, ld_paths, ld_shocks;
+    uint32_t n_steps, calls_per_step, n_assets;
+    RoundKeys rk;
+    const Real* shocks;
+    Real* paths;
+    Real* terminal;
+    Real v0;                          // portfolio value at t=0
+    double center;
+    BlockPartial* partials;
+    unsigned int* hist0;
+    Real chol[D * (D + 1) / 2];       // packed lower triangle, row-major, kernel units
+    Real drift[D];                    // per step, kernel units
+    Real s0w[D];                      // w_i * S0_i
+};
+
+template <typename Real, int D>
+__device__ __forceinline__ Real portfolio_value(const PortArgs<Real, D>& a, const Real (&x)[D], Real steps_done) {
+    Real v = Real(0);
+#pragma unroll
+    for (int i = 0; i < D; ++i) v = fma_units(a.s0w[i], exp_units(fma_units(steps_done, a.drift[i], x[i])), v);
+    return v;
+}
+
+template <typename Real, int D, bool INJECTED, bool STORE>
+__global__ void __launch_bounds__(SIM_BLOCK) portfolio_kernel(const __grid_constant__ PortArgs<Real, D> a) {
+    __shared__ unsigned int s_hist[DIGIT0_BINS];
+    __shared__ BlockPartial s_warp[32];
+    for (int i = threadIdx.x; i < DIGIT0_BINS; i += blockDim.x) s_hist[i] = 0u;
+    __syncthreads();
+
+    BlockPartial acc = empty_partial();
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n_paths;
+         i += stride) {
+        const unsigned long long gid = a.path_offset + i;
+        const uint32_t c0 = (uint32_t)gid, c1 = (uint32_t)(gid >> 32);
+        Real x[D];
+#pragma unroll
+        for (int k = 0; k < D; ++k) x[k] = Real(0);
+        if (STORE) a.paths[i] = a.v0;
+        uint32_t call = 0;
+        for (uint32_t t = 0; t < a.n_steps; ++t) {
+            Real z[D];
+            if (INJECTED) {
+#pragma unroll
+                for (int k = 0; k < D; ++k) {
+                    const unsigned long long row = (unsigned long long)t * a.n_assets + k;
+                    z[k] = (k < (int)a.n_assets) ? a.shocks[row * a.ld_shocks + i] : Real(0);
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < D / 4; ++q) {
+                    Real zq[4] = {Real(0), Real(0), Real(0), Real(0)};
+                    if (q < (int)a.calls_per_step) {
+                        const u32x4 w = philox4x32_10(c0, c1, call + q, 0u, a.rk);
+                        normals4<Real>(w, zq);
+                    }
+                    z[4 * q + 0] = zq[0]; z[4 * q + 1] = zq[1]; z[4 * q + 2] = zq[2]; z[4 * q + 3] = zq[3];
+                }
+                call += a.calls_per_step;
+            }
+#pragma unroll
+            for (int r = 0; r < D; ++r) {
+                Real s = x[r];
+#pragma unroll
+                for (int c = 0; c <= r; ++c) s = fma_units(a.chol[r * (r + 1) / 2 + c], z[c], s);
+                x[r] = s;
+            }
+            if (STORE)
+                a.paths[(unsigned long long)(t + 1) * a.ld_paths + i] = portfolio_value<Real, D>(a, x, (Real)(t + 1));
+        }
+        const Real v_final = portfolio_value<Real, D>(a, x, (Real)a.n_steps);
+        a.terminal[i] = v_final;
+        account<Real>(acc, s_hist, v_final, a.v0, a.center);
+    }
+    finish_block(acc, s_hist, s_warp, a.partials, a.hist0);
+}
+
+// ------------------------------------------------------------------ debug / test kernels
+template <typename Real, int SHOCK>
+__global__ void debug_shocks_kernel(const SimArgs<Real> a, Real* out) {
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    const uint32_t n_calls = (a.n_steps + 3) >> 2;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n_paths;
+         i += stride) {
+        const unsigned long long gid = a.path_offset + i;
+        for (uint32_t j = 0; j < n_calls; ++j) {
+            Real z[4];
+            draw4<Real, SHOCK>(a, nullptr, i, (uint32_t)gid, (uint32_t)(gid >> 32), j, 4 * j, z);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (4 * j + k < a.n_steps) out[(unsigned long long)(4 * j + k) * a.n_paths + i] = z[k];
+        }
+    }
+}
+
+__global__ void debug_philox_kernel(const uint32_t* ctr, uint32_t n, uint32_t k0, uint32_t k1, uint32_t* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u32x4 w = philox4x32_10(ctr[4 * i], ctr[4 * i + 1], ctr[4 * i + 2], ctr[4 * i + 3], expand_key(k0, k1));
+    out[4 * i] = w.x; out[4 * i + 1] = w.y; out[4 * i + 2] = w.z; out[4 * i + 3] = w.w;
+}
+
+// per-block partials -> stage-0 header; one block, fixed summation order => deterministic
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const BlockPartial* partials, int n,
+                                                              unsigned long long* words) {
+    __shared__ BlockPartial s[256];
+    BlockPartial acc = empty_partial();
+    for (int i = threadIdx.x; i < n; i += 256) combine(acc, partials[i]);
+    s[threadIdx.x] = acc;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) {
+        if ((int)threadIdx.x < w) combine(s[threadIdx.x], s[threadIdx.x + w]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        words[0] = s[0].n;
+        words[1] = s[0].n_above;
+        words[2] = (unsigned long long)__double_as_longlong(s[0].sum_d);
+        words[3] = (unsigned long long)__double_as_longlong(s[0].sum_d2);
+        words[4] = (unsigned long long)__double_as_longlong(s[0].vmin);
+        words[5] = (unsigned long long)__double_as_longlong(s[0].vmax);
+    }
+}
+
+// ------------------------------------------------------------------ host side
+static const double LOG2E = 1.4426950408889634074;
+
+template <typename Real> static double unit_scale() { return sizeof(Real) == 4 ? LOG2E : 1.0; }
+
+template <typename Real>
+static SimArgs<Real> make_args(const mc_params& p, const SimBuffers& b) {
+    const double u = unit_scale<Real>();
+    SimArgs<Real> a;
+    a.n_paths = p.n_paths;
+    a.path_offset = p.path_offset;
+    a.ld_paths = p.paths_ld ? p.paths_ld : p.n_paths;
+    a.ld_shocks = p.n_paths;
+    a.n_steps = p.n_steps;
+    a.rk = expand_key((uint32_t)p.seed, (uint32_t)(p.seed >> 32));
+    a.pool_len = p.pool_len;
+    a.pool_log2_copies = -1;
+    a.pool = static_cast<const Real*>(b.d_pool);
+    a.shocks = static_cast<const Real*>(b.d_shocks);
+    a.paths = static_cast<Real*>(b.d_paths);
+    a.terminal = static_cast<Real*>(b.d_terminal);
+    a.s0 = (Real)p.s0;
+    a.var0 = (Real)(p.var0 * u * u);
+    a.omega = (Real)(p.omega * u * u);
+    a.alpha = (Real)p.alpha;
+    a.beta = (Real)p.beta;
+    a.drift = (Real)(p.drift * u);
+    a.center = p.s0;
+    a.partials = b.d_partials;
+    a.hist0 = b.d_hist0;
+    return a;
+}
+
+template <typename Kernel>
+static cudaError_t pick_grid(Kernel kernel, int block, size_t smem, const DeviceInfo& dev,
+                             unsigned long long n, int* grid) {
+    cudaError_t e;
+    if (smem > 48 * 1024) {
+        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    unsigned long long resident = (unsigned long long)dev.sm_count * per_sm;
+    if (resident > MAX_SIM_GRID) resident = MAX_SIM_GRID;
+    unsigned long long need = (n + block - 1) / block;
+    if (need < 1) need = 1;
+    unsigned long long g = need < resident ? need : resident;
+    // even out the tail: same number of grid-stride rounds, fewest blocks that cover n
+    const unsigned long long rounds = (n + g * block - 1) / (g * block);
+    if (rounds > 0) {
+        const unsigned long long g2 = (n + rounds * block - 1) / (rounds * block);
+        if (g2 >= 1 && g2 < g) g = g2;
+    }
+    *grid = (int)g;
+    return cudaSuccess;
+}
+
+template <typename Real, int SHOCK, int VAR, bool STORE>
+static cudaError_t launch_single(const mc_params& p, const SimBuffers& b, const DeviceInfo& dev, int* grid,
+                                 cudaStream_t stream) {
+    constexpr int MAXB = sizeof(Real) == 4 ? 1024 : 256;
+    SimArgs<Real> a = make_args<Real>(p, b);
+    int block = SIM_BLOCK;
+    size_t smem = 0;
+    if (SHOCK == MC_SHOCK_BOOTSTRAP) {
+        block = MAXB;
+        // static smem: 16 KB digit histogram + 1.5 KB warp partials
+        const size_t budget = (MAXB == 1024) ? (size_t)dev.max_smem_optin - 20 * 1024 : 40 * 1024;
+        int lg = 5;
+        while (lg >= 0 && ((size_t)p.pool_len << lg) * sizeof(Real) > budget) --lg;
+        a.pool_log2_copies = lg;               // -1 => gather from global/L1
+        smem = lg >= 0 ? ((size_t)p.pool_len << lg) * sizeof(Real) : 0;
+        if (p.n_paths < (unsigned long long)block * dev.sm_count) {
+            // small request: spread over more SMs with narrower blocks and a narrower replication
+            block = 128;
+            int lg2 = 5;
+            while (lg2 >= 0 && ((size_t)p.pool_len << lg2) * sizeof(Real) > 24 * 1024) --lg2;
+            a.pool_log2_copies = lg2;
+            smem = lg2 >= 0 ? ((size_t)p.pool_len << lg2) * sizeof(Real) : 0;
+        }
+    }
+    auto kernel = sim_kernel<Real, SHOCK, VAR, STORE, MAXB>;
+    cudaError_t e = pick_grid(kernel, block, smem, dev, p.n_paths, grid);
+    if (e != cudaSuccess) return e;
+    kernel<<<*grid, block, smem, stream>>>(a);
+    return cudaGetLastError();
+}
+
+template <typename Real, int SHOCK, int VAR>
+static cudaError_t dispatch_store(const mc_params& p, const SimBuffers& b, const DeviceInfo& dev, int* grid,
+                                  cudaStream_t s) {
+    return (p.flags & MC_FLAG_STORE_PATHS) ? launch_single<Real, SHOCK, VAR, true>(p, b, dev, grid, s)
+                                           : launch_single<Real, SHOCK, VAR, false>(p, b, dev, grid, s);
+}
+template <typename Real, int SHOCK>
+static cudaError_t dispatch_var(const mc_params& p, const SimBuffers& b, const DeviceInfo& dev, int* grid,
+                                cudaStream_t s) {
+    return p.var_model == MC_VAR_CONST ? dispatch_store<Real, SHOCK, MC_VAR_CONST>(p, b, dev, grid, s)
+                                       : dispatch_store<Real, SHOCK, MC_VAR_GARCH>(p, b, dev, grid, s);
+}
+template <typename Real>
+static cudaError_t dispatch_shock(const mc_params& p, const SimBuffers& b, const DeviceInfo& dev, int* grid,
+                                  cudaStream_t s) {
+    switch (p.shock) {
+        case MC_SHOCK_BOOTSTRAP: return dispatch_var<Real, MC_SHOCK_BOOTSTRAP>(p, b, dev, grid, s);
+        case MC_SHOCK_NORMAL: return dispatch_var<Real, MC_SHOCK_NORMAL>(p, b, dev, grid, s);
+        case MC_SHOCK_INJECTED: return dispatch_var<Real, MC_SHOCK_INJECTED>(p, b, dev, grid, s);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+template <typename Real, int D, bool INJECTED, bool STORE>
+static cudaError_t launch_portfolio_impl(const mc_params& p, const mc_portfolio& pf, const SimBuffers& b,
+                                         const DeviceInfo& dev, int* grid, cudaStream_t stream) {
+    const double u = unit_scale<Real>();
+    const int d = (int)p.n_assets;
+    static PortArgs<Real, D> proto;      // zero-initialised template; copied, never mutated
+    PortArgs<Real, D> a = proto;
+    a.n_paths = p.n_paths;
+    a.path_offset = p.path_offset;
+    a.ld_paths = p.paths_ld ? p.paths_ld : p.n_paths;
+    a.ld_shocks = p.n_paths;
+    a.n_steps = p.n_steps;
+    a.rk = expand_key((uint32_t)p.seed, (uint32_t)(p.seed >> 32));
+    a.calls_per_step = (uint32_t)((d + 3) / 4);
+    a.n_assets = (uint32_t)d;
+    a.shocks = static_cast<const Real*>(b.d_shocks);
+    a.paths = static_cast<Real*>(b.d_paths);
+    a.terminal = static_cast<Real*>(b.d_terminal);
+    double v0 = 0.0;
+    for (int i = 0; i < d; ++i) {
+        for (int c = 0; c <= i; ++c)
+            a.chol[i * (i + 1) / 2 + c] = (Real)(pf.h_chol[i * d + c] * pf.h_sigma_step[i] * u);
+        a.drift[i] = (Real)(pf.h_drift_step[i] * u);
+        a.s0w[i] = (Real)(pf.h_s0[i] * pf.h_weights[i]);
+        v0 += pf.h_s0[i] * pf.h_weights[i];
+    }
+    a.v0 = (Real)v0;
+    a.center = p.s0;
+    a.partials = b.d_partials;
+    a.hist0 = b.d_hist0;
+    auto kernel = portfolio_kernel<Real, D, INJECTED, STORE>;
+    cudaError_t e = pick_grid(kernel, SIM_BLOCK, 0, dev, p.n_paths, grid);
+    if (e != cudaSuccess) return e;
+    kernel<<<*grid, SIM_BLOCK, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+template <typename Real, int D>
+static cudaError_t launch_portfolio_d(const mc_params& p, const mc_portfolio& pf, const SimBuffers& b,
+                                      const DeviceInfo& dev, int* grid, cudaStream_t s) {
+    const bool inj = p.shock == MC_SHOCK_INJECTED, st = (p.flags & MC_FLAG_STORE_PATHS) != 0;
+    if (inj) return st ? launch_portfolio_impl<Real, D, true, true>(p, pf, b, dev, grid, s)
+                       : launch_portfolio_impl<Real, D, true, false>(p, pf, b, dev, grid, s);
+    return st ? launch_portfolio_impl<Real, D, false, true>(p, pf, b, dev, grid, s)
+              : launch_portfolio_impl<Real, D, false, false>(p, pf, b, dev, grid, s);
+}
+
+template <typename Real>
+static cudaError_t launch_portfolio(const mc_params& p, const mc_portfolio& pf, const SimBuffers& b,
+                                    const DeviceInfo& dev, int* grid, cudaStream_t s) {
+    if (p.shock == MC_SHOCK_BOOTSTRAP || p.var_model != MC_VAR_CONST) return cudaErrorInvalidValue;
+    const int d = (int)p.n_assets;
+    if (d <= 4) return launch_portfolio_d<Real, 4>(p, pf, b, dev, grid, s);
+    if (d <= 8) return launch_portfolio_d<Real, 8>(p, pf, b, dev, grid, s);
+    if (d <= 16) return launch_portfolio_d<Real, 16>(p, pf, b, dev, grid, s);
+    if (d <= 32) return launch_portfolio_d<Real, 32>(p, pf, b, dev, grid, s);
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_simulation(const mc_params& p, const mc_portfolio* pf, const SimBuffers& b,
+                              const DeviceInfo& dev, int* grid, cudaStream_t stream) {
+    if (p.n_assets > 1) {
+        if (!pf) return cudaErrorInvalidValue;
+        return p.dtype == MC_F64 ? launch_portfolio<double>(p, *pf, b, dev, grid, stream)
+                                 : launch_portfolio<float>(p, *pf, b, dev, grid, stream);
+    }
+    return p.dtype == MC_F64 ? dispatch_shock<double>(p, b, dev, grid, stream)
+                             : dispatch_shock<float>(p, b, dev, grid, stream);
+}
+
+template <typename Real>
+static cudaError_t debug_shocks_t(const mc_params& p, const void* d_pool, void* d_out, cudaStream_t stream) {
+    SimBuffers b{};
+    b.d_pool = d_pool;
+    SimArgs<Real> a = make_args<Real>(p, b);
+    const int grid = (int)((p.n_paths + 255) / 256 < 4096 ? (p.n_paths + 255) / 256 : 4096);
+    if (p.shock == MC_SHOCK_NORMAL)
+        debug_shocks_kernel<Real, MC_SHOCK_NORMAL><<<grid ? grid : 1, 256, 0, stream>>>(a, static_cast<Real*>(d_out));
+    else if (p.shock == MC_SHOCK_BOOTSTRAP)
+        debug_shocks_kernel<Real, MC_SHOCK_BOOTSTRAP><<<grid ? grid : 1, 256, 0, stream>>>(a, static_cast<Real*>(d_out));
+    else
+        return cudaErrorInvalidValue;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_debug_shocks(const mc_params& p, const void* d_pool, void* d_out, cudaStream_t stream) {
+    return p.dtype == MC_F64 ? debug_shocks_t<double>(p, d_pool, d_out, stream)
+                             : debug_shocks_t<float>(p, d_pool, d_out, stream);
+}
+
+cudaError_t launch_debug_philox(const uint32_t* d_ctr, uint32_t n, uint32_t k0, uint32_t k1, uint32_t* d_out,
+                                cudaStream_t stream) {
+    if (n == 0) return cudaSuccess;
+    debug_philox_kernel<<<(n + 127) / 128, 128, 0, stream>>>(d_ctr, n, k0, k1, d_out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_reduce_partials(const BlockPartial* d_partials, int n_partials, unsigned long long* d_words,
+                                   cudaStream_t stream) {
+    reduce_partials_kernel<<<1, 256, 0, stream>>>(d_partials, n_partials, d_words);
+    return cudaGetLastError();
+}
+
+}  // namespace mc

@@ -1,0 +1,37 @@
+// mc_sim.cuh -- launch interface of the path-stepping kernels (mc_sim.cu).
+#pragma once
+#include "mc_common.cuh"
+
+namespace mc {
+
+struct SimBuffers {
+    const void* d_pool;
+    const void* d_shocks;
+    void* d_paths;
+    void* d_terminal;
+    BlockPartial* d_partials;     // [max_grid]
+    unsigned int* d_hist0;        // [DIGIT0_BINS], zeroed by the caller
+};
+
+constexpr int MAX_SIM_GRID = 148 * 16;
+
+struct DeviceInfo {
+    int sm_count;
+    int max_smem_optin;
+};
+
+// Enqueue the simulation of p.n_paths paths; returns the grid size used in *grid.
+cudaError_t launch_simulation(const mc_params& p, const mc_portfolio* pf, const SimBuffers& b,
+                              const DeviceInfo& dev, int* grid, cudaStream_t stream);
+
+// z[t, i] exactly as the simulator draws them (tests)
+cudaError_t launch_debug_shocks(const mc_params& p, const void* d_pool, void* d_out,
+                                cudaStream_t stream);
+cudaError_t launch_debug_philox(const uint32_t* d_ctr, uint32_t n, uint32_t k0, uint32_t k1,
+                                uint32_t* d_out, cudaStream_t stream);
+
+// fixed-order reduction of the per-block partials into the stage-0 header words
+cudaError_t launch_reduce_partials(const BlockPartial* d_partials, int n_partials,
+                                   unsigned long long* d_stage_words, cudaStream_t stream);
+
+}  // namespace mc
