@@ -1,0 +1,171 @@
+"""Drop-in replacement for the reference's `garch_monte_carlo` (app.py:586-657) plus the
+north_star's GBM and portfolio modes behind the same return structure.
+
+    from montecarlo_b200 import garch_monte_carlo     # replaces the definition in app.py
+    mc_results = garch_monte_carlo(df, mc_sims, forecast_days, current_price, update_status)
+
+Same positional signature (app.py:586-587), same `None` for short histories (app.py:594-595),
+same single progress callback (app.py:597-598), same nine result keys (app.py:647-657).
+Everything new is keyword-only with reference-equivalent defaults."""
+from __future__ import annotations
+
+import math
+import os
+from typing import Dict, Optional
+
+import numpy as np
+
+from .spec import (MIN_HISTORY, REF_ALPHA, REF_BETA, REF_OMEGA, REF_PATH_PCTS, REF_TAIL_PCT,
+                   REF_TERMINAL_PCTS, PortfolioSpec, SimSpec)
+
+# paths are returned as host NumPy arrays (strict structural parity with app.py:648-649) up to
+# this many elements; beyond it they stay on the device as torch tensors
+HOST_PATHS_LIMIT = 1 << 26
+# full paths are only materialised when (T+1)*N*itemsize fits this budget
+DEVICE_PATHS_LIMIT_BYTES = 64 << 30
+
+
+def _history_inputs(df):
+    """The two DataFrame reads of the reference: app.py:592 and app.py:606."""
+    col = df["log_ret"]
+    returns = col.dropna().values if hasattr(col, "dropna") else np.asarray(col, dtype=np.float64)
+    returns = np.asarray(returns, dtype=np.float64)
+    returns = returns[~np.isnan(returns)]
+    rv = df["rvol_20"]
+    rvol_last = float(rv.iloc[-1]) if hasattr(rv, "iloc") else float(np.asarray(rv)[-1])
+    return returns, rvol_last
+
+
+def bootstrap_pool(returns: np.ndarray) -> np.ndarray:
+    """std_returns (app.py:609): scaled by the population std, not demeaned."""
+    return returns / (np.std(returns) + 1e-10)
+
+
+def _new_seed() -> int:
+    # the reference draws from NumPy's unseeded global generator (no seed control anywhere in app.py)
+    return int.from_bytes(os.urandom(8), "little")
+
+
+def _result_dict(out, s0, return_paths: str) -> Dict:
+    res = {}
+    paths, final = out.paths, out.terminal
+    if return_paths == "numpy":
+        if paths is not None:
+            paths = paths.to("cpu").numpy().astype(np.float64, copy=False)
+            final = paths[-1, :]                       # a view of the last row, like app.py:636
+        else:
+            final = final.to("cpu").numpy().astype(np.float64, copy=False)
+    res["paths"] = paths
+    res["final_prices"] = final
+    summ = out.summary()
+    res["percentiles"] = {k: np.float64(v) for k, v in summ["percentiles"].items()}
+    res["path_percentiles"] = out.fan
+    for k in ("expected_return", "expected_vol", "prob_profit"):
+        res[k] = np.float64(summ[k])
+    for k, v in summ.items():
+        if k.startswith("var_") or k.startswith("cvar_"):
+            res[k] = np.float64(v)
+    if out.hist is not None:
+        res["histogram"] = {"counts": out.hist, "range": out.hist_range,
+                            "edges": np.linspace(out.hist_range[0], out.hist_range[1], len(out.hist) + 1)}
+    res["timing"] = {"sim_ms": out.sim_ms, "total_ms": out.total_ms, "launches": out.launches}
+    return res
+
+
+def _decide_paths(n_sims, n_days, dtype, return_paths):
+    itemsize = 8 if dtype == "float64" else 4
+    elems = (n_days + 1) * n_sims
+    if return_paths in (None, "auto"):
+        if elems <= HOST_PATHS_LIMIT:
+            return True, "numpy"
+        if elems * itemsize <= DEVICE_PATHS_LIMIT_BYTES:
+            return True, "device"
+        return False, "device"
+    if return_paths in (True, "numpy"):
+        return True, "numpy"
+    if return_paths == "device":
+        return True, "device"
+    if return_paths in (False, "none"):
+        return False, "device"
+    raise ValueError("return_paths must be 'auto', 'numpy', 'device' or False")
+
+
+def garch_monte_carlo(df, n_sims: int, n_days: int, current_price: float, progress_callback=None, *,
+                      seed: Optional[int] = None, dtype: str = "float64", return_paths="auto",
+                      omega: float = REF_OMEGA, alpha: float = REF_ALPHA, beta: float = REF_BETA,
+                      shock: str = "bootstrap", injected_shocks=None,
+                      hist_bins: int = 0, hist_range=None, device: Optional[int] = None,
+                      group=None) -> Optional[Dict]:
+    """Monte Carlo with volatility clustering: bootstrap shocks + GARCH(1,1) variance,
+    exactly the model of app.py:592-657, computed on a B200.
+
+    Extra keyword-only options: `seed` (Philox key; random if None, like the unseeded
+    reference), `dtype` ('float64' default = the reference's precision, or 'float32'),
+    `return_paths` ('auto' | 'numpy' | 'device' | False), `shock` ('bootstrap' |
+    'normal' | 'injected' with `injected_shocks[T, N]`), `hist_bins`/`hist_range`
+    (adds a 'histogram' key), `group` (torch.distributed group: shard paths over its ranks).
+    """
+    from .engine import get_engine
+    returns, rvol_last = _history_inputs(df)
+    if len(returns) < MIN_HISTORY:                     # app.py:594-595
+        return None
+    if progress_callback:                              # app.py:597-598
+        progress_callback("Running Monte Carlo simulation...")
+    n_sims, n_days = int(n_sims), int(n_days)
+    current_var = rvol_last ** 2 / 252                 # app.py:606
+    pool = bootstrap_pool(returns)                     # app.py:609
+    store, how = _decide_paths(n_sims, n_days, dtype, return_paths)
+    if group is not None and how == "numpy" and return_paths in (None, "auto"):
+        how = "device"                                 # shards stay on their home GPU
+    spec = SimSpec(n_paths=n_sims, n_steps=n_days, s0=float(current_price), shock=shock, var_model="garch",
+                   var0=current_var, omega=omega, alpha=alpha, beta=beta, dtype=dtype,
+                   seed=_new_seed() if seed is None else int(seed), store_paths=store, fan_chart=store,
+                   pcts=REF_TERMINAL_PCTS, path_pcts=REF_PATH_PCTS, tail_pct=REF_TAIL_PCT,
+                   hist_bins=hist_bins, hist_range=hist_range)
+    out = get_engine(device).simulate(spec, pool=pool if shock == "bootstrap" else None,
+                                      shocks=injected_shocks, group=group)
+    return _result_dict(out, float(current_price), how)
+
+
+def simulate_gbm(n_sims: int, n_days: int, current_price: float, mu: float, sigma: float, *,
+                 dt: float = 1.0 / 252, seed: int = 0, dtype: str = "float32", return_paths=False,
+                 fan_chart: Optional[bool] = None, pcts=REF_TERMINAL_PCTS, path_pcts=REF_PATH_PCTS,
+                 tail_pct: Optional[float] = REF_TAIL_PCT, hist_bins: int = 0, hist_range="auto",
+                 injected_shocks=None, device: Optional[int] = None, group=None) -> Dict:
+    """Mode G (north_star configs 2/4/5): geometric Brownian motion with normal shocks,
+    x += (mu - sigma^2/2) dt + sigma sqrt(dt) z, same reductions and result keys as
+    `garch_monte_carlo`.  `hist_range='auto'` = S0*exp(+-6 sigma sqrt(T dt))."""
+    from .engine import get_engine
+    store, how = _decide_paths(n_sims, n_days, dtype, return_paths)
+    if hist_bins and hist_range == "auto":
+        w = 6.0 * sigma * math.sqrt(n_days * dt)
+        hist_range = (current_price * math.exp(-w), current_price * math.exp(w))
+    elif hist_range == "auto":
+        hist_range = None
+    spec = SimSpec.gbm(int(n_sims), int(n_days), float(current_price), mu, sigma, dt, dtype=dtype, seed=int(seed),
+                       shock="injected" if injected_shocks is not None else "normal", store_paths=store,
+                       fan_chart=store if fan_chart is None else (fan_chart and store),
+                       pcts=tuple(pcts), path_pcts=tuple(path_pcts), tail_pct=tail_pct,
+                       hist_bins=hist_bins, hist_range=hist_range)
+    out = get_engine(device).simulate(spec, shocks=injected_shocks, group=group)
+    return _result_dict(out, float(current_price), how)
+
+
+def simulate_portfolio(n_sims: int, n_days: int, s0, mu, sigma, weights, corr=None, *, chol=None,
+                       dt: float = 1.0 / 252, seed: int = 0, dtype: str = "float32", return_paths=False,
+                       pcts=REF_TERMINAL_PCTS, path_pcts=REF_PATH_PCTS, tail_pct: Optional[float] = REF_TAIL_PCT,
+                       hist_bins: int = 0, hist_range=None, injected_shocks=None,
+                       device: Optional[int] = None, group=None) -> Dict:
+    """Mode P (north_star config 3): d correlated assets, y = L z with L = chol(corr);
+    statistics are those of the portfolio value V = sum_i w_i S_i (VaR/CVaR of V)."""
+    from .engine import get_engine
+    store, how = _decide_paths(n_sims, n_days, dtype, return_paths)
+    pf = PortfolioSpec(s0=s0, mu=mu, sigma=sigma, weights=weights, corr=corr, chol=chol, dt=dt)
+    v0 = pf.arrays()["v0"]
+    spec = SimSpec(n_paths=int(n_sims), n_steps=int(n_days), s0=v0,
+                   shock="injected" if injected_shocks is not None else "normal", var_model="const",
+                   dtype=dtype, seed=int(seed), store_paths=store, fan_chart=store, pcts=tuple(pcts),
+                   path_pcts=tuple(path_pcts), tail_pct=tail_pct, hist_bins=hist_bins, hist_range=hist_range,
+                   portfolio=pf)
+    out = get_engine(device).simulate(spec, shocks=injected_shocks, group=group)
+    return _result_dict(out, v0, how)

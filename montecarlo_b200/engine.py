@@ -1,0 +1,288 @@
+"""Engine: owns one `mc_handle` (one GPU) and runs simulation requests on it.
+
+Single GPU: one `mc_run` call.  Path-sharded multi-GPU (one process per GPU,
+`torch.distributed` over NCCL): the staged C entry points with ONE small
+all-gather per stage (`run_stages`) -- no path data ever crosses GPUs.
+The orchestration is backend-agnostic so the same loop is exercised on CPU with the
+gloo backend in tests."""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from .spec import SimSpec, make_params, make_portfolio, shard_range
+
+
+@dataclass
+class RunOutput:
+    spec: SimSpec
+    n: int
+    n_above: int
+    mean: float
+    std: float
+    min: float
+    max: float
+    pct: dict                       # {'p5': value, ...}
+    pct_bounds: dict                # {'p5': (lo order stat, hi order stat)}
+    tail_count: int
+    tail_sum: float
+    hist: Optional[np.ndarray]      # int64[bins]
+    hist_range: Optional[tuple]
+    fan: Optional[dict]             # {'p5': float64[T+1], ...}
+    terminal: Optional[torch.Tensor]   # this rank's final prices (device)
+    paths: Optional[torch.Tensor]      # this rank's [(T+1), n_local] (device) or None
+    sim_ms: float
+    total_ms: float
+    launches: int
+    path_offset: int = 0
+
+    @property
+    def center(self) -> float:
+        return self.spec._pf_arrays["v0"] if self.spec.portfolio is not None else self.spec.s0
+
+    def summary(self) -> dict:
+        """The scalar keys of the reference's result dict (app.py:652-656)."""
+        s0 = self.center
+        out = {
+            "percentiles": dict(self.pct),
+            "expected_return": (self.mean / s0 - 1) * 100,
+            "expected_vol": self.std / s0 * 100,
+            "prob_profit": self.n_above / self.n * 100,
+        }
+        tp = self.spec.tail_pct
+        if tp is not None and self.pct:
+            key = f"p{tp:g}"
+            out[f"var_{100 - tp:g}"] = (s0 - self.pct[key]) / s0 * 100
+            tail_mean = self.tail_sum / self.tail_count if self.tail_count else float("nan")
+            out[f"cvar_{100 - tp:g}"] = (s0 - tail_mean) / s0 * 100
+        return out
+
+
+def run_stages(backend, group=None):
+    """Drive a stage backend to completion.  `backend` offers begin(), stage_words(),
+    stage_view(words), gather_view(total_words), next(gathered, n_ranks) -> done."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group) if group is not None else 1
+    backend.begin()
+    done = False
+    while not done:
+        words = backend.stage_words()
+        local = backend.stage_view(words)
+        if world > 1:
+            gathered = backend.gather_view(world * words)
+            dist.all_gather_into_tensor(gathered, local, group=group)
+        else:
+            gathered = local
+        done = backend.next(gathered, world)
+    return world
+
+
+class _CudaStageBackend:
+
+    def __init__(self, engine, params, pf, pool, shocks, paths, terminal, world):
+        self.e, self.params, self.pf = engine, params, pf
+        self.pool, self.shocks, self.paths, self.terminal = pool, shocks, paths, terminal
+        cap = int(engine.lib.mc_stage_max_words(C.byref(params)))
+        self.stage = torch.empty(cap, dtype=torch.int64, device=engine.device)
+        self.gathered = torch.empty(cap * world, dtype=torch.int64, device=engine.device) if world > 1 else None
+        self.cap = cap
+
+    @staticmethod
+    def _ptr(t):
+        return C.c_void_p(t.data_ptr()) if t is not None and t.numel() else C.c_void_p(0)
+
+    def begin(self):
+        e = self.e
+        e.check(e.lib.mc_stage_begin(e.handle, C.byref(self.params), C.byref(self.pf) if self.pf else None,
+                                     self._ptr(self.pool), self._ptr(self.shocks), self._ptr(self.paths),
+                                     self._ptr(self.terminal), self._ptr(self.stage), self.cap, e.stream_ptr()))
+
+    def stage_words(self):
+        return int(self.e.lib.mc_stage_words(self.e.handle))
+
+    def stage_view(self, words):
+        return self.stage[:words]
+
+    def gather_view(self, total):
+        return self.gathered[:total]
+
+    def next(self, gathered, n_ranks):
+        done = C.c_int(0)
+        e = self.e
+        e.check(e.lib.mc_stage_next(e.handle, C.c_void_p(gathered.data_ptr()), n_ranks, self._ptr(self.stage),
+                                    C.byref(done), e.stream_ptr()))
+        return bool(done.value)
+
+
+class Engine:
+    """One per (thread, device).  Thread-safe through the handle's own mutex, but a
+    handle serialises its calls: use one Engine per concurrent caller."""
+
+    def __init__(self, device: Optional[int] = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("montecarlo_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.lib = L.load_library()
+        self.device_index = torch.cuda.current_device() if device is None else int(device)
+        self.device = torch.device("cuda", self.device_index)
+        h = C.c_void_p()
+        rc = self.lib.mc_create(self.device_index, C.byref(h))
+        if rc != 0:
+            raise RuntimeError(f"mc_create failed: {self.lib.mc_last_error(None).decode()}")
+        self.handle = h
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.mc_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def check(self, rc):
+        if rc != 0:
+            raise RuntimeError(f"montecarlo_b200 error {rc}: {self.lib.mc_last_error(self.handle).decode()}")
+
+    def stream_ptr(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # ------------------------------------------------------------------ helpers
+    def _torch_dtype(self, spec):
+        return torch.float64 if spec.dtype == "float64" else torch.float32
+
+    def to_device(self, x, dtype):
+        """Host array -> device through pinned memory (or pass a device tensor through)."""
+        if x is None:
+            return None
+        if isinstance(x, torch.Tensor):
+            if x.device == self.device and x.dtype == dtype and x.is_contiguous():
+                return x
+            return x.to(device=self.device, dtype=dtype).contiguous()
+        host = torch.from_numpy(np.ascontiguousarray(x)).to(dtype)
+        return host.pin_memory().to(self.device, non_blocking=True)
+
+    # ------------------------------------------------------------------ main entry
+    def simulate(self, spec: SimSpec, pool=None, shocks=None, group=None, keep_paths=True) -> RunOutput:
+        """Run `spec`.  With `group` (a torch.distributed process group, or True for the
+        default group) the spec's n_paths are sharded over the group's ranks."""
+        import torch.distributed as dist
+        dt = self._torch_dtype(spec)
+        world, rank = 1, 0
+        if group is True:
+            group = dist.group.WORLD
+        if group is not None:
+            world, rank = dist.get_world_size(group), dist.get_rank(group)
+        offset, n_local = shard_range(spec.n_paths, rank, world)
+        if spec.shock == "bootstrap":
+            if pool is None:
+                raise ValueError("bootstrap shocks need a pool")
+            pool_t = self.to_device(pool, dt)
+            spec.pool_len = int(pool_t.numel())
+        else:
+            pool_t = None
+        shocks_t = self.to_device(shocks, dt) if spec.shock == "injected" else None
+        if shocks_t is not None:
+            rows = spec.n_steps * (spec.portfolio.arrays()["d"] if spec.portfolio is not None else 1)
+            if shocks_t.numel() != rows * n_local:
+                raise ValueError(f"injected shocks must have shape [{rows}, {n_local}] on this rank")
+        with torch.cuda.device(self.device):
+            terminal = torch.empty(n_local, dtype=dt, device=self.device)
+            paths = torch.empty((spec.n_steps + 1, n_local), dtype=dt, device=self.device) if spec.store_paths else None
+            params = make_params(spec, path_offset=offset, n_local=n_local)
+            pf = make_portfolio(spec)
+            res = L.McResult()
+            hist = np.zeros(spec.hist_bins, dtype=np.uint64) if spec.hist_bins else None
+            fan = np.zeros((len(spec.path_pcts), spec.n_steps + 1)) if (spec.fan_chart and spec.path_pcts) else None
+            hist_p = C.c_void_p(hist.ctypes.data) if hist is not None else C.c_void_p(0)
+            fan_p = C.c_void_p(fan.ctypes.data) if fan is not None else C.c_void_p(0)
+            ptr = _CudaStageBackend._ptr
+            if world == 1:
+                self.check(self.lib.mc_run(self.handle, C.byref(params), C.byref(pf) if pf else None, ptr(pool_t),
+                                           ptr(shocks_t), ptr(paths), ptr(terminal), C.byref(res), hist_p, fan_p,
+                                           self.stream_ptr()))
+            else:
+                backend = _CudaStageBackend(self, params, pf, pool_t, shocks_t, paths, terminal, world)
+                run_stages(backend, group)
+                self.check(self.lib.mc_fetch_result(self.handle, C.byref(res), hist_p, fan_p, self.stream_ptr()))
+        return self._pack(spec, res, hist, fan, terminal, paths if keep_paths else None, offset)
+
+    def _pack(self, spec, res, hist, fan, terminal, paths, offset) -> RunOutput:
+        names = [f"p{p:g}" for p in spec.pcts]
+        pct = {k: float(res.pct[i]) for i, k in enumerate(names)}
+        bounds = {k: (float(res.pct_lo[i]), float(res.pct_hi[i])) for i, k in enumerate(names)}
+        fan_d = {f"p{p:g}": fan[i] for i, p in enumerate(spec.path_pcts)} if fan is not None else None
+        return RunOutput(spec=spec, n=int(res.n), n_above=int(res.n_above), mean=float(res.mean), std=float(res.std),
+                         min=float(res.min), max=float(res.max), pct=pct, pct_bounds=bounds,
+                         tail_count=int(res.tail_count), tail_sum=float(res.tail_sum),
+                         hist=hist.astype(np.int64) if hist is not None else None,
+                         hist_range=(float(res.hist_lo), float(res.hist_hi)) if hist is not None else None,
+                         fan=fan_d, terminal=terminal, paths=paths, sim_ms=float(res.sim_ms),
+                         total_ms=float(res.total_ms), launches=int(res.launches), path_offset=offset)
+
+    # ------------------------------------------------------------------ building blocks
+    def percentiles(self, x: torch.Tensor, pcts) -> np.ndarray:
+        """np.percentile(x, pcts, axis=-1) for a device vector or [rows, n] matrix -> [rows, len(pcts)]."""
+        x2 = x if x.dim() == 2 else x.view(1, -1)
+        if x2.stride(1) != 1:
+            x2 = x2.contiguous()
+        rows, n = x2.shape
+        pc = (C.c_double * len(pcts))(*[float(p) for p in pcts])
+        out = np.zeros((rows, len(pcts)))
+        dtype = L.F64 if x2.dtype == torch.float64 else L.F32
+        if x2.dtype not in (torch.float32, torch.float64):
+            raise TypeError("percentiles needs float32/float64")
+        self.check(self.lib.mc_percentiles(self.handle, C.c_void_p(x2.data_ptr()), dtype, rows, n, x2.stride(0), pc,
+                                           len(pcts), C.c_void_p(out.ctypes.data), self.stream_ptr()))
+        return out
+
+    def histogram(self, x: torch.Tensor, bins: int, lo: float, hi: float) -> np.ndarray:
+        x = x.contiguous().view(-1)
+        out = np.zeros(bins, dtype=np.uint64)
+        dtype = L.F64 if x.dtype == torch.float64 else L.F32
+        self.check(self.lib.mc_histogram(self.handle, C.c_void_p(x.data_ptr()), dtype, x.numel(), bins, lo, hi,
+                                         C.c_void_p(out.ctypes.data), self.stream_ptr()))
+        return out.astype(np.int64)
+
+    def debug_shocks(self, spec: SimSpec, pool=None, path_offset=0, n_local=None) -> torch.Tensor:
+        dt = self._torch_dtype(spec)
+        pool_t = self.to_device(pool, dt) if pool is not None else None
+        if pool_t is not None:
+            spec.pool_len = int(pool_t.numel())
+        n_local = spec.n_paths if n_local is None else n_local
+        params = make_params(spec, path_offset=path_offset, n_local=n_local)
+        out = torch.empty((spec.n_steps, n_local), dtype=dt, device=self.device)
+        self.check(self.lib.mc_debug_shocks(self.handle, C.byref(params), _CudaStageBackend._ptr(pool_t),
+                                            C.c_void_p(out.data_ptr()), self.stream_ptr()))
+        return out
+
+    def debug_philox(self, counters: np.ndarray, key0: int, key1: int) -> np.ndarray:
+        ctr = torch.from_numpy(np.ascontiguousarray(counters, dtype=np.uint32).view(np.int32)).to(self.device)
+        n = ctr.numel() // 4
+        out = torch.empty(4 * n, dtype=torch.int32, device=self.device)
+        self.check(self.lib.mc_debug_philox(self.handle, C.c_void_p(ctr.data_ptr()), n, key0, key1,
+                                            C.c_void_p(out.data_ptr()), self.stream_ptr()))
+        return out.cpu().numpy().view(np.uint32).reshape(n, 4)
+
+
+_engines = threading.local()
+
+
+def get_engine(device: Optional[int] = None) -> Engine:
+    """Per-thread, per-device cached Engine (the app runs sessions in threads, app.py:1392)."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("montecarlo_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    idx = torch.cuda.current_device() if device is None else int(device)
+    cache = getattr(_engines, "cache", None)
+    if cache is None:
+        cache = _engines.cache = {}
+    if idx not in cache:
+        cache[idx] = Engine(idx)
+    return cache[idx]
