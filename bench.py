@@ -1,0 +1,383 @@
+#!/usr/bin/env python
+"""bench.py -- path-steps/sec of the Monte Carlo hot path on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c4|c5|c3|ref] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one whole simulation job (all paths x all time steps + every reduction the
+reference's result dict holds) on synthetic parameters.  Default workload is BASELINE.json
+configs[1] ("c2": single-asset GBM, 10M paths x 252 steps fp32, terminal stats + percentiles)
+per GPU -- weak scaling: with N ranks the job is N x 10M paths, sharded by global path id and
+merged with one small all-gather per stage.  Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+SEED = 0x123456789ABCDEF0
+S0, MU, SIGMA, DT = 100.0, 0.05, 0.20, 1.0 / 252
+
+# paths per GPU, steps, description
+WORKLOADS = {
+    "c2": dict(paths=10_000_000, steps=252, desc="single-asset GBM 10M paths x 252 steps fp32, terminal stats + "
+                                                 "9 percentiles + CVaR + 2048-bin histogram (BASELINE configs[1])"),
+    "c4": dict(paths=12_500_000, steps=2520, desc="single-asset GBM 2520 steps fp32, 12.5M paths per GPU "
+                                                  "(= 100M over 8 GPUs, BASELINE configs[3])"),
+    "c5": dict(paths=4_194_304, steps=1024, desc="GBM 4M paths x 1024 steps fp32, full paths stored to HBM + "
+                                                 "per-step fan chart (BASELINE configs[4])"),
+    "c3": dict(paths=1_000_000, steps=252, desc="16-asset Cholesky portfolio 1M paths x 252 steps fp32, "
+                                                "VaR/CVaR (BASELINE configs[2])"),
+    "ref": dict(paths=10_000_000, steps=252, desc="reference model (bootstrap + GARCH(1,1), app.py:618-633) "
+                                                  "10M paths x 252 steps fp32"),
+}
+# algorithmic work per path-step of the fused kernels -> path-steps per SM-clock
+STEPS_PER_SM_CLK = {"c2": 8.0, "c4": 8.0, "ref": 7.5, "c3": 0.33}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0=None, t1=None):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, pw, reasons = [], [], [], set()
+        for ts, line in self.rows:
+            if t0 is not None and not (t0 <= ts <= t1 + 0.1):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw),
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return json.load(fh), "measured"
+    except OSError:
+        return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
+
+
+# --------------------------------------------------------------------------- this repo's arm
+def hist_range(t):
+    w = 6.0 * SIGMA * math.sqrt(t * DT)
+    return (S0 * math.exp(-w), S0 * math.exp(w))
+
+
+def synthetic_history():
+    import numpy as np
+    rs = np.random.RandomState(0)
+    return rs.normal(0.0, 0.02, 1250), 0.02 * math.sqrt(252)
+
+
+def make_spec(workload, world):
+    import numpy as np
+    from montecarlo_b200 import PortfolioSpec, SimSpec
+    from montecarlo_b200.api import bootstrap_pool
+    w = WORKLOADS[workload]
+    n, t = w["paths"] * world, w["steps"]
+    pool = None
+    if workload in ("c2", "c4"):
+        spec = SimSpec.gbm(n, t, S0, MU, SIGMA, DT, seed=SEED, hist_bins=2048, hist_range=hist_range(t))
+    elif workload == "c5":
+        spec = SimSpec.gbm(n, t, S0, MU, SIGMA, DT, seed=SEED, hist_bins=2048, hist_range=hist_range(t),
+                           store_paths=True, fan_chart=True)
+    elif workload == "c3":
+        d = 16
+        corr = np.full((d, d), 0.3) + 0.7 * np.eye(d)
+        pf = PortfolioSpec(s0=np.full(d, S0), mu=MU, sigma=0.15 + 0.01 * np.arange(d), weights=np.full(d, 1 / d),
+                           corr=corr, dt=DT)
+        spec = SimSpec(n_paths=n, n_steps=t, s0=S0, shock="normal", var_model="const", seed=SEED, portfolio=pf)
+    else:
+        returns, rvol = synthetic_history()
+        pool = bootstrap_pool(returns)
+        spec = SimSpec(n_paths=n, n_steps=t, s0=S0, var0=rvol ** 2 / 252, seed=SEED, hist_bins=2048)
+    return spec, pool
+
+
+def api_call(workload, world, group):
+    """The same job through the public API with HOST inputs (what a user of the reference calls)."""
+    import numpy as np
+    import montecarlo_b200 as mc
+    w = WORKLOADS[workload]
+    n, t = w["paths"] * world, w["steps"]
+    if workload in ("c2", "c4"):
+        return mc.simulate_gbm(n, t, S0, MU, SIGMA, dt=DT, seed=SEED, hist_bins=2048, group=group)
+    if workload == "c5":
+        return mc.simulate_gbm(n, t, S0, MU, SIGMA, dt=DT, seed=SEED, hist_bins=2048, return_paths="device", group=group)
+    if workload == "c3":
+        d = 16
+        corr = np.full((d, d), 0.3) + 0.7 * np.eye(d)
+        return mc.simulate_portfolio(n, t, np.full(d, S0), MU, 0.15 + 0.01 * np.arange(d), np.full(d, 1 / d), corr,
+                                     dt=DT, seed=SEED, group=group)
+    import pandas as pd
+    returns, rvol = synthetic_history()
+    df = pd.DataFrame({"log_ret": returns, "rvol_20": rvol})
+    return mc.garch_monte_carlo(df, n, t, S0, seed=SEED, dtype="float32", return_paths=False, hist_bins=2048,
+                                group=group)
+
+
+def io_bytes(workload, spec, pool):
+    """Bytes copied per step: H2D = parameter struct + select plans (+ bootstrap pool);
+    D2H = result block + histogram (+ fan chart)."""
+    import ctypes
+    from montecarlo_b200 import _lib
+    plan_bytes = 592                      # sizeof(mc::SelectPlan)
+    h2d = ctypes.sizeof(_lib.McParams) + plan_bytes * (2 if spec.fan_chart else 1)
+    if pool is not None:
+        h2d += pool.size * 4
+    if spec.portfolio is not None:
+        d = len(spec.portfolio.s0)
+        h2d += 4 * (d * (d + 1) // 2 + 2 * d)
+    d2h = 496 + 8 * spec.hist_bins + (8 * len(spec.path_pcts) * (spec.n_steps + 1) if spec.fan_chart else 0)
+    return h2d, d2h
+
+
+def run_workload(workload, steps, warmup, world, rank, group, device, sample_clocks=True):
+    import torch
+    import torch.distributed as dist
+    from montecarlo_b200.engine import get_engine
+    eng = get_engine(device)
+    spec, pool = make_spec(workload, world)
+    pool_dev = eng.to_device(pool, torch.float32) if pool is not None else None
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=eng.device)       # > 126 MB L2
+    n_local = WORKLOADS[workload]["paths"]
+    t = spec.n_steps
+
+    def barrier():
+        torch.cuda.synchronize(eng.device)
+        if world > 1:
+            dist.barrier(group)
+            torch.cuda.synchronize(eng.device)
+
+    def one_step():
+        out = eng.simulate(spec, pool=pool_dev, group=group)
+        return out
+
+    for _ in range(warmup):
+        one_step()
+        api_call(workload, world, group)
+    sampler = ClockSampler(device) if (rank == 0 and sample_clocks) else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.3)
+    barrier()
+    t0 = time.perf_counter()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    sim_ms, launches, last = [], 0, None
+    for a, b in ev:
+        flush.zero_()                     # L2 flush between timed iterations (untimed)
+        torch.cuda.synchronize(eng.device)
+        a.record()
+        last = one_step()
+        b.record()
+        sim_ms.append(last.sim_ms)
+        launches += last.launches
+    barrier()
+    t1 = time.perf_counter()
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    # end to end: public API, host inputs, wall clock around the call (it synchronises)
+    barrier()
+    e2e_s = 0.0
+    for _ in range(steps):
+        flush.zero_()
+        torch.cuda.synchronize(eng.device)
+        if world > 1:
+            dist.barrier(group)
+        ta = time.perf_counter()
+        api_call(workload, world, group)
+        e2e_s += time.perf_counter() - ta
+    clocks = sampler.stop(t0, t1) if sampler else None
+    tm = torch.tensor([dev_ms, e2e_s * 1e3, sum(sim_ms)], dtype=torch.float64, device=eng.device)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX, group=group)
+    dev_ms, e2e_ms, sim_total = [float(v) for v in tm.tolist()]
+    total_steps = n_local * world * t * steps
+    h2d, d2h = io_bytes(workload, spec, pool)
+    return dict(value=total_steps / (dev_ms * 1e-3), ms_per_step=dev_ms / steps,
+                e2e=dict(value=total_steps / (e2e_ms * 1e-3), unit="path-steps/s", h2d_bytes_per_step=h2d,
+                         d2h_bytes_per_step=d2h, ms_per_step=e2e_ms / steps),
+                sim_ms=sim_total / steps, gpu_launches=launches, clocks=clocks, n_local=n_local, n_steps=t,
+                summary={k: float(v) for k, v in last.summary().items() if not isinstance(v, dict)},
+                p5=last.pct.get("p5"))
+
+
+def roofline_for(workload, r, n_sm, clocks, peaks, peaks_kind):
+    n, t, sim_s = r["n_local"], r["n_steps"], r["sim_ms"] * 1e-3
+    if workload == "c5":
+        bytes_ = 4.0 * n * (t + 1)            # 4 B written per stored price
+        ach = bytes_ / sim_s / 1e9
+        peak = float(peaks["hbm_gbs"])
+        return {"bound": "hbm", "kernel": "sim_kernel<float,NORMAL,CONST,STORE>", "achieved": ach, "peak": peak,
+                "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": f"{peaks_kind} copy bandwidth",
+                "algorithmic_bytes_per_launch": bytes_}
+    mhz_max = float(peaks.get("sm_max_mhz", 1965.0))
+    mhz = (clocks or {}).get("sm_mhz") or mhz_max
+    per_clk = STEPS_PER_SM_CLK[workload]
+    ach = n * t / sim_s
+    peak = per_clk * n_sm * mhz * 1e6
+    lane_ops = {"c2": 16, "c4": 16, "ref": 17, "c3": 388}[workload]
+    return {"bound": "fp32-alu+mufu issue (not hbm, not tensor)", "kernel": "sim_kernel (fused RNG + step + moments)",
+            "achieved": ach / 1e9, "peak": peak / 1e9, "unit": "Gpath-steps/s", "frac": ach / peak,
+            "traffic": None, "peak_source": f"SURVEY 8d: {per_clk} path-steps/SM-clk x {n_sm} SMs x {mhz:.0f} MHz "
+                                            "(median SM clock sampled during the timed region)",
+            "frac_at_max_clock": ach / (per_clk * n_sm * mhz_max * 1e6),
+            "fp32_lane_tflops": ach * lane_ops * 1e-12, "lane_ops_per_path_step": lane_ops}
+
+
+# --------------------------------------------------------------------------- CPU arms
+CPU_KIND = {"c2": "gbm", "c4": "gbm", "c5": "gbm", "c3": "gbm", "ref": "garch"}
+
+
+def cpu_baseline_leg(workload, target_seconds=8.0):
+    """Oracle port (NumPy, one core like the reference's own loop) on a bounded sample."""
+    from oracle import cpu_baseline as cb
+    kind = CPU_KIND[workload]
+    t = min(WORKLOADS[workload]["steps"], 252)
+    n = 200_000
+    sec, rate, cores = cb.time_cpu(kind, n, t, processes=1)
+    if sec < target_seconds / 4:                 # grow the sample towards ~target_seconds
+        n = int(min(2_000_000, n * target_seconds / max(sec, 1e-3) / 2))
+        sec, rate, cores = cb.time_cpu(kind, n, t, processes=1)
+    return {"value": rate, "unit": "path-steps/s", "cores": cores, "kind": "port",
+            "sample": f"oracle NumPy port ({kind} loop of app.py:618-633 + terminal statistics), "
+                      f"{n} paths x {t} steps, {sec:.2f} s, single process"}
+
+
+def reference_arm(args, rank):
+    """--impl reference: the reference's CPU algorithm for this path (the oracle port: the reference
+    is pure Python/NumPy and does not travel to the GPU box) on all host cores."""
+    if rank != 0:
+        return
+    from oracle import cpu_baseline as cb
+    workload = args.workload
+    kind = CPU_KIND[workload]
+    cores = cb.host_cores()
+    procs = max(1, min(cores, 64))
+    t = min(WORKLOADS[workload]["steps"], 252)
+    per_proc = 50_000
+    for _ in range(args.warmup):
+        cb.time_cpu(kind, 2_000 * procs, 8, processes=procs)
+    total_s, total_steps = 0.0, 0
+    for _ in range(args.steps):
+        sec, rate, _ = cb.time_cpu(kind, per_proc * procs, t, processes=procs)
+        total_s += sec
+        total_steps += per_proc * procs * t
+    value = total_steps / total_s
+    line = {"impl": "reference", "metric": "path-steps/sec", "value": value, "unit": "path-steps/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"{workload}: {WORKLOADS[workload]['desc']}",
+                       "sample": f"{per_proc * procs} paths x {t} steps per step"},
+            "cpu_baseline": {"value": value, "unit": "path-steps/s", "cores": procs, "kind": "port",
+                             "sample": f"oracle NumPy port ({kind}), {per_proc} paths x {t} steps in each of "
+                                       f"{procs} processes per step"},
+            "e2e": {"value": value, "unit": "path-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the other BASELINE configs / CPU leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: montecarlo_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    group = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        group = dist.group.WORLD
+    warmup = max(3, args.warmup)
+    r = run_workload(args.workload, args.steps, warmup, world, rank, group, local_rank)
+    peaks, peaks_kind = measured_peaks()
+    n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
+    line = {"metric": "path-steps/sec", "value": r["value"], "unit": "path-steps/s", "n_gpus": world,
+            "steps": args.steps, "warmup": warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {WORKLOADS[args.workload]['desc']}",
+                       "paths_per_gpu": r["n_local"], "n_steps": r["n_steps"], "sharding": f"paths/{world} ranks",
+                       "l2": "256 MB buffer written between timed iterations", "seed": hex(SEED)},
+            "e2e": r["e2e"], "gpu_launches": r["gpu_launches"], "clocks": r["clocks"],
+            "roofline": roofline_for(args.workload, r, n_sm, r["clocks"], peaks, peaks_kind),
+            "sim_kernel_ms": r["sim_ms"], "result": r["summary"]}
+    if rank == 0 and world == 1 and not args.no_extras:
+        line["cpu_baseline"] = cpu_baseline_leg(args.workload)
+        extras = {}
+        for wl in ("c4", "c5", "c3", "ref", "c2"):
+            if wl == args.workload:
+                continue
+            try:
+                x = run_workload(wl, 3, 3, 1, 0, None, local_rank, sample_clocks=True)
+                extras[wl] = {"workload": WORKLOADS[wl]["desc"], "value": x["value"], "ms_per_step": x["ms_per_step"],
+                              "e2e": x["e2e"]["value"], "sim_kernel_ms": x["sim_ms"], "clocks": x["clocks"],
+                              "roofline": roofline_for(wl, x, n_sm, x["clocks"], peaks, peaks_kind)}
+            except Exception as exc:      # an extra must never lose the headline line
+                extras[wl] = {"error": repr(exc)[:200]}
+            torch.cuda.empty_cache()
+        line["extras"] = extras
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -512,7 +512,7 @@ int mc_histogram(mc_handle* h, const void* d_x, int32_t dtype, uint64_t n, uint3
     if (!h) return MC_ERR_INVALID;
     std::lock_guard<std::mutex> lock(h->mu);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    if (!d_x || !h_counts || bins == 0 || bins > (1u << 16) || !(lo < hi))
+    if ((!d_x && n) || !h_counts || bins == 0 || bins > (1u << 16) || !(lo < hi))
         return fail(h, MC_ERR_INVALID, "bad mc_histogram arguments (explicit lo < hi required)");
     MC_CUDA(h, cudaSetDevice(h->device));
     MC_CUDA(h, h->edges.reserve((size_t)bins + 1));

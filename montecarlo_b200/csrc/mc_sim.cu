@@ -106,7 +106,7 @@ __device__ __forceinline__ void account(BlockPartial& acc, unsigned int* s_hist,
     acc.vmin = fmin(acc.vmin, (double)value);
     acc.vmax = fmax(acc.vmax, (double)value);
     acc.n += 1;
-    acc.n_above += (value > s0) ? 1ull : 0ull;       // app.py:654
+    acc.n_above += ((double)value > center) ? 1ull : 0ull;       // app.py:654 (compared in fp64)
     const auto key = key_of(value);
     atomicAdd(&s_hist[(unsigned int)(key >> (KeyT<Real>::bits - DIGIT0_BITS))], 1u);
 }

@@ -1,0 +1,195 @@
+"""GPU parity, part 3: the drop-in function itself, rank-sharding invariance (ranks emulated
+on one GPU through the staged C entry points), and size-independent properties at
+BASELINE.json's full sizes."""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import mc_numpy as port
+from oracle import philox
+from montecarlo_b200 import SimSpec, garch_monte_carlo, simulate_gbm, simulate_portfolio
+from montecarlo_b200 import _lib as L
+from montecarlo_b200.spec import make_params, shard_range
+
+pytestmark = pytest.mark.gpu
+
+
+def _frame(n_rows=1250, seed=0):
+    import pandas as pd
+    rs = np.random.RandomState(seed)
+    return pd.DataFrame({"log_ret": rs.normal(0.0, 0.02, n_rows), "rvol_20": np.full(n_rows, 0.02 * np.sqrt(252))})
+
+
+def test_drop_in_contract():
+    """Every expression the dashboard evaluates on mc_results (app.py:944-1000)."""
+    df, msgs = _frame(), []
+    res = garch_monte_carlo(df, 1000, 20, 100.0, msgs.append, seed=1)
+    assert msgs == ["Running Monte Carlo simulation..."]                       # app.py:597-598
+    assert set(res) >= {"paths", "final_prices", "percentiles", "path_percentiles", "expected_return",
+                        "expected_vol", "prob_profit", "var_95", "cvar_95"}     # app.py:647-657
+    assert isinstance(res["paths"], np.ndarray) and res["paths"].dtype == np.float64
+    assert res["paths"].shape == (21, 1000) and res["final_prices"].shape == (1000,)
+    assert np.shares_memory(res["final_prices"], res["paths"])                  # a view, like app.py:636
+    assert np.all(res["paths"][0] == 100.0)
+    assert list(res["percentiles"]) == [f"p{p}" for p in (1, 5, 10, 25, 50, 75, 90, 95, 99)]
+    for k in ("p5", "p25", "p50", "p75", "p95"):
+        assert len(res["path_percentiles"][k]) == 21                            # app.py:977
+    for k in ("expected_return", "prob_profit", "var_95", "cvar_95"):
+        f"{res[k]:+.2f}"                                                        # app.py:950-953
+    # against NumPy on the returned arrays: the reference's own reductions
+    exp = port.summarize(res["paths"], 100.0)
+    for k in ("expected_return", "expected_vol", "prob_profit", "var_95", "cvar_95"):
+        assert abs(res[k] - exp[k]) < 1e-9 * max(1.0, abs(exp[k])), k
+    for k, v in exp["percentiles"].items():
+        assert res["percentiles"][k] == v
+    for k, v in exp["path_percentiles"].items():
+        assert np.array_equal(res["path_percentiles"][k], v)
+    # reproducible under a seed, different without
+    again = garch_monte_carlo(df, 1000, 20, 100.0, seed=1)
+    assert np.array_equal(again["paths"], res["paths"])
+    assert not np.array_equal(garch_monte_carlo(df, 1000, 20, 100.0)["paths"], res["paths"])
+    assert garch_monte_carlo(_frame(99), 1000, 20, 100.0) is None               # app.py:594-595
+
+
+def test_statistical_parity_with_reference_c1(golden_dir):
+    """BASELINE config 1 (10k x 252): device RNG vs the reference run under np.random.seed(42);
+    agreement within 4 standard errors of the difference of two independent samples."""
+    import os
+    g = np.load(os.path.join(golden_dir, "ref_c1_seed42.npz"))
+    import pandas as pd
+    df = pd.DataFrame({"log_ret": g["returns"], "rvol_20": float(g["rvol_last"])})
+    n, s0 = int(g["n_sims"]), float(g["s0"])
+    res = garch_monte_carlo(df, n, int(g["n_days"]), s0, seed=7, dtype="float32", return_paths="numpy")
+    vol = float(g["expected_vol"])                       # std of terminal / s0 * 100
+    se_mean = vol / math.sqrt(n) * math.sqrt(2)
+    assert abs(res["expected_return"] - float(g["expected_return"])) < 4 * se_mean
+    assert abs(res["expected_vol"] / vol - 1) < 4 * math.sqrt(2) * 1.5 / math.sqrt(n)      # heavy-ish tails
+    assert abs(res["prob_profit"] - float(g["prob_profit"])) < 4 * 100 * math.sqrt(0.5 / n)
+    ref_p = g["percentiles"]
+    final = np.sort(res["final_prices"])
+    for i, p in enumerate(port.REF_TERMINAL_PCTS):
+        # SE of a quantile via the empirical density around it
+        q = p / 100
+        k = int(q * (n - 1))
+        w = max(50, int(0.01 * n))
+        dens = (2 * w / n) / (final[min(n - 1, k + w)] - final[max(0, k - w)])
+        se = math.sqrt(q * (1 - q) / n) / dens * math.sqrt(2)
+        assert abs(res["percentiles"][f"p{p}"] - ref_p[i]) < 4 * se, p
+    fan_ref = g["path_percentiles"]
+    for i, p in enumerate(port.REF_PATH_PCTS):
+        rel = np.abs(res["path_percentiles"][f"p{p}"][1:] / fan_ref[i][1:] - 1)
+        assert rel.max() < 0.02
+
+
+def _staged_emulated_ranks(spec, pool, world):
+    """Run `world` rank-shards on ONE GPU, one handle per rank, gathering stage buffers by hand
+    (kernels are plain sequential launches; nothing waits on another rank)."""
+    from montecarlo_b200.engine import Engine, _CudaStageBackend
+    engines = [Engine(0) for _ in range(world)]
+    dt = torch.float64 if spec.dtype == "float64" else torch.float32
+    backs, outs = [], []
+    for r, e in enumerate(engines):
+        off, cnt = shard_range(spec.n_paths, r, world)
+        pool_t = e.to_device(pool, dt) if pool is not None else None
+        if pool_t is not None:
+            spec.pool_len = pool_t.numel()
+        params = make_params(spec, path_offset=off, n_local=cnt)
+        term = torch.empty(cnt, dtype=dt, device=e.device)
+        backs.append(_CudaStageBackend(e, params, None, pool_t, None, None, term, world))
+        outs.append(term)
+    for b in backs:
+        b.begin()
+    done = False
+    while not done:
+        words = backs[0].stage_words()
+        assert all(b.stage_words() == words for b in backs)
+        gathered = torch.cat([b.stage_view(words) for b in backs])
+        done = all([b.next(gathered, world) for b in backs])
+    results = []
+    for e in engines:
+        res = L.McResult()
+        hist = np.zeros(spec.hist_bins, dtype=np.uint64)
+        e.check(e.lib.mc_fetch_result(e.handle, C.byref(res), C.c_void_p(hist.ctypes.data), None, e.stream_ptr()))
+        results.append((res, hist))
+    for e in engines:
+        e.close()
+    return results, torch.cat(outs)
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+@pytest.mark.parametrize("mode", ["bootstrap", "gbm"])
+def test_shard_invariance_emulated_ranks(engine, world, mode):
+    n, t = 50_001, 24
+    pool = port.bootstrap_pool(np.random.RandomState(4).normal(0, 0.02, 1250)) if mode == "bootstrap" else None
+    def mk():
+        if mode == "bootstrap":
+            return SimSpec(n_paths=n, n_steps=t, s0=100.0, var0=4e-4, seed=11, hist_bins=128, hist_range=(50.0, 200.0))
+        return SimSpec.gbm(n, t, 100.0, 0.05, 0.2, seed=11, hist_bins=128, hist_range=(50.0, 200.0))
+    single = engine.simulate(mk(), pool=pool)
+    results, terminal = _staged_emulated_ranks(mk(), pool, world)
+    assert torch.equal(terminal, single.terminal)                 # per-path values independent of the sharding
+    for res, hist in results:                                    # every rank ends with the same merged result
+        assert res.n == n and res.n_above == single.n_above
+        assert [res.pct[i] for i in range(9)] == list(single.pct.values())
+        assert res.tail_count == single.tail_count
+        assert abs(res.tail_sum - single.tail_sum) <= 1e-12 * abs(single.tail_sum)
+        assert abs(res.mean - single.mean) <= 1e-13 * abs(single.mean)
+        assert abs(res.std - single.std) <= 1e-11 * single.std
+        assert res.min == single.min and res.max == single.max
+        assert np.array_equal(hist.astype(np.int64), single.hist)
+
+
+def test_full_size_c2_properties():
+    """BASELINE config 2: 10M x 252 fp32 GBM.  Size-independent checks: exact percentiles of the
+    returned terminals, histogram mass, closed-form lognormal answers within 4 SE."""
+    n, t, s0, mu, sigma, dt = 10_000_000, 252, 100.0, 0.05, 0.2, 1 / 252
+    res = simulate_gbm(n, t, s0, mu, sigma, dt=dt, seed=0x123456789ABCDEF0, hist_bins=2048)
+    term = res["final_prices"].cpu().numpy().astype(np.float64)
+    assert term.shape == (n,)
+    for p, v in zip(port.REF_TERMINAL_PCTS, np.percentile(term, port.REF_TERMINAL_PCTS)):
+        assert res["percentiles"][f"p{p}"] == v
+    h = res["histogram"]
+    assert np.array_equal(h["counts"], np.histogram(term, bins=2048, range=h["range"])[0])
+    cf = port.gbm_closed_form(s0, mu, sigma, t * dt, q=np.array(port.REF_TERMINAL_PCTS) / 100)
+    assert abs(term.mean() - cf["mean"]) < 4 * cf["std"] / math.sqrt(n)
+    assert abs(term.std() / cf["std"] - 1) < 4 * 2.5 / math.sqrt(n)
+    from scipy.stats import norm
+    for p, qv in zip(port.REF_TERMINAL_PCTS, cf["quantiles"]):
+        q = p / 100
+        dens = norm.pdf(norm.ppf(q)) / (qv * sigma * math.sqrt(t * dt))
+        assert abs(res["percentiles"][f"p{p}"] - qv) < 4 * math.sqrt(q * (1 - q) / n) / dens, p
+    exp = port.terminal_statistics(term, s0)
+    for k in ("expected_return", "expected_vol", "prob_profit", "var_95", "cvar_95"):
+        assert abs(res[k] - exp[k]) < 1e-9 * max(1.0, abs(exp[k])), k
+
+
+def test_full_size_c3_portfolio_properties():
+    """BASELINE config 3: 16 correlated assets, 1M x 252: portfolio mean and VaR/CVaR consistency."""
+    d, n, t, dt = 16, 1_000_000, 252, 1 / 252
+    corr = np.full((d, d), 0.3) + 0.7 * np.eye(d)
+    sigma = 0.15 + 0.01 * np.arange(d)
+    res = simulate_portfolio(n, t, np.full(d, 100.0), 0.05, sigma, np.full(d, 1 / d), corr, dt=dt, seed=3)
+    v = res["final_prices"].cpu().numpy().astype(np.float64)
+    assert abs(v.mean() - 100.0 * math.exp(0.05)) < 4 * v.std() / math.sqrt(n)
+    # variance of the log of a single-asset-equivalent is not closed form; check VaR/CVaR on own values
+    exp = port.terminal_statistics(v, 100.0)
+    for k in ("var_95", "cvar_95", "prob_profit", "expected_vol"):
+        assert abs(res[k] - exp[k]) < 1e-9 * max(1.0, abs(exp[k])), k
+    assert res["cvar_95"] > res["var_95"] > 0
+
+
+def test_full_size_c5_materialised_fan_chart():
+    """BASELINE config 5 shape at reduced N (the full 17 GB case runs in bench.py --workload c5):
+    1M x 1024 fp32 paths stored time-major; fan chart exact on sampled rows."""
+    n, t = 1_000_000, 1024
+    res = simulate_gbm(n, t, 100.0, 0.05, 0.2, seed=9, return_paths="device")
+    paths = res["paths"]
+    assert paths.shape == (t + 1, n) and paths.dtype == torch.float32
+    for row in (0, 1, 511, 1024):
+        ref = np.percentile(paths[row].cpu().numpy().astype(np.float64), port.REF_PATH_PCTS)
+        got = [res["path_percentiles"][f"p{p}"][row] for p in port.REF_PATH_PCTS]
+        assert list(ref) == got
+    assert torch.equal(paths[-1], res["final_prices"])

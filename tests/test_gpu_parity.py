@@ -1,0 +1,147 @@
+"""GPU parity, part 2: the simulation path against the oracle and the reference's golden
+fixtures, through the drop-in API and the C ABI.  Tolerances are BASELINE.json's:
+1e-5 relative (fp32) / 1e-12 (fp64) per path on identical shocks; exact counts."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import mc_numpy as port
+from oracle import philox
+from montecarlo_b200 import SimSpec, PortfolioSpec
+
+pytestmark = pytest.mark.gpu
+RTOL = {"float32": 1e-5, "float64": 1e-12}
+PCTS = port.REF_TERMINAL_PCTS
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name))
+
+
+def _rel(a, b):
+    return np.abs(np.asarray(a, dtype=np.float64) - b).max() / np.abs(b).max() if np.size(b) else 0.0
+
+
+def _check_reductions(out, values64, s0, spec):
+    """Everything the device reduced, against NumPy on the device's own terminal values."""
+    exp = port.terminal_statistics(values64, s0, spec.pcts)
+    summ = out.summary()
+    for p in spec.pcts:
+        assert out.pct[f"p{p:g}"] == exp["percentiles"][f"p{p}"], p      # exact
+    assert out.n == values64.size and out.n_above == int((values64 > s0).sum())
+    assert abs(summ["expected_return"] - exp["expected_return"]) <= 1e-9 * max(1, abs(exp["expected_return"]))
+    assert abs(summ["expected_vol"] - exp["expected_vol"]) <= 1e-9 * exp["expected_vol"] + 1e-12
+    assert summ["prob_profit"] == exp["prob_profit"]
+    assert summ["var_95"] == exp["var_95"]
+    assert abs(summ["cvar_95"] - exp["cvar_95"]) <= 1e-10 * max(1, abs(exp["cvar_95"]))
+    assert out.min == values64.min() and out.max == values64.max()
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+@pytest.mark.parametrize("name", ["ref_small_bootstrap.npz", "ref_ragged_heavytail.npz",
+                                  "ref_normal_through_garch.npz"])
+def test_injected_shocks_match_reference_golden(engine, golden_dir, dtype, name):
+    g = _load(golden_dir, name)
+    pool = port.bootstrap_pool(g["returns"])
+    shocks = g["shocks"] if "shocks" in g.files else pool[g["indices"]]
+    n, t, s0 = int(g["n_sims"]), int(g["n_days"]), float(g["s0"])
+    spec = SimSpec(n_paths=n, n_steps=t, s0=s0, shock="injected", var_model="garch",
+                   var0=port.initial_variance(float(g["rvol_last"])), dtype=dtype, store_paths=True, fan_chart=True)
+    out = engine.simulate(spec, shocks=shocks)
+    paths = out.paths.cpu().numpy().astype(np.float64)
+    assert paths.shape == g["paths"].shape
+    assert np.abs(paths / g["paths"] - 1).max() < RTOL[dtype]
+    assert np.array_equal(paths[-1], out.terminal.cpu().numpy().astype(np.float64))
+    _check_reductions(out, paths[-1], s0, spec)
+    fan = np.stack([out.fan[f"p{p}"] for p in port.REF_PATH_PCTS])
+    assert np.array_equal(fan, np.percentile(paths, port.REF_PATH_PCTS, axis=1))      # exact on own paths
+    assert np.abs(fan / g["path_percentiles"] - 1).max() < RTOL[dtype]                # and close to the reference
+    got = np.array([out.pct[f"p{p}"] for p in PCTS])
+    assert np.abs(got / g["percentiles"] - 1).max() < RTOL[dtype]
+    summ = out.summary()
+    tol = 2e-4 if dtype == "float32" else 1e-9
+    for k in ("expected_return", "expected_vol", "var_95", "cvar_95"):
+        assert abs(summ[k] - float(g[k])) < tol * max(1.0, abs(float(g[k]))), k
+    if dtype == "float64":
+        assert summ["prob_profit"] == float(g["prob_profit"])
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+@pytest.mark.parametrize("n,t", [(1000, 20), (5000, 60), (10_000, 252), (777, 1), (3, 5)])
+def test_device_bootstrap_run_matches_port(engine, dtype, n, t):
+    """Mode R end to end: the device's own Philox draws, replayed through the oracle port."""
+    seed, s0 = 2024 + n, 100.0
+    rs = np.random.RandomState(t)
+    returns = rs.standard_t(4, 1250) * 0.014
+    pool = port.bootstrap_pool(returns)
+    spec = SimSpec(n_paths=n, n_steps=t, s0=s0, var0=port.initial_variance(0.02 * np.sqrt(252)), dtype=dtype,
+                   seed=seed, store_paths=True, fan_chart=True, hist_bins=64)
+    out = engine.simulate(spec, pool=pool)
+    idx = philox.bootstrap_indices(seed, 0, n, t, len(pool))
+    pool_dev = pool.astype(dtype).astype(np.float64)            # the device pool is stored in `dtype`
+    ref = port.step_paths(pool_dev[idx], s0, spec.var0)
+    paths = out.paths.cpu().numpy().astype(np.float64)
+    assert np.abs(paths / ref - 1).max() < RTOL[dtype]
+    _check_reductions(out, paths[-1], s0, spec)
+    fan = np.stack([out.fan[f"p{p}"] for p in port.REF_PATH_PCTS])
+    assert np.array_equal(fan, np.percentile(paths, port.REF_PATH_PCTS, axis=1))
+    counts, _ = np.histogram(paths[-1], bins=64, range=(paths[-1].min(), paths[-1].max()))
+    assert np.array_equal(out.hist, counts) and out.hist.sum() == n
+    # no-store run gives the same terminals bit-for-bit
+    spec2 = SimSpec(n_paths=n, n_steps=t, s0=s0, var0=spec.var0, dtype=dtype, seed=seed)
+    out2 = engine.simulate(spec2, pool=pool)
+    assert torch.equal(out2.terminal, out.terminal)
+    assert out2.pct == out.pct and out2.paths is None and out2.fan is None
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+def test_gbm_injected_and_device_normals(engine, dtype):
+    n, t, s0, mu, sigma, dt, seed = 4099, 37, 100.0, 0.05, 0.2, 1 / 252, 99
+    z = philox.normal_shocks(seed, 0, n, t, dtype=np.dtype(dtype))
+    ref = port.gbm_paths(z.astype(dtype).astype(np.float64), s0, mu, sigma, dt)
+    # (a) identical pre-generated normal matrix
+    spec = SimSpec.gbm(n, t, s0, mu, sigma, dt, dtype=dtype, shock="injected", store_paths=True, fan_chart=True)
+    out = engine.simulate(spec, shocks=z)
+    paths = out.paths.cpu().numpy().astype(np.float64)
+    assert np.abs(paths / ref - 1).max() < RTOL[dtype]
+    _check_reductions(out, paths[-1], s0, spec)
+    # on-device normals: stored and fused-sum kernels agree with the bit model
+    tol = 2e-5 if dtype == "float32" else 1e-11
+    ref2 = port.gbm_paths(z, s0, mu, sigma, dt)
+    for store in (True, False):
+        sp = SimSpec.gbm(n, t, s0, mu, sigma, dt, dtype=dtype, seed=seed, store_paths=store, fan_chart=store)
+        o = engine.simulate(sp)
+        term = o.terminal.cpu().numpy().astype(np.float64)
+        assert np.abs(term / ref2[-1] - 1).max() < tol
+        _check_reductions(o, term, s0, sp)
+        if store:
+            assert np.abs(o.paths.cpu().numpy() / ref2 - 1).max() < tol
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+@pytest.mark.parametrize("d", [2, 5, 16, 32])
+def test_portfolio_matches_port(engine, dtype, d):
+    n, t, dt, seed = 2050, 13, 1 / 252, 5
+    rs = np.random.RandomState(7)
+    a = rs.normal(size=(d, d))
+    cov = a @ a.T
+    corr = cov / np.sqrt(np.outer(np.diag(cov), np.diag(cov)))
+    sigma = 0.15 + 0.01 * np.arange(d)
+    s0 = 50.0 + 10 * np.arange(d)
+    w = rs.dirichlet(np.ones(d))
+    pf = PortfolioSpec(s0=s0, mu=0.05, sigma=sigma, weights=w, corr=corr, dt=dt)
+    z = philox.normal_shocks(seed, 0, n, t, dtype=np.dtype(dtype), n_assets=d)
+    v_ref, _ = port.portfolio_terminal(z, s0, 0.05, sigma, np.linalg.cholesky(corr), w, dt)
+    v0 = float(w @ s0)
+    tol = 3e-5 if dtype == "float32" else 1e-11
+    for shock, shocks in (("normal", None), ("injected", z.reshape(t * d, n))):
+        spec = SimSpec(n_paths=n, n_steps=t, s0=v0, shock=shock, var_model="const", dtype=dtype, seed=seed,
+                       portfolio=pf, store_paths=True, fan_chart=True)
+        out = engine.simulate(spec, shocks=shocks)
+        v = out.terminal.cpu().numpy().astype(np.float64)
+        assert np.abs(v / v_ref - 1).max() < tol
+        _check_reductions(out, v, v0, spec)
+        paths = out.paths.cpu().numpy().astype(np.float64)
+        assert np.allclose(paths[0], v0, rtol=1e-6) and np.array_equal(paths[-1], v)
