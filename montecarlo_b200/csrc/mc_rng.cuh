@@ -120,12 +120,54 @@ __device__ __forceinline__ void box_muller(uint32_t ua, uint32_t ub, double& z0,
     z1 = r * s;
 }
 
-// four normals from one Philox call
-template <typename Real>
-__device__ __forceinline__ void normals4(const u32x4& w, Real (&z)[4]) {
+// ---- fp32: SIX normals from one 128-bit Philox call -------------------------------------
+// The Philox multiply (IMAD.WIDE) runs at a quarter of the FP32 rate on sm_100a (measured:
+// tools/microbench.cu), so the generator -- not the transform -- bounds the fused kernels.
+// A float only holds 23 mantissa bits, so 4 x 32 bits are cut into three Box-Muller pairs
+// instead of two:   radius uniform k = word_k[22:0]            (23 bits, k = 0,1,2)
+//                   angle A = word_3[31:9]                      (23 bits)
+//                   angle B = word_0[31:24] : word_1[31:24]     (16 bits)
+//                   angle C = word_2[31:24] : word_3[7:0]       (16 bits)
+// All fields are disjoint, so the six uniforms are independent.  (The low mantissa bits of the
+// 16-bit angles repeat the field's own top byte: 65,536 distinct, near-equispaced angles.)
+__device__ __forceinline__ float radius_uniform(uint32_t w) {           // (0, 1]
+    return 2.0f - __uint_as_float((w & 0x007FFFFFu) | 0x3F800000u);
+}
+__device__ __forceinline__ float rho_of(uint32_t w) { return fast_sqrt(-fast_lg2(radius_uniform(w))); }
+__device__ __forceinline__ float theta_of(uint32_t field_at_top) {       // [-pi, pi)
+    return fmaf(mantissa_float(field_at_top), TWO_PI_F, -THREE_PI_F);
+}
+__device__ __forceinline__ uint32_t angle_b_bits(const u32x4& w) { return __byte_perm(w.x, w.y, 0x3733); }
+__device__ __forceinline__ uint32_t angle_c_bits(const u32x4& w) { return __byte_perm(w.z, w.w, 0x3433); }
+
+__device__ __forceinline__ void normals6(const u32x4& w, float (&z)[6]) {
+    const float ra = BM_RADIUS_SCALE_F * rho_of(w.x), rb = BM_RADIUS_SCALE_F * rho_of(w.y),
+                rc = BM_RADIUS_SCALE_F * rho_of(w.z);
+    const float ta = theta_of(w.w), tb = theta_of(angle_b_bits(w)), tc = theta_of(angle_c_bits(w));
+    z[0] = ra * fast_cos(ta); z[1] = ra * fast_sin(ta);
+    z[2] = rb * fast_cos(tb); z[3] = rb * fast_sin(tb);
+    z[4] = rc * fast_cos(tc); z[5] = rc * fast_sin(tc);
+}
+// sum of the six normals / sqrt(2 ln 2), one FFMA per normal (constant folded in by the caller)
+__device__ __forceinline__ float normals6_sum(const u32x4& w, float s) {
+    const float ra = rho_of(w.x), rb = rho_of(w.y), rc = rho_of(w.z);
+    const float ta = theta_of(w.w), tb = theta_of(angle_b_bits(w)), tc = theta_of(angle_c_bits(w));
+    s = fmaf(ra, fast_cos(ta), s); s = fmaf(ra, fast_sin(ta), s);
+    s = fmaf(rb, fast_cos(tb), s); s = fmaf(rb, fast_sin(tb), s);
+    s = fmaf(rc, fast_cos(tc), s); s = fmaf(rc, fast_sin(tc), s);
+    return s;
+}
+
+// ---- fp64: four normals per call from full 32-bit uniforms ------------------------------
+__device__ __forceinline__ void normals4(const u32x4& w, double (&z)[6]) {
     box_muller(w.x, w.y, z[0], z[1]);
     box_muller(w.z, w.w, z[2], z[3]);
+    z[4] = 0.0; z[5] = 0.0;
 }
+
+template <typename Real> struct NormalsPerCall { static constexpr int value = sizeof(Real) == 4 ? 6 : 4; };
+__device__ __forceinline__ void draw_normals(const u32x4& w, float (&z)[6]) { normals6(w, z); }
+__device__ __forceinline__ void draw_normals(const u32x4& w, double (&z)[6]) { normals4(w, z); }
 
 // bootstrap index: floor(u * H / 2^32), exact, unbiased to 2^-32 * H
 __device__ __forceinline__ uint32_t bootstrap_index(uint32_t u, uint32_t pool_len) {

@@ -123,18 +123,27 @@ __device__ __forceinline__ void finish_block(BlockPartial acc, unsigned int* s_h
 }
 
 // ------------------------------------------------------------------ shock sources
+// Shocks per Philox call: 6 for fp32 normals (mc_rng.cuh: three Box-Muller pairs from 128 bits),
+// 4 for fp64 normals and for bootstrap indices (one full 32-bit word each).  Injected shocks are
+// read in groups of 4.  Step t of a path uses shock (t mod K) of call (t div K).
 template <typename Real, int SHOCK>
-__device__ __forceinline__ void draw4(const SimArgs<Real>& a, const Real* s_pool, unsigned long long i,
-                                      uint32_t c0, uint32_t c1, uint32_t call, uint32_t t, Real (&z)[4]) {
+struct ShocksPerCall {
+    static constexpr int value = (SHOCK == MC_SHOCK_NORMAL) ? NormalsPerCall<Real>::value : 4;
+};
+
+template <typename Real, int SHOCK>
+__device__ __forceinline__ void draw(const SimArgs<Real>& a, const Real* s_pool, unsigned long long i,
+                                     uint32_t c0, uint32_t c1, uint32_t call, uint32_t t, Real (&z)[6]) {
     if (SHOCK == MC_SHOCK_INJECTED) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
             z[k] = (t + k < a.n_steps) ? a.shocks[(unsigned long long)(t + k) * a.ld_shocks + i] : Real(0);
+        z[4] = Real(0); z[5] = Real(0);
         return;
     }
     const u32x4 w = philox4x32_10(c0, c1, call, 0u, a.rk);
     if (SHOCK == MC_SHOCK_NORMAL) {
-        normals4<Real>(w, z);
+        draw_normals(w, z);
     } else {
         const uint32_t u[4] = {w.x, w.y, w.z, w.w};
         if (a.pool_log2_copies >= 0) {
@@ -149,6 +158,7 @@ __device__ __forceinline__ void draw4(const SimArgs<Real>& a, const Real* s_pool
 #pragma unroll
             for (int k = 0; k < 4; ++k) z[k] = __ldg(&a.pool[bootstrap_index(u[k], a.pool_len)]);
         }
+        z[4] = Real(0); z[5] = Real(0);
     }
 }
 
@@ -170,6 +180,7 @@ __global__ void __launch_bounds__(MAXB) sim_kernel(const __grid_constant__ SimAr
     __shared__ unsigned int s_hist[DIGIT0_BINS];
     __shared__ BlockPartial s_warp[32];
     Real* s_pool = reinterpret_cast<Real*>(smem_dyn);
+    constexpr int K = ShocksPerCall<Real, SHOCK>::value;
 
     for (int i = threadIdx.x; i < DIGIT0_BINS; i += blockDim.x) s_hist[i] = 0u;
     if (SHOCK == MC_SHOCK_BOOTSTRAP && a.pool_log2_copies >= 0) {
@@ -181,7 +192,7 @@ __global__ void __launch_bounds__(MAXB) sim_kernel(const __grid_constant__ SimAr
     BlockPartial acc = empty_partial();
     const Real sig = (VAR == MC_VAR_CONST) ? sqrt_units(a.var0) : Real(0);
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    const uint32_t n_full = a.n_steps >> 2;
+    const uint32_t n_full = a.n_steps / K;
 
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n_paths;
          i += stride) {
@@ -198,37 +209,29 @@ __global__ void __launch_bounds__(MAXB) sim_kernel(const __grid_constant__ SimAr
             // constant and sigma are applied once after the loop; each normal costs one FFMA.
             float s = 0.0f;
 #pragma unroll 2
-            for (uint32_t j = 0; j < n_full; ++j) {
-                const u32x4 w = philox4x32_10(c0, c1, j, 0u, a.rk);
-                const float r0 = bm_rho(w.x), th0 = bm_theta(w.y);
-                const float r1 = bm_rho(w.z), th1 = bm_theta(w.w);
-                s = fmaf(r0, fast_cos(th0), s);
-                s = fmaf(r0, fast_sin(th0), s);
-                s = fmaf(r1, fast_cos(th1), s);
-                s = fmaf(r1, fast_sin(th1), s);
-            }
+            for (uint32_t j = 0; j < n_full; ++j) s = normals6_sum(philox4x32_10(c0, c1, j, 0u, a.rk), s);
             y = (Real)(sig * BM_RADIUS_SCALE_F * s);
-            t = n_full << 2;
+            t = n_full * K;
         } else {
 #pragma unroll 2
             for (uint32_t j = 0; j < n_full; ++j) {
-                Real z[4];
-                draw4<Real, SHOCK>(a, s_pool, i, c0, c1, j, t, z);
+                Real z[6];
+                draw<Real, SHOCK>(a, s_pool, i, c0, c1, j, t, z);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
+                for (int k = 0; k < K; ++k) {
                     step<Real, VAR>(a, z[k], sig, y, v);
                     if (STORE)
                         a.paths[(unsigned long long)(t + k + 1) * a.ld_paths + i] =
                             a.s0 * exp_units(fma_units((Real)(t + k + 1), a.drift, y));
                 }
-                t += 4;
+                t += K;
             }
         }
-        if (t < a.n_steps) {   // ragged tail: n_steps not a multiple of 4
-            Real z[4];
-            draw4<Real, SHOCK>(a, s_pool, i, c0, c1, n_full, t, z);
+        if (t < a.n_steps) {   // ragged tail: n_steps not a multiple of K
+            Real z[6];
+            draw<Real, SHOCK>(a, s_pool, i, c0, c1, n_full, t, z);
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
+            for (int k = 0; k < K - 1; ++k) {
                 if (t + k < a.n_steps) {
                     step<Real, VAR>(a, z[k], sig, y, v);
                     if (STORE)
@@ -302,14 +305,18 @@ __global__ void __launch_bounds__(SIM_BLOCK) portfolio_kernel(const __grid_const
                     z[k] = (k < (int)a.n_assets) ? a.shocks[row * a.ld_shocks + i] : Real(0);
                 }
             } else {
+                constexpr int NPC = NormalsPerCall<Real>::value;
+                constexpr int QMAX = (D + NPC - 1) / NPC;
 #pragma unroll
-                for (int q = 0; q < D / 4; ++q) {
-                    Real zq[4] = {Real(0), Real(0), Real(0), Real(0)};
+                for (int q = 0; q < QMAX; ++q) {
+                    Real zq[6] = {Real(0), Real(0), Real(0), Real(0), Real(0), Real(0)};
                     if (q < (int)a.calls_per_step) {
                         const u32x4 w = philox4x32_10(c0, c1, call + q, 0u, a.rk);
-                        normals4<Real>(w, zq);
+                        draw_normals(w, zq);
                     }
-                    z[4 * q + 0] = zq[0]; z[4 * q + 1] = zq[1]; z[4 * q + 2] = zq[2]; z[4 * q + 3] = zq[3];
+#pragma unroll
+                    for (int k = 0; k < NPC; ++k)
+                        if (NPC * q + k < D) z[NPC * q + k] = zq[k];
                 }
                 call += a.calls_per_step;
             }
@@ -334,16 +341,17 @@ __global__ void __launch_bounds__(SIM_BLOCK) portfolio_kernel(const __grid_const
 template <typename Real, int SHOCK>
 __global__ void debug_shocks_kernel(const SimArgs<Real> a, Real* out) {
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    const uint32_t n_calls = (a.n_steps + 3) >> 2;
+    constexpr int K = ShocksPerCall<Real, SHOCK>::value;
+    const uint32_t n_calls = (a.n_steps + K - 1) / K;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n_paths;
          i += stride) {
         const unsigned long long gid = a.path_offset + i;
         for (uint32_t j = 0; j < n_calls; ++j) {
-            Real z[4];
-            draw4<Real, SHOCK>(a, nullptr, i, (uint32_t)gid, (uint32_t)(gid >> 32), j, 4 * j, z);
+            Real z[6];
+            draw<Real, SHOCK>(a, nullptr, i, (uint32_t)gid, (uint32_t)(gid >> 32), j, K * j, z);
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                if (4 * j + k < a.n_steps) out[(unsigned long long)(4 * j + k) * a.n_paths + i] = z[k];
+            for (int k = 0; k < K; ++k)
+                if (K * j + k < a.n_steps) out[(unsigned long long)(K * j + k) * a.n_paths + i] = z[k];
         }
     }
 }
@@ -422,16 +430,18 @@ static cudaError_t pick_grid(Kernel kernel, int block, size_t smem, const Device
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-    unsigned long long resident = (unsigned long long)dev.sm_count * per_sm;
-    if (resident > MAX_SIM_GRID) resident = MAX_SIM_GRID;
+    const unsigned long long resident = (unsigned long long)dev.sm_count * per_sm;
     unsigned long long need = (n + block - 1) / block;
     if (need < 1) need = 1;
-    unsigned long long g = need < resident ? need : resident;
-    // even out the tail: same number of grid-stride rounds, fewest blocks that cover n
-    const unsigned long long rounds = (n + g * block - 1) / (g * block);
-    if (rounds > 0) {
-        const unsigned long long g2 = (n + rounds * block - 1) / (rounds * block);
-        if (g2 >= 1 && g2 < g) g = g2;
+    unsigned long long g = need;
+    if (need > resident) {
+        // More blocks than fit at once: let the hardware block scheduler balance the load.  Warps of a
+        // resident block do not finish together (the issue arbiter is not fair), so a persistent grid
+        // drains unevenly; ~24 waves of short blocks keep every SM full until the last few percent.
+        unsigned long long per_thread = n / ((unsigned long long)block * resident * 24ull);
+        if (per_thread < 1) per_thread = 1;
+        g = (n + block * per_thread - 1) / (block * per_thread);
+        if (g > MAX_SIM_GRID) g = MAX_SIM_GRID;
     }
     *grid = (int)g;
     return cudaSuccess;
@@ -504,7 +514,7 @@ static cudaError_t launch_portfolio_impl(const mc_params& p, const mc_portfolio&
     a.ld_shocks = p.n_paths;
     a.n_steps = p.n_steps;
     a.rk = expand_key((uint32_t)p.seed, (uint32_t)(p.seed >> 32));
-    a.calls_per_step = (uint32_t)((d + 3) / 4);
+    a.calls_per_step = (uint32_t)((d + NormalsPerCall<Real>::value - 1) / NormalsPerCall<Real>::value);
     a.n_assets = (uint32_t)d;
     a.shocks = static_cast<const Real*>(b.d_shocks);
     a.paths = static_cast<Real*>(b.d_paths);

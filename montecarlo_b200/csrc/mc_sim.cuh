@@ -13,7 +13,7 @@ struct SimBuffers {
     unsigned int* d_hist0;        // [DIGIT0_BINS], zeroed by the caller
 };
 
-constexpr int MAX_SIM_GRID = 148 * 16;
+constexpr int MAX_SIM_GRID = 1 << 16;     // per-block partials are reduced in fixed order afterwards
 
 struct DeviceInfo {
     int sm_count;

@@ -7,12 +7,14 @@ conventions (montecarlo_b200/csrc/mc_rng.cuh) -- the reference has no counter
 based generator (it bootstraps with np.random.choice, app.py:620).
 
 Counter layout:  ctr = (path_lo, path_hi, call_index, stream), key = (seed_lo, seed_hi)
-  fp32 uniform:  m = bits(0x3f800000 | (u >> 9)) in [1,2)
-  Box-Muller  :  r = sqrt(-2 ln(2 - m1)),  theta = 2*pi*m2 - 3*pi in [-pi, pi)
-                 z0 = r*cos(theta), z1 = r*sin(theta)
-  fp64 uniform:  v1 = (u+1) * 2^-32 in (0,1],  theta = 2*pi*(u2 * 2^-32) - pi
-  bootstrap   :  idx = (u * H) >> 32   (mulhi)
-One call yields 4 words -> 4 normals (steps 4j..4j+3) or 4 bootstrap indices.
+  fp32 normals:  SIX per call (three Box-Muller pairs cut from the 128 bits):
+                 radius uniform k = 2 - bits(0x3f800000 | word_k[22:0])      k = 0,1,2
+                 angle A field = word_3 (top 23 bits used), B = byte_perm(w0,w1,0x3733),
+                 C = byte_perm(w2,w3,0x3433);  m = bits(0x3f800000 | (field >> 9))
+                 r = sqrt(-2 ln(radius uniform)), theta = 2*pi*m - 3*pi in [-pi, pi)
+                 z[2p] = r*cos(theta), z[2p+1] = r*sin(theta)   -> steps 6j..6j+5
+  fp64 normals:  FOUR per call: v1 = (u+1) * 2^-32 in (0,1],  theta = 2*pi*(u2 * 2^-32) - pi
+  bootstrap   :  FOUR per call: idx = (u * H) >> 32   (mulhi)
 """
 from __future__ import annotations
 
@@ -59,19 +61,46 @@ def mantissa_float(u):
     return ((u >> np.uint32(9)) | np.uint32(0x3F800000)).view(np.float32)
 
 
-def box_muller_pair(ua, ub, dtype=np.float32):
-    """Two words -> two normals, computed in float64 from the device's uniforms."""
-    if np.dtype(dtype) == np.float32:
-        m1 = mantissa_float(ua).astype(np.float64)
-        m2 = mantissa_float(ub).astype(np.float64)
-        v1 = 2.0 - m1
-        # the device forms theta = fma(m2, 2pi_f32, -3pi_f32) in fp32; model it in fp64
-        theta = m2 * float(np.float32(2 * np.pi)) - float(np.float32(3 * np.pi))
-    else:
-        v1 = (np.asarray(ua, dtype=np.float64) + 1.0) * 2.0 ** -32
-        theta = 2.0 * np.pi * (np.asarray(ub, dtype=np.float64) * 2.0 ** -32) - np.pi
+def normals_per_call(dtype) -> int:
+    return 6 if np.dtype(dtype) == np.float32 else 4
+
+
+def _byte_perm(x, y, selector):
+    """CUDA __byte_perm: result byte i = byte (selector nibble i) of the 8 bytes {x0..x3, y0..y3}."""
+    x = np.asarray(x, dtype=np.uint32).astype(np.uint64)
+    y = np.asarray(y, dtype=np.uint32).astype(np.uint64)
+    both = x | (y << np.uint64(32))
+    out = np.zeros_like(x)
+    for i in range(4):
+        sel = (selector >> (4 * i)) & 0x7
+        out |= ((both >> np.uint64(8 * sel)) & np.uint64(0xFF)) << np.uint64(8 * i)
+    return out.astype(np.uint32)
+
+
+def _pair_f32(radius_word, angle_field):
+    m1 = ((np.asarray(radius_word, dtype=np.uint32) & np.uint32(0x007FFFFF)) | np.uint32(0x3F800000)).view(np.float32)
+    v1 = 2.0 - m1.astype(np.float64)
+    m2 = mantissa_float(angle_field).astype(np.float64)
+    # the device forms theta = fma(m2, 2pi_f32, -3pi_f32) in fp32; model it in fp64
+    theta = m2 * float(np.float32(2 * np.pi)) - float(np.float32(3 * np.pi))
     r = np.sqrt(-2.0 * np.log(v1))
     return r * np.cos(theta), r * np.sin(theta)
+
+
+def normals_from_words(w, dtype):
+    """All normals of one call (list of arrays): 6 for float32, 4 for float64."""
+    if np.dtype(dtype) == np.float32:
+        za = _pair_f32(w[0], w[3])
+        zb = _pair_f32(w[1], _byte_perm(w[0], w[1], 0x3733))
+        zc = _pair_f32(w[2], _byte_perm(w[2], w[3], 0x3433))
+        return [za[0], za[1], zb[0], zb[1], zc[0], zc[1]]
+    out = []
+    for ua, ub in ((w[0], w[1]), (w[2], w[3])):
+        v1 = (np.asarray(ua, dtype=np.float64) + 1.0) * 2.0 ** -32
+        theta = 2.0 * np.pi * (np.asarray(ub, dtype=np.float64) * 2.0 ** -32) - np.pi
+        r = np.sqrt(-2.0 * np.log(v1))
+        out += [r * np.cos(theta), r * np.sin(theta)]
+    return out
 
 
 def normal_shocks(seed: int, path_offset: int, n_paths: int, n_steps: int,
@@ -79,21 +108,18 @@ def normal_shocks(seed: int, path_offset: int, n_paths: int, n_steps: int,
     """Z[t, i] (single asset) or Z[t, a, i] (n_assets>1), float64 values, exactly the
     draws the device makes for global paths path_offset..path_offset+n_paths-1."""
     pid = np.arange(path_offset, path_offset + n_paths, dtype=np.uint64)
+    k = normals_per_call(dtype)
     if n_assets == 1:
-        n_calls = (n_steps + 3) // 4
-        z = np.empty((n_calls * 4, n_paths), dtype=np.float64)
+        n_calls = (n_steps + k - 1) // k
+        z = np.empty((n_calls * k, n_paths), dtype=np.float64)
         for j in range(n_calls):
-            w = path_words(seed, pid, j)
-            z[4 * j + 0], z[4 * j + 1] = box_muller_pair(w[0], w[1], dtype)
-            z[4 * j + 2], z[4 * j + 3] = box_muller_pair(w[2], w[3], dtype)
+            z[k * j:k * (j + 1)] = normals_from_words(path_words(seed, pid, j), dtype)
         return z[:n_steps]
-    q_per_step = (n_assets + 3) // 4
-    z = np.empty((n_steps, q_per_step * 4, n_paths), dtype=np.float64)
+    q_per_step = (n_assets + k - 1) // k
+    z = np.empty((n_steps, q_per_step * k, n_paths), dtype=np.float64)
     for t in range(n_steps):
         for q in range(q_per_step):
-            w = path_words(seed, pid, t * q_per_step + q)
-            z[t, 4 * q + 0], z[t, 4 * q + 1] = box_muller_pair(w[0], w[1], dtype)
-            z[t, 4 * q + 2], z[t, 4 * q + 3] = box_muller_pair(w[2], w[3], dtype)
+            z[t, k * q:k * (q + 1)] = normals_from_words(path_words(seed, pid, t * q_per_step + q), dtype)
     return z[:, :n_assets]
 
 

@@ -101,12 +101,7 @@ __global__ void k_normals(float* out, uint32_t seed, const __grid_constant__ Rou
     float s = 0.f;
     const uint32_t c0 = seed + threadIdx.x + blockIdx.x * blockDim.x;
 #pragma unroll 2
-    for (int j = 0; j < ITERS; ++j) {
-        const u32x4 w = philox4x32_10(c0, 0u, j, 0u, rk);
-        const float r0 = bm_rho(w.x), th0 = bm_theta(w.y), r1 = bm_rho(w.z), th1 = bm_theta(w.w);
-        s = fmaf(r0, fast_cos(th0), s); s = fmaf(r0, fast_sin(th0), s);
-        s = fmaf(r1, fast_cos(th1), s); s = fmaf(r1, fast_sin(th1), s);
-    }
+    for (int j = 0; j < ITERS; ++j) s = normals6_sum(philox4x32_10(c0, 0u, j, 0u, rk), s);
     if (s == 123.456f) out[0] = s;
 }
 
@@ -141,9 +136,9 @@ int main() {
         run("philox call", (double)ITERS, 256, bps, [&](int g, int b) { k_philox<<<g, b>>>(out, 7u, rk); });
     run("boxmuller pair", (double)ITERS, 256, 8, [&](int g, int b) { k_boxmuller_only<<<g, b>>>(out, 7u); });
     for (int bps : {2, 4, 6, 8})
-        run("4 normals", (double)ITERS, 256, bps, [&](int g, int b) { k_normals<<<g, b>>>(out, 7u, rk); });
-    run("4 normals b1024", (double)ITERS, 1024, 2, [&](int g, int b) { k_normals<<<g, b>>>(out, 7u, rk); });
-    run("4 normals b128", (double)ITERS, 128, 16, [&](int g, int b) { k_normals<<<g, b>>>(out, 7u, rk); });
+        run("6 normals/call", (double)ITERS, 256, bps, [&](int g, int b) { k_normals<<<g, b>>>(out, 7u, rk); });
+    run("6 normals b1024", (double)ITERS, 1024, 2, [&](int g, int b) { k_normals<<<g, b>>>(out, 7u, rk); });
+    run("6 normals b128", (double)ITERS, 128, 16, [&](int g, int b) { k_normals<<<g, b>>>(out, 7u, rk); });
     cudaError_t e = cudaDeviceSynchronize();
     printf("status: %s\n", cudaGetErrorString(e));
     return e != cudaSuccess;
