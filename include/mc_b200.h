@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define MC_ABI_VERSION 1u
+#define MC_ABI_VERSION 2u
 #define MC_MAX_PCTS 16u       /* terminal percentiles per call (reference uses 9, app.py:639) */
 #define MC_MAX_PATH_PCTS 8u   /* fan-chart percentiles (reference uses 5, app.py:644) */
 #define MC_MAX_ASSETS 32u
@@ -93,6 +93,8 @@ typedef struct mc_params {
     double pcts[MC_MAX_PCTS];
     double path_pcts[MC_MAX_PATH_PCTS];
     double tail_pct;            /* CVaR level in percent (reference: 5, app.py:656); <0 = none */
+    uint32_t n_ranks;           /* ranks sharing n_paths_global (0 or 1 = single GPU); sizes the per-rank pilot sample */
+    uint32_t reserved0;
 } mc_params;
 
 /* Portfolio description (n_assets > 1); host arrays, copied at launch. */
@@ -148,9 +150,12 @@ int mc_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf,
  * Staged variant for path-sharded multi-GPU runs.  Each stage writes
  * a packed buffer of 8-byte words; the host all-gathers it over ranks (NCCL) and
  * hands the gathered [n_ranks][words] buffer to the next stage.  With n_ranks=1
- * the "gathered" buffer is the stage buffer itself.
+ * the "gathered" buffer is the stage buffer itself.  Stages: local moments + pilot
+ * sample -> per-bracket counts/histograms (normally two narrowing passes; a pass
+ * count that depends on the data is agreed on through a device flag every rank
+ * computes identically) -> tail sums + fixed-bin histogram.
  *
- *   mc_stage_begin(...)                 simulate + local moments + first digit histogram
+ *   mc_stage_begin(...)                 simulate + local moments + pilot sample
  *   loop: words = mc_stage_words(h)     size of the buffer the next call writes/expects
  *         mc_stage_next(h, d_gathered, n_ranks, d_out, &done)
  *   mc_fetch_result(...)                D2H of the merged result, synchronises

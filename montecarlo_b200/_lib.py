@@ -8,7 +8,7 @@ import threading
 
 from .build import LIB_PATH
 
-MC_ABI_VERSION = 1
+MC_ABI_VERSION = 2
 MC_MAX_PCTS = 16
 MC_MAX_PATH_PCTS = 8
 MC_MAX_ASSETS = 32
@@ -42,6 +42,7 @@ class McParams(C.Structure):
         ("pcts", C.c_double * MC_MAX_PCTS),
         ("path_pcts", C.c_double * MC_MAX_PATH_PCTS),
         ("tail_pct", C.c_double),
+        ("n_ranks", C.c_uint32), ("reserved0", C.c_uint32),
     ]
 
 

@@ -3,10 +3,11 @@
 // The stage machine is what lets one code path serve both the single-GPU call
 // (mc_run: every "gathered" buffer is the local stage buffer) and the path-sharded
 // multi-GPU run (the host all-gathers each stage buffer over ranks between calls).
-// Stages:   0 .. P-1 : digit histograms of radix pass k (stage 0 also carries the moments)
-//           P        : tail (count, sum) + fixed-bin histogram counts
-// with P = number of radix passes (3 for fp32 keys, 7 for fp64), or 0 when no
-// percentile is requested.
+// Stages:   0        : moments header + pilot samples (terminal values, fan-chart rows)
+//           1 .. P   : output of narrowing pass k (bracket counts, histograms, candidates)
+//           P + 1    : tail (count, sum) + fixed-bin histogram counts
+// P is normally 2; after the second pass the host reads a device counter of rows that
+// still have undecided order statistics (identical on every rank) and keeps going if needed.
 #include <cuda_runtime.h>
 
 #include <cstdio>
@@ -65,7 +66,9 @@ struct mc_handle {
     DevBuf<BlockPartial> partials;
     DevBuf<DeviceResult> res;
     DevBuf<SelectPlan> plans;           // [2]: terminal, fan
-    DevBuf<RowState> states_t, states_f;
+    DevBuf<RowSel> states_t, states_f;
+    DevBuf<unsigned int> pending;       // [1] rows with undecided targets after the latest scan
+    PinnedBuf<unsigned int> h_pending;
     DevBuf<double> pct_t;               // [3 * MC_MAX_PCTS]
     DevBuf<double> fan;                 // [rows * n_path_pcts]
     DevBuf<double> tail_scratch;        // [2 * 1024]
@@ -80,8 +83,8 @@ struct mc_handle {
     mc_params p{};
     SelectProblem prob_t{}, prob_f{};
     bool has_t = false, has_f = false;
-    int n_sel = 0;          // radix passes to run
-    int call_idx = 0;
+    int phase = 0;          // 0: gathered = stage 0; 1: gathered = a pass stage; 2: gathered = final stage
+    int pass_idx = 0;       // narrowing passes enqueued so far
     int tail_idx = -1;
     size_t next_words = 0;  // words of the stage buffer most recently written
     unsigned launches = 0;
@@ -103,27 +106,37 @@ int cuda_fail(mc_handle* h, cudaError_t e, const char* where) {
         if (e__ != cudaSuccess) return cuda_fail((h), e__, #call);        \
     } while (0)
 
-size_t hist_words(const SelectProblem& sp, int pass) {
-    const size_t nb = (size_t)1 << sp.plan.pass_bits[pass];
-    const size_t g_cap = pass == 0 ? 1 : (size_t)sp.plan.n_targets;
-    return (sp.rows * g_cap * nb + 1) / 2;
-}
-
-// words of hist stage `pass` and the offsets of its parts
-struct StageLayout { size_t off_t, off_f, words; };
-StageLayout layout_hist_stage(const mc_handle* h, int pass) {
-    StageLayout L{};
-    size_t w = pass == 0 ? STAGE0_HEADER : 0;
+// ---- stage buffer layouts (8-byte words) ----
+struct Stage0Layout { size_t off_t, off_f, words; };
+Stage0Layout layout_stage0(const mc_handle* h) {
+    Stage0Layout L{};
+    size_t w = STAGE0_HEADER;
     L.off_t = w;
-    // the stage-0 histogram of the terminal values is always produced (it is fused into the sim kernel)
-    if (pass == 0) w += DIGIT0_BINS / 2;
-    else if (h->has_t) w += hist_words(h->prob_t, pass);
+    if (h->has_t) w += sample_words(h->prob_t);
     L.off_f = w;
-    if (h->has_f) w += hist_words(h->prob_f, pass);
+    if (h->has_f) w += sample_words(h->prob_f);
+    L.words = w;
+    return L;
+}
+struct PassLayout { size_t off_t, off_f, words; };
+PassLayout layout_pass(const mc_handle* h) {
+    PassLayout L{};
+    L.off_t = 0;
+    size_t w = h->has_t ? pass_words(h->prob_t) : 0;
+    L.off_f = w;
+    if (h->has_f) w += pass_words(h->prob_f);
     L.words = w;
     return L;
 }
 size_t final_stage_words(const mc_params& p) { return 2 + (size_t)p.hist_bins; }
+
+unsigned int ranks_of(const mc_params& p) { return p.n_ranks ? p.n_ranks : 1u; }
+
+void setup_sampling(SelectProblem& sp, unsigned int n_ranks, bool contiguous) {
+    sp.m_slot = sample_slot(sp.dtype, n_ranks);
+    sp.m_local = sp.n < sp.m_slot ? (unsigned int)sp.n : sp.m_slot;
+    sp.sample_contiguous = contiguous ? 1 : 0;
+}
 
 int validate(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void* d_pool, const void* d_shocks,
              void* d_paths, void* d_terminal) {
@@ -194,7 +207,8 @@ int mc_create(int device_ordinal, mc_handle** out) {
     h->dev.max_smem_optin = (int)prop.sharedMemPerBlockOptin;
     bool ok = h->partials.reserve(MAX_SIM_GRID) == cudaSuccess && h->res.reserve(1) == cudaSuccess &&
               h->plans.reserve(2) == cudaSuccess && h->states_t.reserve(1) == cudaSuccess &&
-              h->pct_t.reserve(3 * MC_MAX_PCTS) == cudaSuccess && h->tail_scratch.reserve(2 * 1024) == cudaSuccess;
+              h->pct_t.reserve(3 * MC_MAX_PCTS) == cudaSuccess && h->tail_scratch.reserve(2 * 1024) == cudaSuccess &&
+              h->pending.reserve(1) == cudaSuccess && h->h_pending.reserve(1) == cudaSuccess;
     for (int i = 0; i < 3 && ok; ++i) ok = cudaEventCreate(&h->ev[i]) == cudaSuccess;
     if (!ok) {
         e = cudaGetLastError();
@@ -210,7 +224,7 @@ int mc_destroy(mc_handle* h) {
     cudaSetDevice(h->device);
     h->partials.release(); h->res.release(); h->plans.release(); h->states_t.release(); h->states_f.release();
     h->pct_t.release(); h->fan.release(); h->tail_scratch.release(); h->edges.release(); h->hist_total.release();
-    h->stage.release(); h->h_stage.release();
+    h->stage.release(); h->h_stage.release(); h->pending.release(); h->h_pending.release();
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     delete h;
     return MC_OK;
@@ -218,10 +232,13 @@ int mc_destroy(mc_handle* h) {
 
 int64_t mc_stage_max_words(const mc_params* p) {
     if (!p) return -1;
-    const size_t rows_f = (p->flags & MC_FLAG_FAN_CHART) ? (size_t)p->n_steps + 1 : 0;
-    const size_t nt_t = 2 * (size_t)p->n_pcts, nt_f = 2 * (size_t)p->n_path_pcts;
-    size_t w0 = STAGE0_HEADER + DIGIT0_BINS / 2 + rows_f * DIGIT0_BINS / 2;
-    size_t wk = nt_t * DIGIT_BINS / 2 + rows_f * nt_f * DIGIT_BINS / 2;
+    const unsigned int R = ranks_of(*p);
+    const size_t ku = (size_t)key_units(p->dtype), slot = sample_slot(p->dtype, R);
+    const size_t rows_f = ((p->flags & MC_FLAG_FAN_CHART) && p->n_path_pcts) ? (size_t)p->n_steps + 1 : 0;
+    const bool sel_t = p->n_pcts > 0 && !(p->flags & MC_FLAG_NO_TERMINAL_SELECT);
+    const size_t nt_t = sel_t ? 2 * (size_t)p->n_pcts : 0, nt_f = 2 * (size_t)p->n_path_pcts;
+    size_t w0 = STAGE0_HEADER + (sel_t ? (slot * ku + 1) / 2 : 0) + (rows_f * slot * ku + 1) / 2;
+    size_t wk = (row_slot_u32(p->dtype, (int)nt_t) + rows_f * row_slot_u32(p->dtype, (int)nt_f)) / 2;
     size_t wf = 2 + (size_t)p->hist_bins;
     size_t m = w0 > wk ? w0 : wk;
     return (int64_t)(m > wf ? m : wf);
@@ -238,16 +255,19 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
     h->active = false;
     h->p = *p;
     h->launches = 0;
-    h->call_idx = 0;
+    h->phase = 0;
+    h->pass_idx = 0;
     h->d_terminal = d_terminal;
     h->has_t = p->n_pcts > 0 && !(p->flags & MC_FLAG_NO_TERMINAL_SELECT);
     h->has_f = (p->flags & MC_FLAG_FAN_CHART) && p->n_path_pcts > 0;
     h->tail_idx = -1;
+    const unsigned int R = ranks_of(*p);
     if (h->has_t) {
         if (!build_select_plan(p->pcts, (int)p->n_pcts, p->n_paths_global, p->dtype, &h->prob_t.plan))
             return fail(h, MC_ERR_INVALID, "percentiles must be ascending and within [0, 100]");
         h->prob_t.x = d_terminal; h->prob_t.dtype = p->dtype; h->prob_t.rows = 1; h->prob_t.n = p->n_paths;
         h->prob_t.ld = p->n_paths; h->prob_t.d_states = h->states_t.p;
+        setup_sampling(h->prob_t, R, true);            // paths are iid: the first values are a random sample
         if ((rc = upload_plan(h, h->prob_t, 0, s))) return rc;
         if (p->tail_pct >= 0.0) {
             for (unsigned k = 0; k < p->n_pcts; ++k) if (p->pcts[k] == p->tail_pct) h->tail_idx = (int)k;
@@ -263,31 +283,37 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
         MC_CUDA(h, h->fan.reserve(rows * p->n_path_pcts));
         h->prob_f.x = d_paths; h->prob_f.dtype = p->dtype; h->prob_f.rows = rows; h->prob_f.n = p->n_paths;
         h->prob_f.ld = p->paths_ld ? p->paths_ld : p->n_paths; h->prob_f.d_states = h->states_f.p;
+        setup_sampling(h->prob_f, R, true);
         if ((rc = upload_plan(h, h->prob_f, 1, s))) return rc;
     }
-    h->n_sel = (h->has_t || h->has_f) ? (h->has_t ? h->prob_t.plan.n_passes : h->prob_f.plan.n_passes) : 0;
     if (p->hist_bins) {
-        MC_CUDA(h, h->edges.reserve((size_t)p->hist_bins + 1));
+        MC_CUDA(h, h->edges.reserve(2 * ((size_t)p->hist_bins + 2)));
         MC_CUDA(h, h->hist_total.reserve(p->hist_bins));
     }
-    const StageLayout L = layout_hist_stage(h, 0);
+    const Stage0Layout L = layout_stage0(h);
     if (!d_stage_out || cap_words < (uint64_t)mc_stage_max_words(p))
         return fail(h, MC_ERR_INVALID, "stage buffer smaller than mc_stage_max_words()");
     unsigned long long* out = static_cast<unsigned long long*>(d_stage_out);
 
     MC_CUDA(h, cudaEventRecord(h->ev[0], s));
-    MC_CUDA(h, cudaMemsetAsync(out, 0, L.words * sizeof(unsigned long long), s));
     SimBuffers b{};
     b.d_pool = d_pool; b.d_shocks = d_shocks; b.d_paths = d_paths; b.d_terminal = d_terminal;
     b.d_partials = h->partials.p;
-    b.d_hist0 = reinterpret_cast<unsigned int*>(out + L.off_t);
     int grid = 0;
-    MC_CUDA(h, launch_simulation(*p, pf, b, h->dev, &grid, s));
+    if (p->n_paths) {
+        MC_CUDA(h, launch_simulation(*p, pf, b, h->dev, &grid, s));
+        h->launches += 1;
+    }
     MC_CUDA(h, cudaEventRecord(h->ev[1], s));
-    MC_CUDA(h, launch_reduce_partials(h->partials.p, grid, out, s));
-    h->launches += 2;
-    if (h->has_f) {
-        MC_CUDA(h, launch_select_hist(h->prob_f, 0, reinterpret_cast<unsigned int*>(out + L.off_f), h->dev.sm_count, s));
+    MC_CUDA(h, launch_reduce_partials(h->partials.p, grid, out, h->has_t ? h->prob_t.m_local : 0,
+                                      h->has_f ? h->prob_f.m_local : 0, s));
+    h->launches += 1;
+    if (h->has_t && h->prob_t.m_local) {
+        MC_CUDA(h, launch_select_sample(h->prob_t, out + L.off_t, s));
+        h->launches += 1;
+    }
+    if (h->has_f && h->prob_f.m_local) {
+        MC_CUDA(h, launch_select_sample(h->prob_f, out + L.off_f, s));
         h->launches += 1;
     }
     h->next_words = L.words;
@@ -295,19 +321,60 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
     return MC_OK;
 }
 
+// enqueue one narrowing pass of every selection problem into `out`
+static int enqueue_pass(mc_handle* h, unsigned long long* out, cudaStream_t s) {
+    const PassLayout L = layout_pass(h);
+    const bool first = h->pass_idx == 0;
+    if (h->has_t) {
+        MC_CUDA(h, launch_select_pass(h->prob_t, first, out + L.off_t, h->dev.sm_count, s));
+        h->launches += h->prob_t.n ? 1 : 0;
+    }
+    if (h->has_f) {
+        MC_CUDA(h, launch_select_pass(h->prob_f, first, out + L.off_f, h->dev.sm_count, s));
+        h->launches += h->prob_f.n ? 1 : 0;
+    }
+    h->pass_idx += 1;
+    h->next_words = L.words;
+    return MC_OK;
+}
+
+// percentiles from the decided keys, then the final stage: [tail count, tail sum, histogram counts...]
+static int enqueue_closing(mc_handle* h, unsigned long long* out, cudaStream_t s) {
+    const mc_params& p = h->p;
+    if (h->has_t) {
+        double* pct = h->pct_t.p;
+        MC_CUDA(h, launch_select_finish(h->prob_t, pct, pct + MC_MAX_PCTS, pct + 2 * MC_MAX_PCTS, s));
+        MC_CUDA(h, launch_publish_percentiles(pct, pct + MC_MAX_PCTS, pct + 2 * MC_MAX_PCTS, (int)p.n_pcts,
+                                              h->tail_idx, h->res.p, s));
+        h->launches += 2;
+    }
+    if (h->has_f) {
+        MC_CUDA(h, launch_select_finish(h->prob_f, h->fan.p, nullptr, nullptr, s));
+        h->launches += 1;
+    }
+    const bool want_tail = h->has_t && h->tail_idx >= 0;
+    MC_CUDA(h, launch_tail_hist(h->d_terminal, p.dtype, p.n_paths, want_tail, p.hist_bins, p.hist_lo, p.hist_hi,
+                                h->res.p, h->edges.p, h->tail_scratch.p, out, h->dev.sm_count, s));
+    h->launches += (p.hist_bins ? 1 : 0) + ((p.n_paths && (want_tail || p.hist_bins)) ? 1 : 0) + (want_tail && p.n_paths ? 1 : 0);
+    h->next_words = final_stage_words(p);
+    h->phase = 2;
+    return MC_OK;
+}
+
 static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ranks, void* d_stage_out, int* done,
                              cudaStream_t s) {
     if (!h->active) return fail(h, MC_ERR_STATE, "mc_stage_next without mc_stage_begin");
     if (!d_gathered || !d_stage_out || n_ranks == 0 || !done) return fail(h, MC_ERR_INVALID, "bad stage arguments");
+    if (n_ranks != ranks_of(h->p)) return fail(h, MC_ERR_INVALID, "n_ranks differs from mc_params.n_ranks");
     MC_CUDA(h, cudaSetDevice(h->device));
     const unsigned long long* g = static_cast<const unsigned long long*>(d_gathered);
     unsigned long long* out = static_cast<unsigned long long*>(d_stage_out);
     const mc_params& p = h->p;
     const size_t stride = h->next_words;      // words per rank in `gathered`
-    const int c = h->call_idx++;
+    const bool selecting = h->has_t || h->has_f;
     *done = 0;
 
-    if (c == (h->n_sel > 0 ? h->n_sel : 1)) {      // gathered = final stage
+    if (h->phase == 2) {                      // gathered = final stage
         MC_CUDA(h, launch_merge_final(g, n_ranks, stride, p.hist_bins, h->res.p, h->hist_total.p, s));
         h->launches += 1;
         MC_CUDA(h, cudaEventRecord(h->ev[2], s));
@@ -315,63 +382,43 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
         h->active = false;
         return MC_OK;
     }
-    if (c == 0) {
+    if (h->phase == 0) {                      // gathered = stage 0: moments + pilot samples
         MC_CUDA(h, launch_merge_moments(g, n_ranks, stride, p.s0, h->res.p, s));
         h->launches += 1;
-    }
-    if (c < h->n_sel) {
-        const StageLayout L = layout_hist_stage(h, c);
+        if (!selecting) return enqueue_closing(h, out, s);
+        const Stage0Layout L = layout_stage0(h);
         if (h->has_t) {
-            MC_CUDA(h, launch_select_scan(h->prob_t, c, reinterpret_cast<const unsigned int*>(g + L.off_t), n_ranks,
-                                          stride * 2, s));
+            MC_CUDA(h, launch_select_brackets(h->prob_t, g, L.off_t, 6, n_ranks, stride, h->dev.max_smem_optin, s));
             h->launches += 1;
         }
         if (h->has_f) {
-            MC_CUDA(h, launch_select_scan(h->prob_f, c, reinterpret_cast<const unsigned int*>(g + L.off_f), n_ranks,
-                                          stride * 2, s));
+            MC_CUDA(h, launch_select_brackets(h->prob_f, g, L.off_f, 7, n_ranks, stride, h->dev.max_smem_optin, s));
             h->launches += 1;
         }
-        if (c + 1 < h->n_sel) {
-            const StageLayout N = layout_hist_stage(h, c + 1);
-            if (h->has_t) {
-                MC_CUDA(h, launch_select_hist(h->prob_t, c + 1, reinterpret_cast<unsigned int*>(out + N.off_t),
-                                              h->dev.sm_count, s));
-                h->launches += 1;
-            }
-            if (h->has_f) {
-                MC_CUDA(h, launch_select_hist(h->prob_f, c + 1, reinterpret_cast<unsigned int*>(out + N.off_f),
-                                              h->dev.sm_count, s));
-                h->launches += 1;
-            }
-            h->next_words = N.words;
-            return MC_OK;
-        }
-        // last radix pass done: keys are exact -> percentiles
-        if (h->has_t) {
-            double* pct = h->pct_t.p;
-            MC_CUDA(h, launch_select_finish(h->prob_t, pct, pct + MC_MAX_PCTS, pct + 2 * MC_MAX_PCTS, s));
-            MC_CUDA(h, launch_publish_percentiles(pct, pct + MC_MAX_PCTS, pct + 2 * MC_MAX_PCTS, (int)p.n_pcts,
-                                                  h->tail_idx, h->res.p, s));
-            h->launches += 2;
-        }
-        if (h->has_f) {
-            MC_CUDA(h, launch_select_finish(h->prob_f, h->fan.p, nullptr, nullptr, s));
-            h->launches += 1;
-        }
+        h->phase = 1;
+        return enqueue_pass(h, out, s);
     }
-    // emit the final stage: [tail count, tail sum, histogram counts...]
-    MC_CUDA(h, cudaMemsetAsync(out, 0, 2 * sizeof(unsigned long long), s));
-    if (h->has_t && h->tail_idx >= 0) {
-        MC_CUDA(h, launch_tail(h->d_terminal, p.dtype, p.n_paths, h->res.p, h->tail_scratch.p, out, h->dev.sm_count, s));
-        h->launches += 2;
+    // gathered = output of narrowing pass `pass_idx`
+    const PassLayout L = layout_pass(h);
+    MC_CUDA(h, cudaMemsetAsync(h->pending.p, 0, sizeof(unsigned int), s));
+    if (h->has_t) {
+        MC_CUDA(h, launch_select_scan(h->prob_t, g + L.off_t, n_ranks, stride, h->pending.p, s));
+        h->launches += 1;
     }
-    if (p.hist_bins) {
-        MC_CUDA(h, launch_value_hist(h->d_terminal, p.dtype, p.n_paths, p.hist_bins, p.hist_lo, p.hist_hi, h->res.p,
-                                     h->edges.p, out + 2, h->dev.sm_count, s));
-        h->launches += 2;
+    if (h->has_f) {
+        MC_CUDA(h, launch_select_scan(h->prob_f, g + L.off_f, n_ranks, stride, h->pending.p, s));
+        h->launches += 1;
     }
-    h->next_words = final_stage_words(p);
-    return MC_OK;
+    bool more = true;
+    if (h->pass_idx >= 2) {
+        // the second pass normally decides everything; ask the device (same answer on every rank)
+        MC_CUDA(h, cudaMemcpyAsync(h->h_pending.p, h->pending.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
+        MC_CUDA(h, cudaStreamSynchronize(s));
+        more = *h->h_pending.p != 0;
+        if (more && h->pass_idx >= SEL_MAX_PASSES) return fail(h, MC_ERR_STATE, "selection did not converge");
+    }
+    if (more) return enqueue_pass(h, out, s);
+    return enqueue_closing(h, out, s);
 }
 
 static int fetch_locked(mc_handle* h, mc_result* r, uint64_t* h_hist, double* h_fan, cudaStream_t s) {
@@ -442,7 +489,7 @@ int mc_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void*
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (!p) return fail(h, MC_ERR_INVALID, "params is NULL");
     if (p->struct_size != sizeof(mc_params)) return fail(h, MC_ERR_VERSION, "mc_params struct_size mismatch");
-    if (p->n_paths != p->n_paths_global || p->path_offset + p->n_paths < p->n_paths)
+    if (p->n_paths != p->n_paths_global || p->path_offset + p->n_paths < p->n_paths || p->n_ranks > 1)
         return fail(h, MC_ERR_INVALID, "mc_run is single-rank: n_paths must equal n_paths_global");
     MC_CUDA(h, cudaSetDevice(h->device));
     const size_t cap = (size_t)mc_stage_max_words(p);
@@ -481,25 +528,36 @@ int mc_percentiles(mc_handle* h, const void* d_x, int32_t dtype, uint64_t rows, 
     if (!h) return MC_ERR_INVALID;
     std::lock_guard<std::mutex> lock(h->mu);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    if (!d_x || !pcts || !h_out || rows == 0 || n == 0 || n_pcts == 0 || rows > 65535 || ld < n)
+    if (!d_x || !pcts || !h_out || rows == 0 || n == 0 || n_pcts == 0 || rows > 65535 || ld < n ||
+        (dtype != MC_F32 && dtype != MC_F64))
         return fail(h, MC_ERR_INVALID, "bad mc_percentiles arguments");
+    if (h->active) return fail(h, MC_ERR_STATE, "a staged run is in flight on this handle");
     MC_CUDA(h, cudaSetDevice(h->device));
     SelectProblem sp{};
     if (!build_select_plan(pcts, (int)n_pcts, n, dtype, &sp.plan))
         return fail(h, MC_ERR_INVALID, "percentiles must be ascending and within [0, 100]");
     sp.x = d_x; sp.dtype = dtype; sp.rows = rows; sp.n = n; sp.ld = ld;
+    setup_sampling(sp, 1, false);                      // arbitrary data: strided sample
     MC_CUDA(h, h->states_f.reserve(rows));
     MC_CUDA(h, h->fan.reserve(rows * n_pcts));
     sp.d_states = h->states_f.p;
     int rc = upload_plan(h, sp, 1, s);
     if (rc) return rc;
-    size_t cap = 0;
-    for (int k = 0; k < sp.plan.n_passes; ++k) { const size_t w = hist_words(sp, k); if (w > cap) cap = w; }
-    MC_CUDA(h, h->stage.reserve(cap));
-    unsigned int* hist = reinterpret_cast<unsigned int*>(h->stage.p);
-    for (int k = 0; k < sp.plan.n_passes; ++k) {
-        MC_CUDA(h, launch_select_hist(sp, k, hist, h->dev.sm_count, s));
-        MC_CUDA(h, launch_select_scan(sp, k, hist, 1, 0, s));
+    const size_t w0 = STAGE0_HEADER + sample_words(sp), wk = pass_words(sp);
+    MC_CUDA(h, h->stage.reserve(w0 > wk ? w0 : wk));
+    unsigned long long* st = h->stage.p;
+    MC_CUDA(h, launch_reduce_partials(h->partials.p, 0, st, 0, sp.m_local, s));
+    MC_CUDA(h, launch_select_sample(sp, st + STAGE0_HEADER, s));
+    MC_CUDA(h, launch_select_brackets(sp, st, STAGE0_HEADER, 7, 1, w0, h->dev.max_smem_optin, s));
+    for (int pass = 0;; ++pass) {
+        MC_CUDA(h, launch_select_pass(sp, pass == 0, st, h->dev.sm_count, s));
+        MC_CUDA(h, cudaMemsetAsync(h->pending.p, 0, sizeof(unsigned int), s));
+        MC_CUDA(h, launch_select_scan(sp, st, 1, wk, h->pending.p, s));
+        if (pass == 0) continue;
+        MC_CUDA(h, cudaMemcpyAsync(h->h_pending.p, h->pending.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
+        MC_CUDA(h, cudaStreamSynchronize(s));
+        if (*h->h_pending.p == 0) break;
+        if (pass + 1 >= SEL_MAX_PASSES) return fail(h, MC_ERR_STATE, "selection did not converge");
     }
     MC_CUDA(h, launch_select_finish(sp, h->fan.p, nullptr, nullptr, s));
     MC_CUDA(h, cudaMemcpyAsync(h_out, h->fan.p, rows * n_pcts * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -512,13 +570,16 @@ int mc_histogram(mc_handle* h, const void* d_x, int32_t dtype, uint64_t n, uint3
     if (!h) return MC_ERR_INVALID;
     std::lock_guard<std::mutex> lock(h->mu);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    if ((!d_x && n) || !h_counts || bins == 0 || bins > (1u << 16) || !(lo < hi))
+    if ((!d_x && n) || !h_counts || bins == 0 || bins > (1u << 16) || !(lo < hi) ||
+        (dtype != MC_F32 && dtype != MC_F64))
         return fail(h, MC_ERR_INVALID, "bad mc_histogram arguments (explicit lo < hi required)");
+    if (h->active) return fail(h, MC_ERR_STATE, "a staged run is in flight on this handle");
     MC_CUDA(h, cudaSetDevice(h->device));
-    MC_CUDA(h, h->edges.reserve((size_t)bins + 1));
-    MC_CUDA(h, h->hist_total.reserve(bins));
-    MC_CUDA(h, launch_value_hist(d_x, dtype, n, bins, lo, hi, h->res.p, h->edges.p, h->hist_total.p, h->dev.sm_count, s));
-    MC_CUDA(h, cudaMemcpyAsync(h_counts, h->hist_total.p, (size_t)bins * 8, cudaMemcpyDeviceToHost, s));
+    MC_CUDA(h, h->edges.reserve(2 * ((size_t)bins + 2)));
+    MC_CUDA(h, h->stage.reserve(2 + (size_t)bins));
+    MC_CUDA(h, launch_tail_hist(d_x, dtype, n, false, bins, lo, hi, h->res.p, h->edges.p, h->tail_scratch.p,
+                                h->stage.p, h->dev.sm_count, s));
+    MC_CUDA(h, cudaMemcpyAsync(h_counts, h->stage.p + 2, (size_t)bins * 8, cudaMemcpyDeviceToHost, s));
     MC_CUDA(h, cudaStreamSynchronize(s));
     return MC_OK;
 }

@@ -9,12 +9,14 @@
 namespace mc {
 
 constexpr int SIM_BLOCK = 256;
-constexpr int DIGIT0_BITS = 12;                 // first radix digit, histogrammed inside the sim kernel
-constexpr int DIGIT0_BINS = 1 << DIGIT0_BITS;
-constexpr int DIGIT_BITS = 10;                  // later digits
-constexpr int DIGIT_BINS = 1 << DIGIT_BITS;
 constexpr int MAX_TARGETS = 2 * MC_MAX_PCTS;    // two order statistics per percentile
-constexpr int MAX_PASSES = 8;
+constexpr int MAX_IV = MAX_TARGETS;             // key intervals tracked per row
+constexpr int SEL_BIN_BITS = 10;
+constexpr int SEL_BINS = 1 << SEL_BIN_BITS;     // sub-bins per interval per narrowing pass
+constexpr int SEL_CAND = 1024;                  // an interval holding <= this many values is collected and sorted
+constexpr int SEL_SAMPLE_MAX = 32768;           // pilot sample per row (all ranks together), fp32 keys
+constexpr int SEL_SAMPLE_MAX_F64 = 16384;       // ... fp64 keys (sorted in shared memory)
+constexpr int SEL_MAX_PASSES = 12;              // hard stop of the narrowing loop (never reached: 64 bits / 10 + miss)
 
 // ---- order-preserving integer keys ------------------------------------------------
 // key(a) < key(b)  <=>  a < b  for all non-NaN floats (negative portfolio values included)
@@ -65,8 +67,9 @@ struct BlockPartial {
 };
 
 // ---- stage-0 packed words (per rank) --------------------------------------------
-// [0] n  [1] n_above  [2] sum_d  [3] sum_d2  [4] min  [5] max  [6..] digit-0 histogram
-constexpr int STAGE0_HEADER = 6;
+// [0] n  [1] n_above  [2] sum_d  [3] sum_d2  [4] min  [5] max  [6] unused  [7] unused
+// then the pilot samples: terminal problem, then the rows of the fan-chart problem
+constexpr int STAGE0_HEADER = 8;
 
 // ---- merged result block kept on the device, copied out by mc_fetch_result --------
 struct DeviceResult {
@@ -80,29 +83,34 @@ struct DeviceResult {
     double center;        // s0: moments are accumulated about it
 };
 
-// ---- radix-select bookkeeping -------------------------------------------------------
+// ---- exact selection by interval narrowing ------------------------------------------
 // One SelectPlan per problem (terminal values, or the rows of the stored paths).
 struct SelectPlan {
     int n_targets;                        // sorted, distinct global ranks
     int n_pcts;
-    int n_passes;
     int key_bits;
-    int pass_bits[MAX_PASSES];
-    int pass_shift[MAX_PASSES];
+    int pad;
+    unsigned long long n_global;          // values per row over all ranks
     unsigned long long rank[MAX_TARGETS]; // global 0-based order-statistic ranks
     int pct_lo_idx[MC_MAX_PCTS];          // target index of floor(h) and floor(h)+1
     int pct_hi_idx[MC_MAX_PCTS];
     double pct_gamma[MC_MAX_PCTS];
 };
 
-// per-row mutable state of the select
-struct RowState {
-    unsigned long long prefix[MAX_TARGETS];     // key bits decided so far (right-aligned)
-    unsigned long long remaining[MAX_TARGETS];  // rank within the elements sharing the prefix
-    int group[MAX_TARGETS];                     // index into group_prefix
-    int n_groups;
-    int pad;
-    unsigned long long group_prefix[MAX_TARGETS];
+enum { IV_HIST = 0, IV_COLLECT = 1 };
+
+// per-row state: a sorted list of disjoint key intervals [lo, hi], each known to hold some
+// of the row's target ranks.  A pass histograms (or, for small populations, collects) the
+// values inside each interval; the scan then shrinks every target's interval.
+struct RowSel {
+    int n_iv;                                   // 0: every target of this row is decided
+    int below_known;                            // 0 before the first pass (counts below lo come from it)
+    unsigned long long lo[MAX_IV], hi[MAX_IV];  // inclusive key bounds
+    unsigned long long below[MAX_IV];           // # values (all ranks) with key < lo
+    int shift[MAX_IV];                          // bin = (key - lo) >> shift  (< SEL_BINS)
+    int mode[MAX_IV];                           // IV_HIST / IV_COLLECT
+    int target_iv[MAX_TARGETS];                 // interval of target j, -1 when decided
+    unsigned long long key[MAX_TARGETS];        // decided key of target j
 };
 
 }  // namespace mc

@@ -1,14 +1,24 @@
-// mc_select.cu -- exact percentiles by multi-target radix select, CVaR tail sums and
-// the fixed-bin histogram, for sm_100a.
+// mc_select.cu -- exact percentiles by pilot-bracketed interval narrowing, CVaR tail sums
+// and the fixed-bin histogram, for sm_100a.
 //
 // Replaces the reference's `np.percentile(final_prices, p)` x9 (app.py:638-640) and
 // `np.percentile(paths, p, axis=1)` x5 (app.py:643-645), each of which re-partitions
-// its whole input on the host.  Here all order statistics of a row are found together:
-// values are mapped to order-preserving integer keys and every target rank is narrowed
-// one radix digit per pass from digit histograms.  The histograms are the ONLY thing
-// that crosses GPUs when paths are sharded (a few KB per pass), so the result is the
-// exact global order statistic with no data movement.  The first digit of the terminal
-// values comes for free from the simulation kernel.
+// its whole input on the host (61-72 % of the reference's run time).
+//
+// All order statistics of a row are found together, exactly, in (normally) two streaming
+// reads of the row:
+//   pilot    a small sample of the row (the first columns: paths are iid) is histogrammed
+//            and gives, for every percentile, a key bracket that holds its order statistics
+//            with probability 1 - 1e-5 (4.5 sigma of the sample-quantile error);
+//   pass 1   every value is compared with the bracket bounds IN REGISTERS (exact counts of
+//            the values below each bracket); only the few percent inside a bracket touch
+//            shared memory (a 1024-bin histogram of the bracket);
+//   scan     the target's bin becomes its new interval: 1/1024 of the bracket;
+//   pass 2   intervals holding <= 1024 values are collected and sorted -> exact keys;
+//            wider ones are histogrammed again (x1024 narrower each time).
+// A bracket that missed (or a heavy tie) just costs that row extra passes; the result is
+// always the exact order statistic.  Counts, histograms and candidates are the ONLY thing
+// that crosses GPUs when paths are sharded, so no path data moves.
 //
 // Interpolation follows NumPy's method='linear' exactly (lib/_function_base_impl.py
 // `_lerp`): a + (b-a)*t, and b - (b-a)*(1-t) when t >= 0.5, in fp64 without FMA
@@ -19,6 +29,10 @@
 
 namespace mc {
 
+constexpr double SEL_Z = 4.5;            // bracket half-width in sample-quantile standard errors
+constexpr int PILOT_BIN_BITS = 12;
+constexpr int PILOT_BINS = 1 << PILOT_BIN_BITS;
+
 // ------------------------------------------------------------------ plan (host)
 bool build_select_plan(const double* pcts, int n_pcts, unsigned long long n_global, int dtype,
                        SelectPlan* plan) {
@@ -27,17 +41,7 @@ bool build_select_plan(const double* pcts, int n_pcts, unsigned long long n_glob
     sp = SelectPlan{};
     sp.n_pcts = n_pcts;
     sp.key_bits = dtype == MC_F64 ? 64 : 32;
-    int left = sp.key_bits;
-    int np_ = 0;
-    while (left > 0) {
-        const int want = np_ == 0 ? DIGIT0_BITS : DIGIT_BITS;
-        const int b = left < want ? left : want;
-        left -= b;
-        sp.pass_bits[np_] = b;
-        sp.pass_shift[np_] = left;
-        ++np_;
-    }
-    sp.n_passes = np_;
+    sp.n_global = n_global;
     // np.percentile: q = p/100; virtual index (n-1)*q; floor and floor+1 (clamped); gamma
     unsigned long long lo[MC_MAX_PCTS], hi[MC_MAX_PCTS];
     for (int k = 0; k < n_pcts; ++k) {
@@ -56,15 +60,13 @@ bool build_select_plan(const double* pcts, int n_pcts, unsigned long long n_glob
     }
     // sorted distinct target ranks (ranks are non-decreasing in k already; merge lo/hi)
     int nt = 0;
-    auto push = [&](unsigned long long r) -> int {
+    auto push = [&](unsigned long long r) {
         for (int j = 0; j < nt; ++j)
-            if (sp.rank[j] == r) return j;
-        sp.rank[nt] = r;
-        return nt++;
+            if (sp.rank[j] == r) return;
+        sp.rank[nt++] = r;
     };
     for (int k = 0; k < n_pcts; ++k) { push(lo[k]); push(hi[k]); }
-    // insertion sort (nt <= 32)
-    for (int a = 1; a < nt; ++a) {
+    for (int a = 1; a < nt; ++a) {      // insertion sort (nt <= 32)
         const unsigned long long v = sp.rank[a];
         int b = a - 1;
         while (b >= 0 && sp.rank[b] > v) { sp.rank[b + 1] = sp.rank[b]; --b; }
@@ -80,184 +82,480 @@ bool build_select_plan(const double* pcts, int n_pcts, unsigned long long n_glob
     return true;
 }
 
-// ------------------------------------------------------------------ digit histograms
-template <typename Real>
-__global__ void __launch_bounds__(256) select_hist_kernel(const Real* __restrict__ x, unsigned long long ld,
-                                                          unsigned long long n, const SelectPlan* __restrict__ plan,
-                                                          int pass, const RowState* __restrict__ states,
-                                                          unsigned int* __restrict__ hist) {
-    using Key = typename KeyT<Real>::type;
-    extern __shared__ unsigned int s_bins[];
-    __shared__ unsigned long long s_gp[MAX_TARGETS];
-    const unsigned long long row = blockIdx.y;
-    const int bits = plan->pass_bits[pass], shift = plan->pass_shift[pass];
-    const int nb = 1 << bits;
-    const int g_cap = pass == 0 ? 1 : plan->n_targets;
-    const int ng = pass == 0 ? 1 : states[row].n_groups;
-    if (pass > 0 && threadIdx.x < ng) s_gp[threadIdx.x] = states[row].group_prefix[threadIdx.x];
-    for (int i = threadIdx.x; i < ng * nb; i += blockDim.x) s_bins[i] = 0u;
-    __syncthreads();
-
-    const Real* xr = x + row * ld;
-    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const Key key = key_of(xr[i]);
-        int g = 0;
-        if (pass > 0) {
-            const unsigned long long pfx = (unsigned long long)(key >> (shift + bits));
-            // group prefixes are strictly increasing: binary search
-            int lo = 0, hi = ng - 1;
-            g = -1;
-            while (lo <= hi) {
-                const int mid = (lo + hi) >> 1;
-                const unsigned long long v = s_gp[mid];
-                if (v == pfx) { g = mid; break; }
-                if (v < pfx) lo = mid + 1; else hi = mid - 1;
-            }
-            if (g < 0) continue;
-        }
-        atomicAdd(&s_bins[g * nb + (int)((key >> shift) & (Key)(nb - 1))], 1u);
-    }
-    __syncthreads();
-    unsigned int* out = hist + row * (unsigned long long)g_cap * nb;
-    for (int i = threadIdx.x; i < ng * nb; i += blockDim.x) {
-        const unsigned int c = s_bins[i];
-        if (c) atomicAdd(&out[i], c);
-    }
+unsigned int sample_slot(int dtype, unsigned int n_ranks) {
+    const unsigned int m = dtype == MC_F64 ? SEL_SAMPLE_MAX_F64 : SEL_SAMPLE_MAX;
+    const unsigned int s = m / (n_ranks ? n_ranks : 1);
+    return s < 64 ? 64 : s;
 }
 
-cudaError_t launch_select_hist(const SelectProblem& sp, int pass, unsigned int* d_hist, int sm_count,
-                               cudaStream_t stream) {
-    const int nb = 1 << sp.plan.pass_bits[pass];
-    const int g_cap = pass == 0 ? 1 : sp.plan.n_targets;
-    const size_t bytes = (size_t)sp.rows * g_cap * nb * sizeof(unsigned int);
-    cudaError_t e = cudaMemsetAsync(d_hist, 0, bytes, stream);
-    if (e != cudaSuccess) return e;
-    if (sp.n == 0) return cudaSuccess;
-    const size_t smem = (size_t)g_cap * nb * sizeof(unsigned int);
-    unsigned long long chunks = (sp.n + 256ull * 8 - 1) / (256ull * 8);
-    unsigned long long budget = (unsigned long long)sm_count * 8 / sp.rows;
-    if (budget < 1) budget = 1;
-    if (chunks > budget) chunks = budget;
+template <typename Key> __device__ __forceinline__ Key key_max();
+template <> __device__ __forceinline__ uint32_t key_max<uint32_t>() { return 0xFFFFFFFFu; }
+template <> __device__ __forceinline__ uint64_t key_max<uint64_t>() { return 0xFFFFFFFFFFFFFFFFull; }
+
+__device__ __forceinline__ int bit_length(unsigned long long v) { return v ? 64 - __clzll((long long)v) : 0; }
+
+// ------------------------------------------------------------------ pilot sample
+template <typename Real>
+__global__ void __launch_bounds__(256) select_sample_kernel(const Real* __restrict__ x, unsigned long long ld,
+                                                            unsigned long long n, unsigned int m_local,
+                                                            unsigned int m_slot, unsigned long long stride,
+                                                            typename KeyT<Real>::type* __restrict__ out) {
+    const unsigned long long row = blockIdx.y;
+    const Real* xr = x + row * ld;
+    for (unsigned int s = blockIdx.x * blockDim.x + threadIdx.x; s < m_local; s += gridDim.x * blockDim.x)
+        out[row * m_slot + s] = key_of(xr[(unsigned long long)s * stride]);
+}
+
+cudaError_t launch_select_sample(const SelectProblem& sp, void* d_out, cudaStream_t stream) {
+    if (sp.m_local == 0 || sp.rows == 0) return cudaSuccess;
     if (sp.rows > 65535) return cudaErrorInvalidValue;
-    dim3 grid((unsigned)chunks, (unsigned)sp.rows);
-    if (sp.dtype == MC_F64) {
-        auto k = select_hist_kernel<double>;
-        if (smem > 48 * 1024) {
-            e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e != cudaSuccess) return e;
-        }
-        k<<<grid, 256, smem, stream>>>(static_cast<const double*>(sp.x), sp.ld, sp.n, sp.d_plan, pass,
-                                       sp.d_states, d_hist);
-    } else {
-        auto k = select_hist_kernel<float>;
-        if (smem > 48 * 1024) {
-            e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e != cudaSuccess) return e;
-        }
-        k<<<grid, 256, smem, stream>>>(static_cast<const float*>(sp.x), sp.ld, sp.n, sp.d_plan, pass,
-                                       sp.d_states, d_hist);
-    }
+    const unsigned long long stride = sp.sample_contiguous ? 1ull : (sp.n / sp.m_local ? sp.n / sp.m_local : 1ull);
+    dim3 grid((sp.m_local + 255) / 256, (unsigned)sp.rows);
+    if (grid.x > 32) grid.x = 32;
+    if (sp.dtype == MC_F64)
+        select_sample_kernel<double><<<grid, 256, 0, stream>>>(static_cast<const double*>(sp.x), sp.ld, sp.n, sp.m_local,
+                                                               sp.m_slot, stride, static_cast<uint64_t*>(d_out));
+    else
+        select_sample_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(sp.x), sp.ld, sp.n, sp.m_local,
+                                                              sp.m_slot, stride, static_cast<uint32_t*>(d_out));
     return cudaGetLastError();
 }
 
-// ------------------------------------------------------------------ scan: narrow every target by one digit
-// One block per row.  For each group of targets sharing a key prefix, the block forms the
-// inclusive cumulative count of that group's digit histogram (summed over ranks) and each
-// target binary-searches the digit holding its rank.
-constexpr int SCAN_THREADS = 256;
-
-__global__ void __launch_bounds__(SCAN_THREADS) select_scan_kernel(const SelectPlan* __restrict__ plan, int pass,
-                                                                   const unsigned int* __restrict__ hist,
-                                                                   unsigned int n_ranks, size_t rank_stride_u32,
-                                                                   RowState* __restrict__ states) {
-    __shared__ unsigned long long s_cum[DIGIT0_BINS];
-    __shared__ unsigned long long s_warp[SCAN_THREADS / 32];
-    __shared__ unsigned long long s_prefix[MAX_TARGETS];
+// ------------------------------------------------------------------ brackets from the pilot sample
+// One block per row.  The sample (all ranks' contributions) is histogrammed over its own key
+// range (4096 linear bins: float keys are log-spaced, so this resolves ~0.1 % of a typical
+// row) and each percentile's bracket is rounded OUTWARD to bin edges.
+template <typename Key>
+__global__ void __launch_bounds__(256) select_bracket_kernel(const SelectPlan* __restrict__ plan,
+                                                             const unsigned long long* __restrict__ g,
+                                                             size_t sample_off_words, int hdr_word,
+                                                             unsigned int n_ranks, size_t stride_words,
+                                                             unsigned int m_slot, RowSel* __restrict__ states) {
+    __shared__ unsigned int s_hist[PILOT_BINS];
+    __shared__ unsigned long long s_min[8], s_max[8];
+    __shared__ unsigned int s_warp[8];
+    __shared__ unsigned long long s_lo[MC_MAX_PCTS], s_hi[MC_MAX_PCTS];
     const unsigned long long row = blockIdx.x;
-    RowState& st = states[row];
-    const int nt = plan->n_targets;
-    const int bits = plan->pass_bits[pass];
-    const int nb = 1 << bits;
-    const int g_cap = pass == 0 ? 1 : nt;
-    const int ng = pass == 0 ? 1 : st.n_groups;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    // my target (threads 0..nt-1)
-    unsigned long long my_prefix = 0, my_rem = 0;
-    int my_group = 0;
-    if (tid < nt) {
-        if (pass == 0) { my_prefix = 0; my_rem = plan->rank[tid]; my_group = 0; }
-        else { my_prefix = st.prefix[tid]; my_rem = st.remaining[tid]; my_group = st.group[tid]; }
+    unsigned long long kmin = ~0ull, kmax = 0ull;
+    unsigned int m_total = 0;
+    for (unsigned int r = 0; r < n_ranks; ++r) {
+        const unsigned int m_r = (unsigned int)g[r * stride_words + hdr_word];
+        const Key* src = reinterpret_cast<const Key*>(g + r * stride_words + sample_off_words) + row * m_slot;
+        for (unsigned int i = tid; i < m_r; i += 256) {
+            const unsigned long long k = src[i];
+            kmin = k < kmin ? k : kmin;
+            kmax = k > kmax ? k : kmax;
+        }
+        m_total += m_r;
     }
-    const int per = nb / SCAN_THREADS;            // 16 (pass 0), 4 (10-bit digits), >=1 always? see below
-    for (int g = 0; g < ng; ++g) {
-        const unsigned int* h = hist + (row * g_cap + g) * (unsigned long long)nb;
-        // thread-local inclusive sums over a contiguous segment of bins
-        unsigned long long local[DIGIT0_BINS / SCAN_THREADS];
-        unsigned long long run = 0;
-        const int seg = per > 0 ? per : 1;
-        const int base = tid * seg;
 #pragma unroll
-        for (int k = 0; k < DIGIT0_BINS / SCAN_THREADS; ++k) {
-            if (k < seg && base + k < nb) {
-                unsigned long long c = 0;
-                for (unsigned int r = 0; r < n_ranks; ++r) c += h[r * rank_stride_u32 + base + k];
-                run += c;
-            }
-            local[k] = run;
-        }
-        // exclusive scan of `run` over threads
-        unsigned long long incl = run;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += o;
-        }
-        if (lane == 31) s_warp[warp] = incl;
-        __syncthreads();
-        unsigned long long warp_off = 0;
-        for (int w = 0; w < warp; ++w) warp_off += s_warp[w];
-        const unsigned long long excl = warp_off + incl - run;
-#pragma unroll
-        for (int k = 0; k < DIGIT0_BINS / SCAN_THREADS; ++k)
-            if (k < seg && base + k < nb) s_cum[base + k] = excl + local[k];
-        __syncthreads();
-        if (tid < nt && my_group == g) {
-            // smallest digit d with cum[d] > my_rem
-            int lo = 0, hi = nb - 1;
-            while (lo < hi) {
-                const int mid = (lo + hi) >> 1;
-                if (s_cum[mid] > my_rem) hi = mid; else lo = mid + 1;
-            }
-            my_rem -= lo ? s_cum[lo - 1] : 0ull;
-            my_prefix = (my_prefix << bits) | (unsigned long long)lo;
-        }
-        __syncthreads();
+    for (int d = 16; d > 0; d >>= 1) {
+        const unsigned long long a = __shfl_down_sync(0xffffffffu, kmin, d), b = __shfl_down_sync(0xffffffffu, kmax, d);
+        kmin = a < kmin ? a : kmin;
+        kmax = b > kmax ? b : kmax;
     }
-    if (tid < nt) {
-        st.prefix[tid] = my_prefix;
-        st.remaining[tid] = my_rem;
-        s_prefix[tid] = my_prefix;
+    if (lane == 0) { s_min[warp] = kmin; s_max[warp] = kmax; }
+    for (int i = tid; i < PILOT_BINS; i += 256) s_hist[i] = 0u;
+    __syncthreads();
+    kmin = s_min[0]; kmax = s_max[0];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) { kmin = s_min[w] < kmin ? s_min[w] : kmin; kmax = s_max[w] > kmax ? s_max[w] : kmax; }
+    if (m_total == 0) { kmin = 0; kmax = 0; }
+    const int sh = max(0, bit_length(kmax - kmin) - PILOT_BIN_BITS);
+    for (unsigned int r = 0; r < n_ranks; ++r) {
+        const unsigned int m_r = (unsigned int)g[r * stride_words + hdr_word];
+        const Key* src = reinterpret_cast<const Key*>(g + r * stride_words + sample_off_words) + row * m_slot;
+        for (unsigned int i = tid; i < m_r; i += 256) atomicAdd(&s_hist[(unsigned int)(((unsigned long long)src[i] - kmin) >> sh)], 1u);
+    }
+    __syncthreads();
+    // inclusive scan of the 4096 bins, 16 per thread
+    unsigned int local[PILOT_BINS / 256], run = 0;
+#pragma unroll
+    for (int k = 0; k < PILOT_BINS / 256; ++k) { run += s_hist[tid * (PILOT_BINS / 256) + k]; local[k] = run; }
+    unsigned int incl = run;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned int o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    unsigned int off = incl - run;
+    for (int w = 0; w < warp; ++w) off += s_warp[w];
+#pragma unroll
+    for (int k = 0; k < PILOT_BINS / 256; ++k) s_hist[tid * (PILOT_BINS / 256) + k] = off + local[k];
+    __syncthreads();
+
+    const int np_ = plan->n_pcts;
+    const unsigned long long KMAX = (unsigned long long)key_max<Key>();
+    if (tid < np_) {
+        const double m = (double)m_total, ng = (double)plan->n_global;
+        const double qa = (double)plan->rank[plan->pct_lo_idx[tid]] / ng;
+        const double qb = ((double)plan->rank[plan->pct_hi_idx[tid]] + 1.0) / ng;
+        const double fa = floor(qa * m - SEL_Z * sqrt(m * qa * (1.0 - qa)) - 2.0);
+        const double fb = ceil(qb * m + SEL_Z * sqrt(m * qb * (1.0 - qb)) + 2.0);
+        unsigned long long lo = 0ull, hi = KMAX;
+        auto bin_of_rank = [&](unsigned int r) {       // first bin with cum > r
+            int a = 0, b = PILOT_BINS - 1;
+            while (a < b) { const int mid = (a + b) >> 1; if (s_hist[mid] > r) b = mid; else a = mid + 1; }
+            return a;
+        };
+        if (fa >= 0.0 && m_total) lo = kmin + ((unsigned long long)bin_of_rank((unsigned int)fa) << sh);
+        if (fb < m && m_total) {
+            const unsigned long long span = ((unsigned long long)(bin_of_rank((unsigned int)fb) + 1) << sh) - 1ull;
+            hi = span > KMAX - kmin ? KMAX : kmin + span;
+        }
+        s_lo[tid] = lo; s_hi[tid] = hi;
     }
     __syncthreads();
     if (tid == 0) {
-        // targets are sorted by rank, hence prefixes are non-decreasing: group equal neighbours
-        int g = -1;
-        unsigned long long last = 0;
-        for (int j = 0; j < nt; ++j) {
-            if (j == 0 || s_prefix[j] != last) { ++g; st.group_prefix[g] = s_prefix[j]; last = s_prefix[j]; }
-            st.group[j] = g;
+        RowSel& st = states[row];
+        int iv_of_pct[MC_MAX_PCTS];
+        int n_iv = 0;
+        for (int k = 0; k < np_; ++k) {
+            if (n_iv && s_lo[k] <= st.hi[n_iv - 1]) {             // overlaps the previous bracket: merge
+                if (s_hi[k] > st.hi[n_iv - 1]) st.hi[n_iv - 1] = s_hi[k];
+            } else {
+                st.lo[n_iv] = s_lo[k]; st.hi[n_iv] = s_hi[k];
+                ++n_iv;
+            }
+            iv_of_pct[k] = n_iv - 1;
         }
-        st.n_groups = g + 1;
+        for (int gix = 0; gix < n_iv; ++gix) {
+            st.shift[gix] = max(0, bit_length(st.hi[gix] - st.lo[gix]) - SEL_BIN_BITS);
+            st.mode[gix] = IV_HIST;
+            st.below[gix] = 0ull;
+        }
+        for (int k = 0; k < np_; ++k) {
+            st.target_iv[plan->pct_lo_idx[k]] = iv_of_pct[k];
+            st.target_iv[plan->pct_hi_idx[k]] = iv_of_pct[k];
+        }
+        st.n_iv = n_iv;
+        st.below_known = 0;
     }
 }
 
-cudaError_t launch_select_scan(const SelectProblem& sp, int pass, const unsigned int* d_hist,
-                               unsigned int n_ranks, size_t rank_stride_u32, cudaStream_t stream) {
-    if (sp.plan.n_targets == 0) return cudaSuccess;
-    select_scan_kernel<<<(unsigned)sp.rows, SCAN_THREADS, 0, stream>>>(sp.d_plan, pass, d_hist, n_ranks,
-                                                                       rank_stride_u32, sp.d_states);
+cudaError_t launch_select_brackets(const SelectProblem& sp, const unsigned long long* d_gathered,
+                                   size_t sample_off_words, int hdr_word, unsigned int n_ranks,
+                                   size_t rank_stride_words, int /*max_smem_optin*/, cudaStream_t stream) {
+    if (sp.plan.n_targets == 0 || sp.rows == 0) return cudaSuccess;
+    if (sp.dtype == MC_F64)
+        select_bracket_kernel<uint64_t><<<(unsigned)sp.rows, 256, 0, stream>>>(sp.d_plan, d_gathered, sample_off_words,
+                                                                               hdr_word, n_ranks, rank_stride_words,
+                                                                               sp.m_slot, sp.d_states);
+    else
+        select_bracket_kernel<uint32_t><<<(unsigned)sp.rows, 256, 0, stream>>>(sp.d_plan, d_gathered, sample_off_words,
+                                                                               hdr_word, n_ranks, rank_stride_words,
+                                                                               sp.m_slot, sp.d_states);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ narrowing pass
+// grid (chunks, rows), 256 threads.  NIV > 0: first pass -- the (<= NIV) bracket lower bounds
+// live in registers and every value updates `ge[g] += key >= lo[g]` (2 instructions per
+// bracket, no memory); the same predicates give the candidate bracket.  NIV == 0: later
+// passes -- `below` is already known, intervals are found by a shared-memory binary search.
+constexpr int PASS_UNROLL = 8;
+
+template <typename Key, int NIV>
+struct PassCtx {
+    const Key* s_lo; const Key* s_hi; const int* s_shift; const int* s_mode;
+    unsigned int* s_bins; unsigned int* out_iv; size_t iv_slot; int n_iv;
+    Key lo_r[NIV > 0 ? NIV : 1];
+    unsigned int ge[NIV > 0 ? NIV : 1];
+};
+
+template <typename Key, int NIV>
+__device__ __forceinline__ void pass_one(PassCtx<Key, NIV>& c, Key key) {
+    int j = 0;
+    if (NIV > 0) {
+#pragma unroll
+        for (int g = 0; g < NIV; ++g) {
+            const unsigned int p = key >= c.lo_r[g] ? 1u : 0u;
+            c.ge[g] += p;
+            j += (int)p;
+        }
+    } else {
+        int a = 0, b = c.n_iv;                 // j = #(lo[g] <= key), lo sorted ascending
+        while (a < b) { const int mid = (a + b) >> 1; if (c.s_lo[mid] <= key) a = mid + 1; else b = mid; }
+        j = a;
+    }
+    const int g = j - 1;
+    if (g >= 0 && g < c.n_iv && key <= c.s_hi[g]) {
+        const Key off = key - c.s_lo[g];
+        if (c.s_mode[g] == IV_HIST) {
+            atomicAdd(&c.s_bins[g * SEL_BINS + (unsigned int)(off >> c.s_shift[g])], 1u);
+        } else {
+            unsigned int* slot = c.out_iv + (size_t)g * c.iv_slot;
+            const unsigned int idx = atomicAdd(slot, 1u);
+            if (idx < (unsigned int)SEL_CAND) reinterpret_cast<Key*>(slot + 2)[idx] = key;
+        }
+    }
+}
+
+template <typename Real, int NIV>
+__global__ void __launch_bounds__(256) select_pass_kernel(const Real* __restrict__ x, unsigned long long ld,
+                                                          unsigned long long n, const RowSel* __restrict__ states,
+                                                          unsigned int* __restrict__ out, size_t row_slot,
+                                                          size_t iv_slot, int n_iv_cap) {
+    using Key = typename KeyT<Real>::type;
+    extern __shared__ unsigned int s_bins[];
+    __shared__ Key s_lo[MAX_IV], s_hi[MAX_IV];
+    __shared__ int s_shift[MAX_IV], s_mode[MAX_IV];
+    const unsigned long long row = blockIdx.y;
+    const RowSel& st = states[row];
+    const int n_iv = st.n_iv;
+    if (n_iv == 0) return;                                   // every target of this row is decided
+    const int tid = threadIdx.x;
+    if (tid < n_iv) {
+        s_lo[tid] = (Key)st.lo[tid]; s_hi[tid] = (Key)st.hi[tid];
+        s_shift[tid] = st.shift[tid]; s_mode[tid] = st.mode[tid];
+    }
+    for (int i = tid; i < n_iv * SEL_BINS; i += 256) s_bins[i] = 0u;
+    __syncthreads();
+
+    unsigned int* out_row = out + row * row_slot;
+    PassCtx<Key, NIV> c;
+    c.s_lo = s_lo; c.s_hi = s_hi; c.s_shift = s_shift; c.s_mode = s_mode; c.s_bins = s_bins;
+    c.out_iv = out_row + 2 * (size_t)n_iv_cap; c.iv_slot = iv_slot; c.n_iv = n_iv;
+    if (NIV > 0) {
+#pragma unroll
+        for (int g = 0; g < (NIV > 0 ? NIV : 1); ++g) { c.lo_r[g] = g < n_iv ? s_lo[g] : key_max<Key>(); c.ge[g] = 0u; }
+    }
+    const Real* xr = x + row * ld;
+    const unsigned long long per = (n + gridDim.x - 1) / gridDim.x;
+    const unsigned long long beg = (unsigned long long)blockIdx.x * per;
+    const unsigned long long end = beg + per < n ? beg + per : n;
+    unsigned long long i = beg + tid;
+    for (; i + (PASS_UNROLL - 1) * 256ull < end; i += PASS_UNROLL * 256ull) {
+        Real v[PASS_UNROLL];
+#pragma unroll
+        for (int u = 0; u < PASS_UNROLL; ++u) v[u] = xr[i + u * 256ull];
+#pragma unroll
+        for (int u = 0; u < PASS_UNROLL; ++u) pass_one<Key, NIV>(c, key_of(v[u]));
+    }
+    for (; i < end; i += 256ull) pass_one<Key, NIV>(c, key_of(xr[i]));
+
+    if (NIV > 0) {
+        unsigned long long* out_ge = reinterpret_cast<unsigned long long*>(out_row);
+#pragma unroll
+        for (int g = 0; g < (NIV > 0 ? NIV : 1); ++g) {
+            unsigned int v = c.ge[g];
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+            if ((tid & 31) == 0 && g < n_iv && v) atomicAdd(&out_ge[g], (unsigned long long)v);
+        }
+    }
+    __syncthreads();
+    for (int i2 = tid; i2 < n_iv * SEL_BINS; i2 += 256) {
+        const unsigned int cnt = s_bins[i2];
+        if (cnt) atomicAdd(&c.out_iv[(size_t)(i2 >> SEL_BIN_BITS) * iv_slot + 2 + (i2 & (SEL_BINS - 1))], cnt);
+    }
+}
+
+template <typename Real, int NIV>
+static cudaError_t launch_pass_t(const SelectProblem& sp, void* d_out, int n_iv_smem, dim3 grid, cudaStream_t stream) {
+    auto k = select_pass_kernel<Real, NIV>;
+    const size_t smem = (size_t)n_iv_smem * SEL_BINS * sizeof(unsigned int);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    k<<<grid, 256, smem, stream>>>(static_cast<const Real*>(sp.x), sp.ld, sp.n, sp.d_states,
+                                   static_cast<unsigned int*>(d_out), row_slot_u32(sp.dtype, sp.plan.n_targets),
+                                   iv_slot_u32(sp.dtype), sp.plan.n_targets);
+    return cudaGetLastError();
+}
+
+template <typename Real>
+static cudaError_t launch_pass_real(const SelectProblem& sp, bool first, void* d_out, dim3 grid, cudaStream_t s) {
+    const int np_ = sp.plan.n_pcts;
+    if (!first) return launch_pass_t<Real, 0>(sp, d_out, sp.plan.n_targets, grid, s);
+    if (np_ <= 5) return launch_pass_t<Real, 5>(sp, d_out, np_, grid, s);
+    if (np_ <= 9) return launch_pass_t<Real, 9>(sp, d_out, np_, grid, s);
+    return launch_pass_t<Real, 16>(sp, d_out, np_, grid, s);
+}
+
+cudaError_t launch_select_pass(const SelectProblem& sp, bool first_pass, void* d_out, int sm_count,
+                               cudaStream_t stream) {
+    if (sp.plan.n_targets == 0 || sp.rows == 0) return cudaSuccess;
+    if (sp.rows > 65535) return cudaErrorInvalidValue;
+    cudaError_t e = cudaMemsetAsync(d_out, 0, pass_words(sp) * sizeof(unsigned long long), stream);
+    if (e != cudaSuccess || sp.n == 0) return e;
+    unsigned long long chunks = ((unsigned long long)sm_count * 16 + sp.rows - 1) / sp.rows;
+    const unsigned long long max_chunks = (sp.n + 256ull * PASS_UNROLL - 1) / (256ull * PASS_UNROLL);
+    if (chunks > max_chunks) chunks = max_chunks;
+    if (chunks < 1) chunks = 1;
+    dim3 grid((unsigned)chunks, (unsigned)sp.rows);
+    return sp.dtype == MC_F64 ? launch_pass_real<double>(sp, first_pass, d_out, grid, stream)
+                              : launch_pass_real<float>(sp, first_pass, d_out, grid, stream);
+}
+
+// ------------------------------------------------------------------ scan: shrink every target's interval
+// One block of 1024 threads per row.  Intervals are visited in key order; a histogrammed
+// interval is prefix-summed over its 1024 bins (summed over ranks), a collected one is
+// sorted.  Each target then moves to the bin that holds its rank, is decided outright
+// (single-key bin, or position in the sorted candidates), or -- when its bracket missed --
+// moves to the gap beside the interval, whose population below is known exactly.
+constexpr int SCAN_THREADS = 1024;
+constexpr unsigned long long POP_UNKNOWN = ~0ull;
+
+template <typename Key>
+__global__ void __launch_bounds__(SCAN_THREADS) select_scan_kernel(const SelectPlan* __restrict__ plan,
+                                                                   const unsigned int* __restrict__ g,
+                                                                   unsigned int n_ranks, size_t rank_stride_u32,
+                                                                   size_t row_slot, size_t iv_slot, int n_iv_cap,
+                                                                   RowSel* __restrict__ states,
+                                                                   unsigned int* __restrict__ pending) {
+    __shared__ unsigned long long s_cum[SEL_BINS];
+    __shared__ unsigned long long s_keys[SEL_CAND];
+    __shared__ unsigned long long s_warp[SCAN_THREADS / 32];
+    __shared__ unsigned long long s_total[MAX_IV];
+    __shared__ unsigned long long s_nlo[MAX_TARGETS], s_nhi[MAX_TARGETS], s_nbelow[MAX_TARGETS], s_npop[MAX_TARGETS];
+    __shared__ int s_ndone[MAX_TARGETS];
+    __shared__ RowSel s_st, s_new;
+    const unsigned long long row = blockIdx.x;
+    if (states[row].n_iv == 0) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        const unsigned int* src = reinterpret_cast<const unsigned int*>(&states[row]);
+        unsigned int* dst = reinterpret_cast<unsigned int*>(&s_st);
+        for (int i = tid; i < (int)(sizeof(RowSel) / 4); i += SCAN_THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
+    const int nt = plan->n_targets, n_iv = s_st.n_iv;
+    const unsigned int* grow = g + row * row_slot;
+    if (!s_st.below_known && tid < n_iv) {
+        unsigned long long ge = 0;
+        for (unsigned int r = 0; r < n_ranks; ++r)
+            ge += reinterpret_cast<const unsigned long long*>(grow + r * rank_stride_u32)[tid];
+        s_st.below[tid] = plan->n_global - ge;
+    }
+    __syncthreads();
+
+    for (int gi = 0; gi < n_iv; ++gi) {
+        const int mode = s_st.mode[gi];
+        const unsigned int* slot0 = grow + 2 * (size_t)n_iv_cap + (size_t)gi * iv_slot;
+        unsigned long long total;
+        if (mode == IV_HIST) {
+            unsigned long long c = 0;
+            for (unsigned int r = 0; r < n_ranks; ++r) c += slot0[r * rank_stride_u32 + 2 + tid];
+            unsigned long long incl = c;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += o;
+            }
+            if (lane == 31) s_warp[warp] = incl;
+            __syncthreads();
+            unsigned long long off = 0;
+            for (int w = 0; w < warp; ++w) off += s_warp[w];
+            s_cum[tid] = off + incl;
+            __syncthreads();
+            total = s_cum[SEL_BINS - 1];
+        } else {
+            unsigned int base = 0, cnt_all = 0;
+            for (unsigned int r = 0; r < n_ranks; ++r) {
+                const unsigned int* slot = slot0 + r * rank_stride_u32;
+                unsigned int cr = slot[0];
+                if (cr > (unsigned int)SEL_CAND) cr = SEL_CAND;
+                if ((unsigned int)tid < cr && base + tid < (unsigned int)SEL_CAND)
+                    s_keys[base + tid] = (unsigned long long)reinterpret_cast<const Key*>(slot + 2)[tid];
+                base += cr;
+            }
+            cnt_all = base < (unsigned int)SEL_CAND ? base : SEL_CAND;
+            int P = 1;
+            while (P < (int)cnt_all) P <<= 1;
+            if (tid >= (int)cnt_all && tid < P) s_keys[tid] = ~0ull;
+            __syncthreads();
+            for (int k = 2; k <= P; k <<= 1) {
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    const int ixj = tid ^ j;
+                    if (tid < P && ixj > tid) {
+                        const unsigned long long a = s_keys[tid], b = s_keys[ixj];
+                        const bool up = (tid & k) == 0;
+                        if ((a > b) == up) { s_keys[tid] = b; s_keys[ixj] = a; }
+                    }
+                    __syncthreads();
+                }
+            }
+            total = cnt_all;
+        }
+        if (tid == 0) s_total[gi] = total;
+        if (tid < nt && s_st.target_iv[tid] == gi) {
+            const unsigned long long rank = plan->rank[tid], below = s_st.below[gi];
+            const unsigned long long lo = s_st.lo[gi], hi = s_st.hi[gi];
+            s_ndone[tid] = 0;
+            s_npop[tid] = POP_UNKNOWN;
+            if (rank < below) {                      // bracket missed: the value lies in the gap below
+                const bool first = gi == 0;
+                s_nlo[tid] = first ? 0ull : s_st.hi[gi - 1] + 1ull;
+                s_nhi[tid] = lo - 1ull;
+                s_nbelow[tid] = first ? 0ull : s_st.below[gi - 1] + s_total[gi - 1];
+            } else if (rank - below >= total) {      // ... in the gap above
+                s_nlo[tid] = hi + 1ull;
+                s_nhi[tid] = gi + 1 < n_iv ? s_st.lo[gi + 1] - 1ull : (unsigned long long)key_max<Key>();
+                s_nbelow[tid] = below + total;
+            } else if (mode == IV_HIST) {
+                const unsigned long long r = rank - below;
+                int a = 0, b = SEL_BINS - 1;          // first bin with cum > r
+                while (a < b) { const int mid = (a + b) >> 1; if (s_cum[mid] > r) b = mid; else a = mid + 1; }
+                const int sh = s_st.shift[gi];
+                const unsigned long long before = a ? s_cum[a - 1] : 0ull;
+                const unsigned long long nlo = lo + ((unsigned long long)a << sh);
+                const unsigned long long span = (1ull << sh) - 1ull;
+                s_nlo[tid] = nlo;
+                s_nhi[tid] = (hi - nlo < span) ? hi : nlo + span;
+                s_nbelow[tid] = below + before;
+                s_npop[tid] = s_cum[a] - before;
+                s_ndone[tid] = s_nlo[tid] == s_nhi[tid];
+            } else {
+                s_nlo[tid] = s_nhi[tid] = s_keys[rank - below];
+                s_ndone[tid] = 1;
+            }
+        }
+        __syncthreads();
+    }
+
+    if (tid == 0) {
+        int n_new = 0;
+        for (int j = 0; j < nt; ++j) {
+            s_new.key[j] = s_st.key[j];
+            if (s_st.target_iv[j] < 0) { s_new.target_iv[j] = -1; continue; }
+            if (s_ndone[j]) { s_new.key[j] = s_nlo[j]; s_new.target_iv[j] = -1; continue; }
+            if (!(n_new && s_new.lo[n_new - 1] == s_nlo[j] && s_new.hi[n_new - 1] == s_nhi[j])) {
+                s_new.lo[n_new] = s_nlo[j]; s_new.hi[n_new] = s_nhi[j]; s_new.below[n_new] = s_nbelow[j];
+                s_new.shift[n_new] = max(0, bit_length(s_nhi[j] - s_nlo[j]) - SEL_BIN_BITS);
+                s_new.mode[n_new] = s_npop[j] <= (unsigned long long)SEL_CAND ? IV_COLLECT : IV_HIST;
+                ++n_new;
+            }
+            s_new.target_iv[j] = n_new - 1;
+        }
+        s_new.n_iv = n_new;
+        s_new.below_known = 1;
+        if (n_new) atomicAdd(pending, 1u);
+    }
+    __syncthreads();
+    {
+        const unsigned int* src = reinterpret_cast<const unsigned int*>(&s_new);
+        unsigned int* dst = reinterpret_cast<unsigned int*>(&states[row]);
+        for (int i = tid; i < (int)(sizeof(RowSel) / 4); i += SCAN_THREADS) dst[i] = src[i];
+    }
+}
+
+cudaError_t launch_select_scan(const SelectProblem& sp, const void* d_gathered_pass, unsigned int n_ranks,
+                               size_t rank_stride_words, unsigned int* d_pending, cudaStream_t stream) {
+    if (sp.plan.n_targets == 0 || sp.rows == 0) return cudaSuccess;
+    const unsigned int* g = static_cast<const unsigned int*>(d_gathered_pass);
+    const size_t rs = row_slot_u32(sp.dtype, sp.plan.n_targets), is = iv_slot_u32(sp.dtype);
+    if (sp.dtype == MC_F64)
+        select_scan_kernel<uint64_t><<<(unsigned)sp.rows, SCAN_THREADS, 0, stream>>>(
+            sp.d_plan, g, n_ranks, rank_stride_words * 2, rs, is, sp.plan.n_targets, sp.d_states, d_pending);
+    else
+        select_scan_kernel<uint32_t><<<(unsigned)sp.rows, SCAN_THREADS, 0, stream>>>(
+            sp.d_plan, g, n_ranks, rank_stride_words * 2, rs, is, sp.plan.n_targets, sp.d_states, d_pending);
     return cudaGetLastError();
 }
 
@@ -270,7 +568,7 @@ __device__ __forceinline__ double numpy_lerp(double a, double b, double t) {
     return r;
 }
 
-__global__ void select_finish_kernel(const SelectPlan* __restrict__ plan, const RowState* __restrict__ states,
+__global__ void select_finish_kernel(const SelectPlan* __restrict__ plan, const RowSel* __restrict__ states,
                                      unsigned long long rows, double* __restrict__ out, double* __restrict__ out_lo,
                                      double* __restrict__ out_hi) {
     const unsigned long long idx = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -278,8 +576,8 @@ __global__ void select_finish_kernel(const SelectPlan* __restrict__ plan, const 
     if (idx >= rows * (unsigned long long)np_) return;
     const unsigned long long row = idx / np_;
     const int k = (int)(idx % np_);
-    const RowState& st = states[row];
-    const unsigned long long ka = st.prefix[plan->pct_lo_idx[k]], kb = st.prefix[plan->pct_hi_idx[k]];
+    const RowSel& st = states[row];
+    const unsigned long long ka = st.key[plan->pct_lo_idx[k]], kb = st.key[plan->pct_hi_idx[k]];
     double a, b;
     if (plan->key_bits == 32) { a = (double)value_of((uint32_t)ka); b = (double)value_of((uint32_t)kb); }
     else { a = value_of((uint64_t)ka); b = value_of((uint64_t)kb); }
@@ -349,32 +647,90 @@ cudaError_t launch_publish_percentiles(const double* d_pct, const double* d_lo, 
     return cudaGetLastError();
 }
 
-// ------------------------------------------------------------------ tail: mean(final[final <= p]) (app.py:656)
+// ------------------------------------------------------------------ closing pass over the terminal values
+// tail: mean(final[final <= p]) (app.py:656) and the fixed-bin histogram in ONE read.
+// Histogram semantics: np.histogram(x.astype(float64), bins, range=(lo, hi)) -- numpy/lib/_histograms_impl.py
+// uniform-bin path: values outside [lo, hi] dropped; the bin is the one whose edges (np.linspace(lo, hi,
+// bins+1)) bracket the value, last bin closed on the right.  For fp32 data every comparison "v < edge" with a
+// float64 edge is done exactly in fp32 against ceil_f32(edge), so the kernel needs no fp64 arithmetic.
+__global__ void hist_edges_kernel(unsigned int bins, double lo, double hi, DeviceResult* res, double* edges,
+                                  float* edges_f) {
+    if (lo >= hi) { lo = res->vmin; hi = res->vmax; }       // range=None: (a.min(), a.max())
+    if (lo == hi) { lo -= 0.5; hi += 0.5; }                 // _get_outer_edges
+    if (blockIdx.x == 0 && threadIdx.x == 0) { res->hist_lo = lo; res->hist_hi = hi; }
+    const double step = __ddiv_rn(__dsub_rn(hi, lo), (double)bins);      // np.linspace
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i <= bins; i += gridDim.x * blockDim.x) {
+        const double e = (i == bins) ? hi : __dadd_rn(__dmul_rn((double)i, step), lo);
+        edges[i] = e;
+        float f = (float)e;
+        if (i == bins) { if ((double)f > e) f = nextafterf(f, -INFINITY); }   // v <= hi  <=>  v <= floor_f32(hi)
+        else if ((double)f < e) f = nextafterf(f, INFINITY);                  // v <  e   <=>  v <  ceil_f32(e)
+        edges_f[i] = f;
+    }
+}
+
+template <typename Real> struct EdgeSrc;
+template <> struct EdgeSrc<float> { static __device__ const float* get(const double*, const float* f) { return f; } };
+template <> struct EdgeSrc<double> { static __device__ const double* get(const double* d, const float*) { return d; } };
+
 template <typename Real>
-__global__ void __launch_bounds__(256) tail_kernel(const Real* __restrict__ x, unsigned long long n,
-                                                   const DeviceResult* __restrict__ res, double* __restrict__ scratch) {
+__global__ void __launch_bounds__(256) tail_hist_kernel(const Real* __restrict__ x, unsigned long long n,
+                                                        const DeviceResult* __restrict__ res, int want_tail,
+                                                        unsigned int bins, const double* __restrict__ edges,
+                                                        const float* __restrict__ edges_f,
+                                                        double* __restrict__ scratch,
+                                                        unsigned long long* __restrict__ counts) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double s_sum[8];
     __shared__ unsigned long long s_cnt[8];
-    const double thr = res->tail_threshold;
+    Real* s_edge = reinterpret_cast<Real*>(smem_raw);                               // [bins + 1]
+    unsigned int* s_counts = reinterpret_cast<unsigned int*>(s_edge + (bins ? bins + 2 : 0));   // [bins]
+    const Real* esrc = EdgeSrc<Real>::get(edges, edges_f);
+    for (unsigned int i = threadIdx.x; i < bins; i += blockDim.x) s_counts[i] = 0u;
+    for (unsigned int i = threadIdx.x; bins && i <= bins; i += blockDim.x) s_edge[i] = esrc[i];
+    __syncthreads();
+    // v <= thr (a double) for a float v  <=>  v <= floor_f32(thr)
+    Real thr = (Real)(-INFINITY);
+    if (want_tail) {
+        const double t = res->tail_threshold;
+        thr = (Real)t;
+        if ((double)thr > t) thr = sizeof(Real) == 4 ? (Real)nextafterf((float)thr, -INFINITY) : thr;
+    }
+    Real lo = Real(0), top = Real(0), inv_w = Real(0);
+    if (bins) { lo = s_edge[0]; top = s_edge[bins]; inv_w = (Real)bins / (top - lo); }
+    const int last = (int)bins - 1;
     double sum = 0.0;
     unsigned long long cnt = 0;
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const double v = (double)x[i];
-        if (v <= thr) { sum += v; ++cnt; }
+        const Real v = x[i];
+        if (v <= thr) { sum += (double)v; ++cnt; }
+        if (bins && v >= lo && v <= top) {
+            int idx = (int)((v - lo) * inv_w);
+            idx = idx < 0 ? 0 : (idx > last ? last : idx);
+            while (idx > 0 && v < s_edge[idx]) --idx;
+            while (idx < last && v >= s_edge[idx + 1]) ++idx;
+            atomicAdd(&s_counts[idx], 1u);
+        }
     }
+    if (want_tail) {
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) {
-        sum += __shfl_down_sync(0xffffffffu, sum, d);
-        cnt += __shfl_down_sync(0xffffffffu, cnt, d);
+        for (int d = 16; d > 0; d >>= 1) {
+            sum += __shfl_down_sync(0xffffffffu, sum, d);
+            cnt += __shfl_down_sync(0xffffffffu, cnt, d);
+        }
+        if ((threadIdx.x & 31) == 0) { s_sum[threadIdx.x >> 5] = sum; s_cnt[threadIdx.x >> 5] = cnt; }
     }
-    if ((threadIdx.x & 31) == 0) { s_sum[threadIdx.x >> 5] = sum; s_cnt[threadIdx.x >> 5] = cnt; }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (want_tail && threadIdx.x == 0) {
         double ts = 0.0; unsigned long long tc = 0;
         for (int w = 0; w < 8; ++w) { ts += s_sum[w]; tc += s_cnt[w]; }
         scratch[2 * blockIdx.x] = ts;
         scratch[2 * blockIdx.x + 1] = __longlong_as_double((long long)tc);
+    }
+    for (unsigned int i = threadIdx.x; i < bins; i += blockDim.x) {
+        const unsigned int c = s_counts[i];
+        if (c) atomicAdd(&counts[i], (unsigned long long)c);
     }
 }
 
@@ -395,82 +751,40 @@ __global__ void __launch_bounds__(256) tail_reduce_kernel(const double* scratch,
     if (threadIdx.x == 0) { words[0] = s_cnt[0]; words[1] = (unsigned long long)__double_as_longlong(s_sum[0]); }
 }
 
-cudaError_t launch_tail(const void* x, int dtype, unsigned long long n, const DeviceResult* d_res, double* d_scratch,
-                        unsigned long long* d_words, int sm_count, cudaStream_t stream) {
+cudaError_t launch_tail_hist(const void* x, int dtype, unsigned long long n, bool want_tail, unsigned int bins,
+                             double lo, double hi, DeviceResult* d_res, double* d_edges, double* d_scratch,
+                             unsigned long long* d_words, int sm_count, cudaStream_t stream) {
+    cudaError_t e = cudaMemsetAsync(d_words, 0, (2 + (size_t)bins) * sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    float* d_edges_f = reinterpret_cast<float*>(d_edges + bins + 1);
+    if (bins) {
+        hist_edges_kernel<<<(bins + 256) / 256, 256, 0, stream>>>(bins, lo, hi, d_res, d_edges, d_edges_f);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
+    if (n == 0 || (!want_tail && !bins)) return cudaSuccess;
     unsigned long long blocks = (n + 256ull * 8 - 1) / (256ull * 8);
     if (blocks < 1) blocks = 1;
     if (blocks > 1024) blocks = 1024;
     if (blocks > (unsigned long long)sm_count * 6) blocks = (unsigned long long)sm_count * 6;
-    if (dtype == MC_F64) tail_kernel<double><<<(unsigned)blocks, 256, 0, stream>>>(static_cast<const double*>(x), n, d_res, d_scratch);
-    else tail_kernel<float><<<(unsigned)blocks, 256, 0, stream>>>(static_cast<const float*>(x), n, d_res, d_scratch);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    tail_reduce_kernel<<<1, 256, 0, stream>>>(d_scratch, (int)blocks, d_words);
-    return cudaGetLastError();
-}
-
-// ------------------------------------------------------------------ fixed-bin histogram
-// Semantics: np.histogram(x.astype(float64), bins, range=(lo, hi)) -- numpy/lib/_histograms_impl.py
-// uniform-bin path: values outside [lo, hi] dropped; estimate the bin by scaling, then correct it
-// against edges = linspace(lo, hi, bins+1); last bin closed on the right.
-__global__ void hist_edges_kernel(unsigned int bins, double lo, double hi, DeviceResult* res, double* edges) {
-    if (lo >= hi) { lo = res->vmin; hi = res->vmax; }       // range=None: (a.min(), a.max())
-    if (lo == hi) { lo -= 0.5; hi += 0.5; }                 // _get_outer_edges
-    if (blockIdx.x == 0 && threadIdx.x == 0) { res->hist_lo = lo; res->hist_hi = hi; }
-    const double step = __ddiv_rn(__dsub_rn(hi, lo), (double)bins);      // np.linspace
-    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i <= bins; i += gridDim.x * blockDim.x)
-        edges[i] = (i == bins) ? hi : __dadd_rn(__dmul_rn((double)i, step), lo);
-}
-
-template <typename Real>
-__global__ void __launch_bounds__(256) value_hist_kernel(const Real* __restrict__ x, unsigned long long n,
-                                                         unsigned int bins, const double* __restrict__ edges,
-                                                         unsigned long long* __restrict__ counts) {
-    extern __shared__ unsigned int s_counts[];
-    for (unsigned int i = threadIdx.x; i < bins; i += blockDim.x) s_counts[i] = 0u;
-    __syncthreads();
-    const double lo = edges[0], hi = edges[bins];
-    const double denom = __dsub_rn(hi, lo);
-    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const double v = (double)x[i];
-        if (!(v >= lo && v <= hi)) continue;
-        const double f = __dmul_rn(__ddiv_rn(__dsub_rn(v, lo), denom), (double)bins);
-        long long idx = (long long)f;
-        if (idx >= (long long)bins) idx = bins - 1;
-        if (idx < 0) idx = 0;
-        if (v < edges[idx]) --idx;
-        else if (v >= edges[idx + 1] && idx != (long long)bins - 1) ++idx;
-        atomicAdd(&s_counts[idx], 1u);
-    }
-    __syncthreads();
-    for (unsigned int i = threadIdx.x; i < bins; i += blockDim.x) {
-        const unsigned int c = s_counts[i];
-        if (c) atomicAdd(&counts[i], (unsigned long long)c);
-    }
-}
-
-cudaError_t launch_value_hist(const void* x, int dtype, unsigned long long n, unsigned int bins, double lo, double hi,
-                              DeviceResult* d_res, double* d_edges, unsigned long long* d_counts, int sm_count,
-                              cudaStream_t stream) {
-    cudaError_t e = cudaMemsetAsync(d_counts, 0, (size_t)bins * sizeof(unsigned long long), stream);
-    if (e != cudaSuccess) return e;
-    hist_edges_kernel<<<(bins + 256) / 256, 256, 0, stream>>>(bins, lo, hi, d_res, d_edges);
-    e = cudaGetLastError();
-    if (e != cudaSuccess || n == 0) return e;
-    unsigned long long blocks = (n + 256ull * 8 - 1) / (256ull * 8);
-    if (blocks > (unsigned long long)sm_count * 8) blocks = (unsigned long long)sm_count * 8;
-    const size_t smem = (size_t)bins * sizeof(unsigned int);
+    const size_t esz = dtype == MC_F64 ? 8 : 4;
+    const size_t smem = bins ? ((size_t)bins + 2) * esz + (size_t)bins * 4 : 0;
     if (dtype == MC_F64) {
-        auto k = value_hist_kernel<double>;
+        auto k = tail_hist_kernel<double>;
         if (smem > 48 * 1024 && (e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
-        k<<<(unsigned)blocks, 256, smem, stream>>>(static_cast<const double*>(x), n, bins, d_edges, d_counts);
+        k<<<(unsigned)blocks, 256, smem, stream>>>(static_cast<const double*>(x), n, d_res, want_tail ? 1 : 0, bins,
+                                                   d_edges, d_edges_f, d_scratch, d_words + 2);
     } else {
-        auto k = value_hist_kernel<float>;
+        auto k = tail_hist_kernel<float>;
         if (smem > 48 * 1024 && (e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
-        k<<<(unsigned)blocks, 256, smem, stream>>>(static_cast<const float*>(x), n, bins, d_edges, d_counts);
+        k<<<(unsigned)blocks, 256, smem, stream>>>(static_cast<const float*>(x), n, d_res, want_tail ? 1 : 0, bins,
+                                                   d_edges, d_edges_f, d_scratch, d_words + 2);
     }
-    return cudaGetLastError();
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (want_tail) {
+        tail_reduce_kernel<<<1, 256, 0, stream>>>(d_scratch, (int)blocks, d_words);
+        e = cudaGetLastError();
+    }
+    return e;
 }
 
 // ------------------------------------------------------------------ final merge over ranks

@@ -11,9 +11,12 @@ struct SelectProblem {
     const void* x;
     int dtype;
     unsigned long long rows, n, ld;
+    unsigned int m_slot;      // pilot-sample slots per row in this rank's stage-0 buffer
+    unsigned int m_local;     // pilot samples this rank contributes per row (<= m_slot, <= n)
+    int sample_contiguous;    // 1: first m_local values of the row (iid columns), 0: strided
     SelectPlan plan;          // host copy
     SelectPlan* d_plan;       // device copy
-    RowState* d_states;       // [rows]
+    RowSel* d_states;         // [rows]
 };
 
 // Build the plan for np.percentile(method='linear') over n_global values.
@@ -21,18 +24,36 @@ struct SelectProblem {
 bool build_select_plan(const double* pcts, int n_pcts, unsigned long long n_global, int dtype,
                        SelectPlan* plan);
 
-inline size_t hist_words_pass0(unsigned long long rows) { return (size_t)rows * DIGIT0_BINS / 2; }
-inline size_t hist_words_pass(unsigned long long rows, int n_targets) {
-    return (size_t)rows * n_targets * DIGIT_BINS / 2;
+// ---- stage buffer geometry (uint32 units unless noted) ------------------------------
+inline int key_units(int dtype) { return dtype == MC_F64 ? 2 : 1; }                  // uint32 per key
+inline size_t iv_slot_u32(int dtype) { return 2 + (size_t)SEL_CAND * key_units(dtype); }
+inline size_t row_slot_u32(int dtype, int n_targets) {                                // per row, per pass
+    return (size_t)n_targets * (2 + iv_slot_u32(dtype));
 }
+inline size_t pass_words(const SelectProblem& sp) {                                   // 8-byte words
+    return (size_t)sp.rows * row_slot_u32(sp.dtype, sp.plan.n_targets) / 2;
+}
+inline size_t sample_words(const SelectProblem& sp) {                                 // 8-byte words
+    return ((size_t)sp.rows * sp.m_slot * key_units(sp.dtype) + 1) / 2;
+}
+// pilot-sample slots per row for one rank of n_ranks
+unsigned int sample_slot(int dtype, unsigned int n_ranks);
 
-// pass-p digit histogram of the rows' local values into d_hist (uint32, zeroed by callee)
-cudaError_t launch_select_hist(const SelectProblem& sp, int pass, unsigned int* d_hist, int sm_count,
+// copy this rank's pilot sample (as keys) into its stage-0 buffer
+cudaError_t launch_select_sample(const SelectProblem& sp, void* d_sample_out, cudaStream_t stream);
+// sort the pilot samples of all ranks (rank r's block at d_samples + r*rank_stride_words) and
+// derive the starting intervals of every row; m_local of rank r is header word `hdr_word`
+cudaError_t launch_select_brackets(const SelectProblem& sp, const unsigned long long* d_gathered,
+                                   size_t sample_off_words, int hdr_word, unsigned int n_ranks,
+                                   size_t rank_stride_words, int max_smem_optin, cudaStream_t stream);
+// one narrowing pass over the local values: per row and interval, counts / histogram /
+// collected candidates into d_out (layout row_slot_u32; zeroed by the callee)
+cudaError_t launch_select_pass(const SelectProblem& sp, bool first_pass, void* d_out, int sm_count,
                                cudaStream_t stream);
-// consume the pass-p histograms of all ranks (rank r at d_hist + r*rank_stride_u32) and
-// narrow every target by one digit
-cudaError_t launch_select_scan(const SelectProblem& sp, int pass, const unsigned int* d_hist,
-                               unsigned int n_ranks, size_t rank_stride_u32, cudaStream_t stream);
+// merge the pass output of all ranks and shrink every target's interval; adds the number of
+// rows that still have undecided targets to *d_pending
+cudaError_t launch_select_scan(const SelectProblem& sp, const void* d_gathered_pass, unsigned int n_ranks,
+                               size_t rank_stride_words, unsigned int* d_pending, cudaStream_t stream);
 // keys -> values, np.percentile's _lerp; d_out[rows][n_pcts] (and lo/hi order statistics if non-null)
 cudaError_t launch_select_finish(const SelectProblem& sp, double* d_out, double* d_lo, double* d_hi,
                                  cudaStream_t stream);
@@ -45,15 +66,13 @@ cudaError_t launch_merge_moments(const unsigned long long* d_gathered, unsigned 
 cudaError_t launch_publish_percentiles(const double* d_pct, const double* d_lo, const double* d_hi,
                                        int n_pcts, int tail_idx, DeviceResult* d_res, cudaStream_t stream);
 
-// count and sum of x <= res->tail_threshold -> words[0..1] (count, sum bits); deterministic
-cudaError_t launch_tail(const void* x, int dtype, unsigned long long n, const DeviceResult* d_res,
-                        double* d_block_scratch /*[2*1024]*/, unsigned long long* d_words, int sm_count,
-                        cudaStream_t stream);
-// np.histogram(x, bins, range): edges from (lo,hi) or, if lo >= hi, from res->(vmin, vmax)
-cudaError_t launch_value_hist(const void* x, int dtype, unsigned long long n, unsigned int bins, double lo,
-                              double hi, DeviceResult* d_res, double* d_edges /*[bins+1]*/,
-                              unsigned long long* d_counts /*[bins], zeroed by callee*/, int sm_count,
-                              cudaStream_t stream);
+// ONE pass over the terminal values for both closing reductions: count and sum of
+// x <= res->tail_threshold -> words[0..1] (deterministic), and np.histogram(x, bins, range)
+// -> words[2..2+bins).  Edges from (lo,hi) or, if lo >= hi, from res->(vmin, vmax).
+cudaError_t launch_tail_hist(const void* x, int dtype, unsigned long long n, bool want_tail, unsigned int bins,
+                             double lo, double hi, DeviceResult* d_res, double* d_edges /*[bins+1]*/,
+                             double* d_block_scratch /*[2*1024]*/, unsigned long long* d_words, int sm_count,
+                             cudaStream_t stream);
 // final merge: tail (count,sum) and histogram over ranks
 cudaError_t launch_merge_final(const unsigned long long* d_gathered, unsigned int n_ranks,
                                size_t rank_stride_words, unsigned int bins, DeviceResult* d_res,

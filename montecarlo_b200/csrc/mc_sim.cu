@@ -9,9 +9,7 @@
 // case each step adds one coalesced store per path.
 //
 // The terminal reductions of app.py:636-656 start here too: each thread
-// accumulates moments about s0 in fp64, and the first radix digit of the terminal
-// value's order-preserving key is histogrammed in shared memory so the later
-// exact percentile selection (mc_select.cu) does not need a pass of its own.
+// accumulates moments about s0 in fp64 (one partial per block, reduced in fixed order).
 //
 // Units: the fp32 kernels accumulate the log-price in log2 units (the host
 // pre-multiplies drift, omega and var0 by log2(e) or its square; GARCH is
@@ -35,7 +33,6 @@ struct SimArgs {
     Real s0, var0, omega, alpha, beta, drift;   // kernel units
     double center;
     BlockPartial* partials;
-    unsigned int* hist0;
 };
 
 __device__ __forceinline__ float exp_units(float y) { return fast_ex2(y); }
@@ -98,8 +95,7 @@ __device__ __forceinline__ BlockPartial empty_partial() {
 }
 
 template <typename Real>
-__device__ __forceinline__ void account(BlockPartial& acc, unsigned int* s_hist, Real value, Real s0,
-                                        double center) {
+__device__ __forceinline__ void account(BlockPartial& acc, Real value, double center) {
     const double d = (double)value - center;
     acc.sum_d += d;
     acc.sum_d2 = fma(d, d, acc.sum_d2);
@@ -107,19 +103,11 @@ __device__ __forceinline__ void account(BlockPartial& acc, unsigned int* s_hist,
     acc.vmax = fmax(acc.vmax, (double)value);
     acc.n += 1;
     acc.n_above += ((double)value > center) ? 1ull : 0ull;       // app.py:654 (compared in fp64)
-    const auto key = key_of(value);
-    atomicAdd(&s_hist[(unsigned int)(key >> (KeyT<Real>::bits - DIGIT0_BITS))], 1u);
 }
 
-__device__ __forceinline__ void finish_block(BlockPartial acc, unsigned int* s_hist, BlockPartial* s_warp,
-                                             BlockPartial* partials, unsigned int* hist0) {
+__device__ __forceinline__ void finish_block(BlockPartial acc, BlockPartial* s_warp, BlockPartial* partials) {
     acc = block_reduce(acc, s_warp);
     if (threadIdx.x == 0) partials[blockIdx.x] = acc;
-    __syncthreads();
-    for (int i = threadIdx.x; i < DIGIT0_BINS; i += blockDim.x) {
-        const unsigned int c = s_hist[i];
-        if (c) atomicAdd(&hist0[i], c);
-    }
 }
 
 // ------------------------------------------------------------------ shock sources
@@ -177,12 +165,10 @@ __device__ __forceinline__ void step(const SimArgs<Real>& a, Real z, Real sig, R
 template <typename Real, int SHOCK, int VAR, bool STORE, int MAXB>
 __global__ void __launch_bounds__(MAXB) sim_kernel(const __grid_constant__ SimArgs<Real> a) {
     extern __shared__ __align__(16) unsigned char smem_dyn[];
-    __shared__ unsigned int s_hist[DIGIT0_BINS];
     __shared__ BlockPartial s_warp[32];
     Real* s_pool = reinterpret_cast<Real*>(smem_dyn);
     constexpr int K = ShocksPerCall<Real, SHOCK>::value;
 
-    for (int i = threadIdx.x; i < DIGIT0_BINS; i += blockDim.x) s_hist[i] = 0u;
     if (SHOCK == MC_SHOCK_BOOTSTRAP && a.pool_log2_copies >= 0) {
         const uint32_t total = a.pool_len << a.pool_log2_copies;
         for (uint32_t i = threadIdx.x; i < total; i += blockDim.x) s_pool[i] = a.pool[i >> a.pool_log2_copies];
@@ -242,9 +228,9 @@ __global__ void __launch_bounds__(MAXB) sim_kernel(const __grid_constant__ SimAr
         }
         const Real final_price = a.s0 * exp_units(fma_units((Real)a.n_steps, a.drift, y));
         a.terminal[i] = final_price;                               // app.py:636
-        account<Real>(acc, s_hist, final_price, a.s0, a.center);
+        account<Real>(acc, final_price, a.center);
     }
-    finish_block(acc, s_hist, s_warp, a.partials, a.hist0);
+    finish_block(acc, s_warp, a.partials);
 }
 
 // ------------------------------------------------------------------ correlated portfolio
@@ -264,7 +250,6 @@ struct PortArgs {
     Real v0;                          // portfolio value at t=0
     double center;
     BlockPartial* partials;
-    unsigned int* hist0;
     Real chol[D * (D + 1) / 2];       // packed lower triangle, row-major, kernel units
     Real drift[D];                    // per step, kernel units
     Real s0w[D];                      // w_i * S0_i
@@ -280,10 +265,7 @@ __device__ __forceinline__ Real portfolio_value(const PortArgs<Real, D>& a, cons
 
 template <typename Real, int D, bool INJECTED, bool STORE>
 __global__ void __launch_bounds__(SIM_BLOCK) portfolio_kernel(const __grid_constant__ PortArgs<Real, D> a) {
-    __shared__ unsigned int s_hist[DIGIT0_BINS];
     __shared__ BlockPartial s_warp[32];
-    for (int i = threadIdx.x; i < DIGIT0_BINS; i += blockDim.x) s_hist[i] = 0u;
-    __syncthreads();
 
     BlockPartial acc = empty_partial();
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
@@ -332,9 +314,9 @@ __global__ void __launch_bounds__(SIM_BLOCK) portfolio_kernel(const __grid_const
         }
         const Real v_final = portfolio_value<Real, D>(a, x, (Real)a.n_steps);
         a.terminal[i] = v_final;
-        account<Real>(acc, s_hist, v_final, a.v0, a.center);
+        account<Real>(acc, v_final, a.center);
     }
-    finish_block(acc, s_hist, s_warp, a.partials, a.hist0);
+    finish_block(acc, s_warp, a.partials);
 }
 
 // ------------------------------------------------------------------ debug / test kernels
@@ -365,7 +347,8 @@ __global__ void debug_philox_kernel(const uint32_t* ctr, uint32_t n, uint32_t k0
 
 // per-block partials -> stage-0 header; one block, fixed summation order => deterministic
 __global__ void __launch_bounds__(256) reduce_partials_kernel(const BlockPartial* partials, int n,
-                                                              unsigned long long* words) {
+                                                              unsigned long long* words, unsigned long long w6,
+                                                              unsigned long long w7) {
     __shared__ BlockPartial s[256];
     BlockPartial acc = empty_partial();
     for (int i = threadIdx.x; i < n; i += 256) combine(acc, partials[i]);
@@ -382,6 +365,8 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const BlockPartial
         words[3] = (unsigned long long)__double_as_longlong(s[0].sum_d2);
         words[4] = (unsigned long long)__double_as_longlong(s[0].vmin);
         words[5] = (unsigned long long)__double_as_longlong(s[0].vmax);
+        words[6] = w6;       // pilot samples this rank contributes per row: terminal / fan-chart problem
+        words[7] = w7;
     }
 }
 
@@ -414,7 +399,6 @@ static SimArgs<Real> make_args(const mc_params& p, const SimBuffers& b) {
     a.drift = (Real)(p.drift * u);
     a.center = p.s0;
     a.partials = b.d_partials;
-    a.hist0 = b.d_hist0;
     return a;
 }
 
@@ -456,8 +440,8 @@ static cudaError_t launch_single(const mc_params& p, const SimBuffers& b, const 
     size_t smem = 0;
     if (SHOCK == MC_SHOCK_BOOTSTRAP) {
         block = MAXB;
-        // static smem: 16 KB digit histogram + 1.5 KB warp partials
-        const size_t budget = (MAXB == 1024) ? (size_t)dev.max_smem_optin - 20 * 1024 : 40 * 1024;
+        // static smem: 1.5 KB warp partials
+        const size_t budget = (MAXB == 1024) ? (size_t)dev.max_smem_optin - 4 * 1024 : 40 * 1024;
         int lg = 5;
         while (lg >= 0 && ((size_t)p.pool_len << lg) * sizeof(Real) > budget) --lg;
         a.pool_log2_copies = lg;               // -1 => gather from global/L1
@@ -530,7 +514,6 @@ static cudaError_t launch_portfolio_impl(const mc_params& p, const mc_portfolio&
     a.v0 = (Real)v0;
     a.center = p.s0;
     a.partials = b.d_partials;
-    a.hist0 = b.d_hist0;
     auto kernel = portfolio_kernel<Real, D, INJECTED, STORE>;
     cudaError_t e = pick_grid(kernel, SIM_BLOCK, 0, dev, p.n_paths, grid);
     if (e != cudaSuccess) return e;
@@ -599,8 +582,8 @@ cudaError_t launch_debug_philox(const uint32_t* d_ctr, uint32_t n, uint32_t k0, 
 }
 
 cudaError_t launch_reduce_partials(const BlockPartial* d_partials, int n_partials, unsigned long long* d_words,
-                                   cudaStream_t stream) {
-    reduce_partials_kernel<<<1, 256, 0, stream>>>(d_partials, n_partials, d_words);
+                                   unsigned long long w6, unsigned long long w7, cudaStream_t stream) {
+    reduce_partials_kernel<<<1, 256, 0, stream>>>(d_partials, n_partials, d_words, w6, w7);
     return cudaGetLastError();
 }
 

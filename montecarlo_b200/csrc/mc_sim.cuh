@@ -10,7 +10,6 @@ struct SimBuffers {
     void* d_paths;
     void* d_terminal;
     BlockPartial* d_partials;     // [max_grid]
-    unsigned int* d_hist0;        // [DIGIT0_BINS], zeroed by the caller
 };
 
 constexpr int MAX_SIM_GRID = 1 << 16;     // per-block partials are reduced in fixed order afterwards
@@ -30,8 +29,10 @@ cudaError_t launch_debug_shocks(const mc_params& p, const void* d_pool, void* d_
 cudaError_t launch_debug_philox(const uint32_t* d_ctr, uint32_t n, uint32_t k0, uint32_t k1,
                                 uint32_t* d_out, cudaStream_t stream);
 
-// fixed-order reduction of the per-block partials into the stage-0 header words
+// fixed-order reduction of the per-block partials into the stage-0 header words [0..5];
+// header words [6], [7] are set to w6, w7 (n_partials may be 0: header only)
 cudaError_t launch_reduce_partials(const BlockPartial* d_partials, int n_partials,
-                                   unsigned long long* d_stage_words, cudaStream_t stream);
+                                   unsigned long long* d_stage_words, unsigned long long w6,
+                                   unsigned long long w7, cudaStream_t stream);
 
 }  // namespace mc

@@ -196,7 +196,7 @@ class Engine:
         with torch.cuda.device(self.device):
             terminal = torch.empty(n_local, dtype=dt, device=self.device)
             paths = torch.empty((spec.n_steps + 1, n_local), dtype=dt, device=self.device) if spec.store_paths else None
-            params = make_params(spec, path_offset=offset, n_local=n_local)
+            params = make_params(spec, path_offset=offset, n_local=n_local, n_ranks=world)
             pf = make_portfolio(spec)
             res = L.McResult()
             hist = np.zeros(spec.hist_bins, dtype=np.uint64) if spec.hist_bins else None

@@ -96,7 +96,7 @@ def _staged_emulated_ranks(spec, pool, world):
         pool_t = e.to_device(pool, dt) if pool is not None else None
         if pool_t is not None:
             spec.pool_len = pool_t.numel()
-        params = make_params(spec, path_offset=off, n_local=cnt)
+        params = make_params(spec, path_offset=off, n_local=cnt, n_ranks=world)
         term = torch.empty(cnt, dtype=dt, device=e.device)
         backs.append(_CudaStageBackend(e, params, None, pool_t, None, None, term, world))
         outs.append(term)
