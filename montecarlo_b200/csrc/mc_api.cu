@@ -64,6 +64,7 @@ struct mc_handle {
     std::string err;
 
     DevBuf<BlockPartial> partials;
+    DevBuf<float2> lut;                 // Box-Muller direction table of the fp32 normal shocks (mc_rng.cuh)
     DevBuf<DeviceResult> res;
     DevBuf<SelectPlan> plans;           // [2]: terminal, fan
     DevBuf<RowSel> states_t, states_f;
@@ -208,7 +209,9 @@ int mc_create(int device_ordinal, mc_handle** out) {
     bool ok = h->partials.reserve(MAX_SIM_GRID) == cudaSuccess && h->res.reserve(1) == cudaSuccess &&
               h->plans.reserve(2) == cudaSuccess && h->states_t.reserve(1) == cudaSuccess &&
               h->pct_t.reserve(3 * MC_MAX_PCTS) == cudaSuccess && h->tail_scratch.reserve(2 * 1024) == cudaSuccess &&
-              h->pending.reserve(1) == cudaSuccess && h->h_pending.reserve(1) == cudaSuccess;
+              h->pending.reserve(1) == cudaSuccess && h->h_pending.reserve(1) == cudaSuccess &&
+              h->lut.reserve(4096) == cudaSuccess && launch_build_direction_table(h->lut.p, nullptr) == cudaSuccess &&
+              cudaStreamSynchronize(nullptr) == cudaSuccess;
     for (int i = 0; i < 3 && ok; ++i) ok = cudaEventCreate(&h->ev[i]) == cudaSuccess;
     if (!ok) {
         e = cudaGetLastError();
@@ -222,7 +225,7 @@ int mc_create(int device_ordinal, mc_handle** out) {
 int mc_destroy(mc_handle* h) {
     if (!h) return MC_OK;
     cudaSetDevice(h->device);
-    h->partials.release(); h->res.release(); h->plans.release(); h->states_t.release(); h->states_f.release();
+    h->partials.release(); h->lut.release(); h->res.release(); h->plans.release(); h->states_t.release(); h->states_f.release();
     h->pct_t.release(); h->fan.release(); h->tail_scratch.release(); h->edges.release(); h->hist_total.release();
     h->stage.release(); h->h_stage.release(); h->pending.release(); h->h_pending.release();
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
@@ -299,6 +302,7 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
     SimBuffers b{};
     b.d_pool = d_pool; b.d_shocks = d_shocks; b.d_paths = d_paths; b.d_terminal = d_terminal;
     b.d_partials = h->partials.p;
+    b.d_lut = h->lut.p;
     int grid = 0;
     if (p->n_paths) {
         MC_CUDA(h, launch_simulation(*p, pf, b, h->dev, &grid, s));
@@ -510,7 +514,7 @@ int mc_debug_shocks(mc_handle* h, const mc_params* p, const void* d_pool, void* 
     if (!p || p->struct_size != sizeof(mc_params)) return fail(h, MC_ERR_VERSION, "mc_params mismatch");
     if (p->shock == MC_SHOCK_BOOTSTRAP && !d_pool) return fail(h, MC_ERR_INVALID, "pool missing");
     MC_CUDA(h, cudaSetDevice(h->device));
-    MC_CUDA(h, launch_debug_shocks(*p, d_pool, d_out, static_cast<cudaStream_t>(stream)));
+    MC_CUDA(h, launch_debug_shocks(*p, d_pool, h->lut.p, d_out, static_cast<cudaStream_t>(stream)));
     return MC_OK;
 }
 

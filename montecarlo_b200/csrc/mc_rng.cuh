@@ -8,7 +8,7 @@
 //
 // Conventions (mirrored bit-for-bit by oracle/philox.py):
 //   ctr = (path_lo, path_hi, call, stream), key = (seed_lo, seed_hi)
-//   one call -> 4 words -> 4 normals (steps 4j..4j+3) or 4 bootstrap indices
+//   one call -> 4 words -> 8 fp32 normals / 5 fp32 bootstrap indices, or 4 of either in fp64
 #pragma once
 #include <stdint.h>
 
@@ -90,24 +90,7 @@ constexpr float TWO_PI_F = 6.28318530717958647692f;
 constexpr float THREE_PI_F = 9.42477796076937971538f;
 constexpr float LN2_F = 0.69314718055994530942f;
 
-// Box-Muller radius with the factor sqrt(2 ln 2) left out: rho = sqrt(-lg2(v1)),
-// r = sqrt(2 ln2) * rho.  Callers that only need sigma * sum(z) fold the constant
-// into sigma and save one multiply per pair.
-__device__ __forceinline__ float bm_rho(uint32_t ua) {
-    const float v1 = 2.0f - mantissa_float(ua);       // (0, 1]
-    return fast_sqrt(-fast_lg2(v1));
-}
-__device__ __forceinline__ float bm_theta(uint32_t ub) {
-    return fmaf(mantissa_float(ub), TWO_PI_F, -THREE_PI_F);   // [-pi, pi)
-}
 constexpr float BM_RADIUS_SCALE_F = 1.17741002251547469101f;   // sqrt(2 ln 2)
-
-__device__ __forceinline__ void box_muller(uint32_t ua, uint32_t ub, float& z0, float& z1) {
-    const float r = BM_RADIUS_SCALE_F * bm_rho(ua);
-    const float th = bm_theta(ub);
-    z0 = r * fast_cos(th);
-    z1 = r * fast_sin(th);
-}
 
 __device__ __forceinline__ void box_muller(uint32_t ua, uint32_t ub, double& z0, double& z1) {
     const double v1 = ((double)ua + 1.0) * 2.3283064365386963e-10;       // (0, 1]
@@ -120,58 +103,89 @@ __device__ __forceinline__ void box_muller(uint32_t ua, uint32_t ub, double& z0,
     z1 = r * s;
 }
 
-// ---- fp32: SIX normals from one 128-bit Philox call -------------------------------------
-// The Philox multiply (IMAD.WIDE) runs at a quarter of the FP32 rate on sm_100a (measured:
-// tools/microbench.cu), so the generator -- not the transform -- bounds the fused kernels.
-// A float only holds 23 mantissa bits, so 4 x 32 bits are cut into three Box-Muller pairs
-// instead of two:   radius uniform k = word_k[22:0]            (23 bits, k = 0,1,2)
-//                   angle A = word_3[31:9]                      (23 bits)
-//                   angle B = word_0[31:24] : word_1[31:24]     (16 bits)
-//                   angle C = word_2[31:24] : word_3[7:0]       (16 bits)
-// All fields are disjoint, so the six uniforms are independent.  (The low mantissa bits of the
-// 16-bit angles repeat the field's own top byte: 65,536 distinct, near-equispaced angles.)
-__device__ __forceinline__ float radius_uniform(uint32_t w) {           // (0, 1]
-    return 2.0f - __uint_as_float((w & 0x007FFFFFu) | 0x3F800000u);
-}
-__device__ __forceinline__ float rho_of(uint32_t w) { return fast_sqrt(-fast_lg2(radius_uniform(w))); }
-__device__ __forceinline__ float theta_of(uint32_t field_at_top) {       // [-pi, pi)
-    return fmaf(mantissa_float(field_at_top), TWO_PI_F, -THREE_PI_F);
-}
-__device__ __forceinline__ uint32_t angle_b_bits(const u32x4& w) { return __byte_perm(w.x, w.y, 0x3733); }
-__device__ __forceinline__ uint32_t angle_c_bits(const u32x4& w) { return __byte_perm(w.z, w.w, 0x3433); }
+// ---- fp32: EIGHT normals from one 128-bit Philox call, directions from a shared-memory table ----
+// Measured on sm_100a (tools/microbench2.cu, profiles/r01/microbench2_sm100a_v3.txt):
+//   * IMAD.WIDE (the Philox multiply) issues at 32 lanes/clk/SM, a quarter of the FP32 rate, and MUFU at
+//     16 lanes/clk/SM; with six normals per call and MUFU.SIN/COS (round-1 v2) both pipes and the issue
+//     port sat within 15 % of each other and the loop reached 6.0 normals/clk/SM;
+//   * one Box-Muller pair per 32-bit word (8 normals per call) cuts the Philox cost per normal by a
+//     quarter: 6.6;  a polynomial sin/cos on the FMA pipes does not pay (FFMAs queue behind IMAD.WIDE
+//     on the heavy FMA pipe): 6.0 - 6.7;
+//   * reading (cos, sin) of the 12-bit direction from a 4096-entry table in shared memory (one LDS.64,
+//     random banks, ~6 wavefronts) takes the two MUFU.SIN/COS off the XU pipe altogether: 8.4 - 8.5.
+// Word layout:  radius uniform = word[19:0]  (20 bits)  v1 = 1 - k 2^-20 in (0, 1],  |z| <= 5.27
+//               direction      = word[31:20] (12 bits)  theta = 2 pi (d / 4096 - 1/2)
+// The fields are disjoint, so radius and direction are independent; 4096 equispaced directions integrate
+// every smooth functional of (z0, z1) exactly (trapezoid rule on a periodic integrand).
+constexpr int DIR_BITS = 12;
+constexpr int DIR_COUNT = 1 << DIR_BITS;                 // float2 (cos, sin) entries: 32 KB
 
-__device__ __forceinline__ void normals6(const u32x4& w, float (&z)[6]) {
-    const float ra = BM_RADIUS_SCALE_F * rho_of(w.x), rb = BM_RADIUS_SCALE_F * rho_of(w.y),
-                rc = BM_RADIUS_SCALE_F * rho_of(w.z);
-    const float ta = theta_of(w.w), tb = theta_of(angle_b_bits(w)), tc = theta_of(angle_c_bits(w));
-    z[0] = ra * fast_cos(ta); z[1] = ra * fast_sin(ta);
-    z[2] = rb * fast_cos(tb); z[3] = rb * fast_sin(tb);
-    z[4] = rc * fast_cos(tc); z[5] = rc * fast_sin(tc);
+__device__ __forceinline__ float radius_uniform20(uint32_t w) {           // (0, 1], multiples of 2^-20
+    return fmaf(__uint_as_float((w & 0x000FFFFFu) | 0x3F800000u), -8.0f, 9.0f);
 }
-// sum of the six normals / sqrt(2 ln 2), one FFMA per normal (constant folded in by the caller)
-__device__ __forceinline__ float normals6_sum(const u32x4& w, float s) {
-    const float ra = rho_of(w.x), rb = rho_of(w.y), rc = rho_of(w.z);
-    const float ta = theta_of(w.w), tb = theta_of(angle_b_bits(w)), tc = theta_of(angle_c_bits(w));
-    s = fmaf(ra, fast_cos(ta), s); s = fmaf(ra, fast_sin(ta), s);
-    s = fmaf(rb, fast_cos(tb), s); s = fmaf(rb, fast_sin(tb), s);
-    s = fmaf(rc, fast_cos(tc), s); s = fmaf(rc, fast_sin(tc), s);
-    return s;
+// Box-Muller radius without its constant: rho = sqrt(-lg2 v1), r = sqrt(2 ln 2) rho
+__device__ __forceinline__ float rho20(uint32_t w) { return fast_sqrt(-fast_lg2(radius_uniform20(w))); }
+
+// (cos, sin) of the word's direction; lut_base = shared-window byte address of the table
+__device__ __forceinline__ void direction_of(uint32_t w, uint32_t lut_base, float& c, float& s) {
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(c), "=f"(s) : "r"(lut_base + ((w >> 17) & 0x7FF8u)));
+}
+
+__device__ __forceinline__ void normals8(const u32x4& w, uint32_t lut_base, float (&z)[8]) {
+    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float r = BM_RADIUS_SCALE_F * rho20(ww[k]);
+        float c, s;
+        direction_of(ww[k], lut_base, c, s);
+        z[2 * k] = r * c;
+        z[2 * k + 1] = r * s;
+    }
+}
+// acc + (sum of the eight normals) / sqrt(2 ln 2): one FFMA per normal, constant applied by the caller
+__device__ __forceinline__ float normals8_sum(const u32x4& w, uint32_t lut_base, float acc) {
+    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float r = rho20(ww[k]);
+        float c, s;
+        direction_of(ww[k], lut_base, c, s);
+        acc = fmaf(r, c, acc);
+        acc = fmaf(r, s, acc);
+    }
+    return acc;
 }
 
 // ---- fp64: four normals per call from full 32-bit uniforms ------------------------------
-__device__ __forceinline__ void normals4(const u32x4& w, double (&z)[6]) {
+__device__ __forceinline__ void normals4(const u32x4& w, double (&z)[8]) {
     box_muller(w.x, w.y, z[0], z[1]);
     box_muller(w.z, w.w, z[2], z[3]);
-    z[4] = 0.0; z[5] = 0.0;
+    z[4] = 0.0; z[5] = 0.0; z[6] = 0.0; z[7] = 0.0;
 }
 
-template <typename Real> struct NormalsPerCall { static constexpr int value = sizeof(Real) == 4 ? 6 : 4; };
-__device__ __forceinline__ void draw_normals(const u32x4& w, float (&z)[6]) { normals6(w, z); }
-__device__ __forceinline__ void draw_normals(const u32x4& w, double (&z)[6]) { normals4(w, z); }
+template <typename Real> struct NormalsPerCall { static constexpr int value = sizeof(Real) == 4 ? 8 : 4; };
+__device__ __forceinline__ void draw_normals(const u32x4& w, uint32_t lut_base, float (&z)[8]) { normals8(w, lut_base, z); }
+__device__ __forceinline__ void draw_normals(const u32x4& w, uint32_t, double (&z)[8]) { normals4(w, z); }
 
-// bootstrap index: floor(u * H / 2^32), exact, unbiased to 2^-32 * H
+// ---- bootstrap indices (the reference's np.random.choice(std_returns, size=n_sims), app.py:620) ----
+// fp64 kernels: FOUR per call, idx = floor(word * H / 2^32) by IMAD.HI; non-uniformity H 2^-32.
 __device__ __forceinline__ uint32_t bootstrap_index(uint32_t u, uint32_t pool_len) {
     return __umulhi(u, pool_len);
+}
+// fp32 kernels: FIVE per call from 23-bit fields, idx = floor(field * H / 2^23), computed on the FMA
+// pipe (IMAD.HI is quarter rate like IMAD.WIDE and the Philox multiplies already saturate that pipe):
+//     g  = bits(0x4B000000 | field)              = 2^23 + field                    (exact)
+//     t  = fma(g, H 2^-23, 2^23 - H + 1/2)       = 2^23 + field H 2^-23 + 1/2      (ONE rounding, ulp 1)
+//        = 2^23 + idx + 1            (a tie -- field H 2^-23 an exact integer -- rounds to even)
+// so bits(t) - 0x4B000000 = idx + 1, and (bits(t) << s) wraps the exponent bits out of a byte offset.
+// Fields 0-3 are word[22:0]; field 4 is the top bytes of words 0, 1, 2.  Per-index probabilities differ
+// by at most H 2^-23 (1.5e-4 at the reference's H ~ 1250); pools longer than 65536 use the IMAD.HI path.
+constexpr uint32_t BOOT32_MAX_POOL = 65536u;
+__device__ __forceinline__ uint32_t boot_field4(const u32x4& w) {
+    return __byte_perm(__byte_perm(w.x, w.y, 0x0073), w.z, 0x7710);
+}
+__device__ __forceinline__ uint32_t boot_index_bits(uint32_t field_word, float scale, float bias) {
+    return __float_as_uint(fmaf(__uint_as_float((field_word & 0x007FFFFFu) | 0x4B000000u), scale, bias));
 }
 
 }  // namespace mc

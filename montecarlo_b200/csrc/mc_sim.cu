@@ -11,6 +11,10 @@
 // The terminal reductions of app.py:636-656 start here too: each thread
 // accumulates moments about s0 in fp64 (one partial per block, reduced in fixed order).
 //
+// Two kernel families: sim32_kernel (fp32, shocks generated on the device: the fast path of
+// every BASELINE config) and the generic sim_kernel (fp64, and injected shocks in either
+// precision: the parity path).
+//
 // Units: the fp32 kernels accumulate the log-price in log2 units (the host
 // pre-multiplies drift, omega and var0 by log2(e) or its square; GARCH is
 // homogeneous so the recursion is unchanged) so that price = s0 * ex2(y) is a
@@ -110,28 +114,27 @@ __device__ __forceinline__ void finish_block(BlockPartial acc, BlockPartial* s_w
     if (threadIdx.x == 0) partials[blockIdx.x] = acc;
 }
 
-// ------------------------------------------------------------------ shock sources
-// Shocks per Philox call: 6 for fp32 normals (mc_rng.cuh: three Box-Muller pairs from 128 bits),
-// 4 for fp64 normals and for bootstrap indices (one full 32-bit word each).  Injected shocks are
-// read in groups of 4.  Step t of a path uses shock (t mod K) of call (t div K).
+// ------------------------------------------------------------------ shock sources (generic kernel)
+// The generic kernel draws its own shocks only in fp64: 4 normals or 4 bootstrap indices per Philox
+// call (one full 32-bit word each).  Injected shocks (either precision) are read in groups of 4.
+// Step t of a path uses shock (t mod 4) of call (t div 4).  fp32 device shocks: sim32_kernel below.
 template <typename Real, int SHOCK>
-struct ShocksPerCall {
-    static constexpr int value = (SHOCK == MC_SHOCK_NORMAL) ? NormalsPerCall<Real>::value : 4;
-};
+struct ShocksPerCall { static constexpr int value = 4; };
 
 template <typename Real, int SHOCK>
 __device__ __forceinline__ void draw(const SimArgs<Real>& a, const Real* s_pool, unsigned long long i,
-                                     uint32_t c0, uint32_t c1, uint32_t call, uint32_t t, Real (&z)[6]) {
+                                     uint32_t c0, uint32_t c1, uint32_t call, uint32_t t, Real (&z)[8]) {
+#pragma unroll
+    for (int k = 4; k < 8; ++k) z[k] = Real(0);
     if (SHOCK == MC_SHOCK_INJECTED) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
             z[k] = (t + k < a.n_steps) ? a.shocks[(unsigned long long)(t + k) * a.ld_shocks + i] : Real(0);
-        z[4] = Real(0); z[5] = Real(0);
         return;
     }
     const u32x4 w = philox4x32_10(c0, c1, call, 0u, a.rk);
     if (SHOCK == MC_SHOCK_NORMAL) {
-        draw_normals(w, z);
+        draw_normals(w, 0u, z);
     } else {
         const uint32_t u[4] = {w.x, w.y, w.z, w.w};
         if (a.pool_log2_copies >= 0) {
@@ -146,7 +149,6 @@ __device__ __forceinline__ void draw(const SimArgs<Real>& a, const Real* s_pool,
 #pragma unroll
             for (int k = 0; k < 4; ++k) z[k] = __ldg(&a.pool[bootstrap_index(u[k], a.pool_len)]);
         }
-        z[4] = Real(0); z[5] = Real(0);
     }
 }
 
@@ -187,34 +189,22 @@ __global__ void __launch_bounds__(MAXB) sim_kernel(const __grid_constant__ SimAr
         Real y = Real(0), v = a.var0;
         if (STORE) a.paths[i] = a.s0;                              // app.py:613
 
-        constexpr bool FUSED_SUM = (SHOCK == MC_SHOCK_NORMAL && VAR == MC_VAR_CONST && !STORE &&
-                                    sizeof(Real) == 4);
         uint32_t t = 0;
-        if (FUSED_SUM) {
-            // constant sigma and nothing stored: y_T = sig * sum z.  The Box-Muller radius
-            // constant and sigma are applied once after the loop; each normal costs one FFMA.
-            float s = 0.0f;
 #pragma unroll 2
-            for (uint32_t j = 0; j < n_full; ++j) s = normals6_sum(philox4x32_10(c0, c1, j, 0u, a.rk), s);
-            y = (Real)(sig * BM_RADIUS_SCALE_F * s);
-            t = n_full * K;
-        } else {
-#pragma unroll 2
-            for (uint32_t j = 0; j < n_full; ++j) {
-                Real z[6];
-                draw<Real, SHOCK>(a, s_pool, i, c0, c1, j, t, z);
+        for (uint32_t j = 0; j < n_full; ++j) {
+            Real z[8];
+            draw<Real, SHOCK>(a, s_pool, i, c0, c1, j, t, z);
 #pragma unroll
-                for (int k = 0; k < K; ++k) {
-                    step<Real, VAR>(a, z[k], sig, y, v);
-                    if (STORE)
-                        a.paths[(unsigned long long)(t + k + 1) * a.ld_paths + i] =
-                            a.s0 * exp_units(fma_units((Real)(t + k + 1), a.drift, y));
-                }
-                t += K;
+            for (int k = 0; k < K; ++k) {
+                step<Real, VAR>(a, z[k], sig, y, v);
+                if (STORE)
+                    a.paths[(unsigned long long)(t + k + 1) * a.ld_paths + i] =
+                        a.s0 * exp_units(fma_units((Real)(t + k + 1), a.drift, y));
             }
+            t += K;
         }
         if (t < a.n_steps) {   // ragged tail: n_steps not a multiple of K
-            Real z[6];
+            Real z[8];
             draw<Real, SHOCK>(a, s_pool, i, c0, c1, n_full, t, z);
 #pragma unroll
             for (int k = 0; k < K - 1; ++k) {
@@ -233,6 +223,10 @@ __global__ void __launch_bounds__(MAXB) sim_kernel(const __grid_constant__ SimAr
     finish_block(acc, s_warp, a.partials);
 }
 
+}  // namespace mc
+#include "mc_sim32.cuh"
+namespace mc {
+
 // ------------------------------------------------------------------ correlated portfolio
 // Mode P (north_star extension; nothing like it in the reference): d assets driven by
 // y = L z with L the Cholesky factor of the correlation matrix.  L (pre-scaled by
@@ -245,6 +239,7 @@ struct PortArgs {
     uint32_t n_steps, calls_per_step, n_assets;
     RoundKeys rk;
     const Real* shocks;
+    const float2* lut;                // fp32 device shocks: Box-Muller direction table (mc_rng.cuh)
     Real* paths;
     Real* terminal;
     Real v0;                          // portfolio value at t=0
@@ -265,7 +260,14 @@ __device__ __forceinline__ Real portfolio_value(const PortArgs<Real, D>& a, cons
 
 template <typename Real, int D, bool INJECTED, bool STORE>
 __global__ void __launch_bounds__(SIM_BLOCK) portfolio_kernel(const __grid_constant__ PortArgs<Real, D> a) {
+    extern __shared__ __align__(16) unsigned char smem_dyn[];
     __shared__ BlockPartial s_warp[32];
+    const uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(smem_dyn);
+    if (!INJECTED && sizeof(Real) == 4) {
+        float2* s_lut = reinterpret_cast<float2*>(smem_dyn);
+        for (int i = threadIdx.x; i < DIR_COUNT; i += blockDim.x) s_lut[i] = a.lut[i];
+    }
+    __syncthreads();
 
     BlockPartial acc = empty_partial();
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
@@ -291,10 +293,10 @@ __global__ void __launch_bounds__(SIM_BLOCK) portfolio_kernel(const __grid_const
                 constexpr int QMAX = (D + NPC - 1) / NPC;
 #pragma unroll
                 for (int q = 0; q < QMAX; ++q) {
-                    Real zq[6] = {Real(0), Real(0), Real(0), Real(0), Real(0), Real(0)};
+                    Real zq[8] = {Real(0), Real(0), Real(0), Real(0), Real(0), Real(0), Real(0), Real(0)};
                     if (q < (int)a.calls_per_step) {
                         const u32x4 w = philox4x32_10(c0, c1, call + q, 0u, a.rk);
-                        draw_normals(w, zq);
+                        draw_normals(w, lut_base, zq);
                     }
 #pragma unroll
                     for (int k = 0; k < NPC; ++k)
@@ -329,8 +331,42 @@ __global__ void debug_shocks_kernel(const SimArgs<Real> a, Real* out) {
          i += stride) {
         const unsigned long long gid = a.path_offset + i;
         for (uint32_t j = 0; j < n_calls; ++j) {
-            Real z[6];
+            Real z[8];
             draw<Real, SHOCK>(a, nullptr, i, (uint32_t)gid, (uint32_t)(gid >> 32), j, K * j, z);
+#pragma unroll
+            for (int k = 0; k < K; ++k)
+                if (K * j + k < a.n_steps) out[(unsigned long long)(K * j + k) * a.n_paths + i] = z[k];
+        }
+    }
+}
+
+// the shocks sim32_kernel consumes: normals (8 per call) or pool[index] (5 per call)
+template <int SHOCK>
+__global__ void debug_shocks32_kernel(const Sim32Args a, float* out) {
+    extern __shared__ __align__(16) unsigned char smem_dyn[];
+    const uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(smem_dyn);
+    if (SHOCK == MC_SHOCK_NORMAL) {
+        float2* s_lut = reinterpret_cast<float2*>(smem_dyn);
+        for (int i = threadIdx.x; i < DIR_COUNT; i += blockDim.x) s_lut[i] = a.lut[i];
+    }
+    __syncthreads();
+    constexpr int K = SHOCK == MC_SHOCK_NORMAL ? 8 : 5;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    const uint32_t n_calls = (a.n_steps + K - 1) / K;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n_paths;
+         i += stride) {
+        const unsigned long long gid = a.path_offset + i;
+        for (uint32_t j = 0; j < n_calls; ++j) {
+            const u32x4 w = philox4x32_10((uint32_t)gid, (uint32_t)(gid >> 32), j, 0u, a.rk);
+            float z[8];
+            if (SHOCK == MC_SHOCK_NORMAL) {
+                normals8(w, lut_base, z);
+            } else {
+                const uint32_t f[5] = {w.x, w.y, w.z, w.w, boot_field4(w)};
+#pragma unroll
+                for (int k = 0; k < 5; ++k)
+                    z[k] = a.pool[(boot_index_bits(f[k], a.idx_scale, a.idx_bias) & 0x007FFFFFu) - 1u];
+            }
 #pragma unroll
             for (int k = 0; k < K; ++k)
                 if (K * j + k < a.n_steps) out[(unsigned long long)(K * j + k) * a.n_paths + i] = z[k];
@@ -474,15 +510,99 @@ static cudaError_t dispatch_var(const mc_params& p, const SimBuffers& b, const D
     return p.var_model == MC_VAR_CONST ? dispatch_store<Real, SHOCK, MC_VAR_CONST>(p, b, dev, grid, s)
                                        : dispatch_store<Real, SHOCK, MC_VAR_GARCH>(p, b, dev, grid, s);
 }
+// generic kernel: fp64 with any shock source; fp32 only with injected shocks
 template <typename Real>
 static cudaError_t dispatch_shock(const mc_params& p, const SimBuffers& b, const DeviceInfo& dev, int* grid,
                                   cudaStream_t s) {
-    switch (p.shock) {
-        case MC_SHOCK_BOOTSTRAP: return dispatch_var<Real, MC_SHOCK_BOOTSTRAP>(p, b, dev, grid, s);
-        case MC_SHOCK_NORMAL: return dispatch_var<Real, MC_SHOCK_NORMAL>(p, b, dev, grid, s);
-        case MC_SHOCK_INJECTED: return dispatch_var<Real, MC_SHOCK_INJECTED>(p, b, dev, grid, s);
-        default: return cudaErrorInvalidValue;
+    if (p.shock == MC_SHOCK_INJECTED) return dispatch_var<Real, MC_SHOCK_INJECTED>(p, b, dev, grid, s);
+    if constexpr (sizeof(Real) == 8) {
+        if (p.shock == MC_SHOCK_BOOTSTRAP) return dispatch_var<Real, MC_SHOCK_BOOTSTRAP>(p, b, dev, grid, s);
+        if (p.shock == MC_SHOCK_NORMAL) return dispatch_var<Real, MC_SHOCK_NORMAL>(p, b, dev, grid, s);
     }
+    return cudaErrorInvalidValue;
+}
+
+// ---- fp32 with device shocks: sim32_kernel -------------------------------------------------
+static bool boot32_eligible(const mc_params& p) { return p.pool_len >= 1 && p.pool_len <= BOOT32_MAX_POOL; }
+
+static Sim32Args make_args32(const mc_params& p, const SimBuffers& b) {
+    Sim32Args a{};
+    a.n_paths = p.n_paths;
+    a.path_offset = p.path_offset;
+    a.ld_paths = p.paths_ld ? p.paths_ld : p.n_paths;
+    a.n_steps = p.n_steps;
+    a.pool_len = p.pool_len;
+    a.table_lc = 0;
+    a.idx_scale = (float)p.pool_len * 1.1920928955078125e-07f;     // H 2^-23: exact
+    a.idx_bias = 8388608.0f - (float)p.pool_len + 0.5f;            // exact: below 2^23 the ulp is <= 1/2
+    a.rk = expand_key((uint32_t)p.seed, (uint32_t)(p.seed >> 32));
+    a.lut = b.d_lut;
+    a.pool = static_cast<const float*>(b.d_pool);
+    a.paths = static_cast<float*>(b.d_paths);
+    a.terminal = static_cast<float*>(b.d_terminal);
+    a.s0 = (float)p.s0;
+    a.var0 = (float)(p.var0 * LOG2E * LOG2E);
+    a.omega = (float)(p.omega * LOG2E * LOG2E);
+    a.alpha = (float)p.alpha;
+    a.beta = (float)p.beta;
+    a.drift = (float)(p.drift * LOG2E);
+    a.sig = (float)(sqrt(p.var0) * LOG2E);
+    a.center = p.s0;
+    a.partials = b.d_partials;
+    return a;
+}
+
+template <int SHOCK, int VAR, bool STORE, int V, bool TAB>
+static cudaError_t launch32_t(Sim32Args& a, const DeviceInfo& dev, int* grid, cudaStream_t stream) {
+    auto kernel = sim32_kernel<SHOCK, VAR, STORE, V, TAB>;
+    const unsigned long long items = (a.n_paths + V - 1) / V;      // threads' worth of work
+    int block;
+    size_t smem;
+    if (SHOCK == MC_SHOCK_NORMAL) {
+        smem = (size_t)DIR_COUNT * sizeof(float2);
+        block = items >= 512ull * dev.sm_count ? 512 : 128;
+    } else {
+        block = items >= 1024ull * dev.sm_count ? 1024 : 256;
+        smem = TAB ? ((size_t)a.pool_len << a.table_lc) * sizeof(float2) : 0;
+    }
+    cudaError_t e = pick_grid(kernel, block, smem, dev, items, grid);
+    if (e != cudaSuccess) return e;
+    kernel<<<*grid, block, smem, stream>>>(a);
+    return cudaGetLastError();
+}
+
+template <int SHOCK, int VAR, bool TAB>
+static cudaError_t launch32_store(Sim32Args& a, const mc_params& p, const DeviceInfo& dev, int* grid, cudaStream_t s) {
+    if (!(p.flags & MC_FLAG_STORE_PATHS)) return launch32_t<SHOCK, VAR, false, 1, TAB>(a, dev, grid, s);
+    // 16-byte stores need rows and base pointers that keep every group of four paths aligned
+    const bool vec = a.ld_paths % 4 == 0 && ((uintptr_t)a.paths & 15u) == 0 && ((uintptr_t)a.terminal & 15u) == 0 &&
+                     a.n_paths >= 4;
+    return vec ? launch32_t<SHOCK, VAR, true, 4, TAB>(a, dev, grid, s)
+               : launch32_t<SHOCK, VAR, true, 1, TAB>(a, dev, grid, s);
+}
+
+template <int SHOCK, bool TAB>
+static cudaError_t launch32_var(Sim32Args& a, const mc_params& p, const DeviceInfo& dev, int* grid, cudaStream_t s) {
+    return p.var_model == MC_VAR_CONST ? launch32_store<SHOCK, MC_VAR_CONST, TAB>(a, p, dev, grid, s)
+                                       : launch32_store<SHOCK, MC_VAR_GARCH, TAB>(a, p, dev, grid, s);
+}
+
+static cudaError_t launch_sim32(const mc_params& p, const SimBuffers& b, const DeviceInfo& dev, int* grid,
+                                cudaStream_t s) {
+    Sim32Args a = make_args32(p, b);
+    if (p.shock == MC_SHOCK_NORMAL) {
+        if (!b.d_lut) return cudaErrorInvalidValue;
+        return launch32_var<MC_SHOCK_NORMAL, true>(a, p, dev, grid, s);
+    }
+    // bootstrap: widest replication (<= 8 copies: a half-warp's LDS.64 then rarely collides) that fits
+    const size_t budget = (size_t)dev.max_smem_optin - 4 * 1024;
+    int lc = 3;
+    while (lc >= 0 && ((size_t)p.pool_len << lc) * sizeof(float2) > budget) --lc;
+    if (lc < 0) return launch32_var<MC_SHOCK_BOOTSTRAP, false>(a, p, dev, grid, s);   // gather from global/L1
+    if (p.n_paths < 1024ull * dev.sm_count)        // small request: cheaper table fill, more blocks per SM
+        while (lc > 0 && ((size_t)p.pool_len << lc) * sizeof(float2) > 40 * 1024) --lc;
+    a.table_lc = lc;
+    return launch32_var<MC_SHOCK_BOOTSTRAP, true>(a, p, dev, grid, s);
 }
 
 template <typename Real, int D, bool INJECTED, bool STORE>
@@ -501,6 +621,7 @@ static cudaError_t launch_portfolio_impl(const mc_params& p, const mc_portfolio&
     a.calls_per_step = (uint32_t)((d + NormalsPerCall<Real>::value - 1) / NormalsPerCall<Real>::value);
     a.n_assets = (uint32_t)d;
     a.shocks = static_cast<const Real*>(b.d_shocks);
+    a.lut = b.d_lut;
     a.paths = static_cast<Real*>(b.d_paths);
     a.terminal = static_cast<Real*>(b.d_terminal);
     double v0 = 0.0;
@@ -515,9 +636,11 @@ static cudaError_t launch_portfolio_impl(const mc_params& p, const mc_portfolio&
     a.center = p.s0;
     a.partials = b.d_partials;
     auto kernel = portfolio_kernel<Real, D, INJECTED, STORE>;
-    cudaError_t e = pick_grid(kernel, SIM_BLOCK, 0, dev, p.n_paths, grid);
+    const size_t smem = (!INJECTED && sizeof(Real) == 4) ? (size_t)DIR_COUNT * sizeof(float2) : 0;
+    if (smem && !b.d_lut) return cudaErrorInvalidValue;
+    cudaError_t e = pick_grid(kernel, SIM_BLOCK, smem, dev, p.n_paths, grid);
     if (e != cudaSuccess) return e;
-    kernel<<<*grid, SIM_BLOCK, 0, stream>>>(a);
+    kernel<<<*grid, SIM_BLOCK, smem, stream>>>(a);
     return cudaGetLastError();
 }
 
@@ -550,8 +673,16 @@ cudaError_t launch_simulation(const mc_params& p, const mc_portfolio* pf, const 
         return p.dtype == MC_F64 ? launch_portfolio<double>(p, *pf, b, dev, grid, stream)
                                  : launch_portfolio<float>(p, *pf, b, dev, grid, stream);
     }
-    return p.dtype == MC_F64 ? dispatch_shock<double>(p, b, dev, grid, stream)
-                             : dispatch_shock<float>(p, b, dev, grid, stream);
+    if (p.dtype == MC_F64) return dispatch_shock<double>(p, b, dev, grid, stream);
+    if (p.shock == MC_SHOCK_NORMAL || (p.shock == MC_SHOCK_BOOTSTRAP && boot32_eligible(p)))
+        return launch_sim32(p, b, dev, grid, stream);
+    if (p.shock == MC_SHOCK_BOOTSTRAP) return cudaErrorNotSupported;   // fp32 pools beyond BOOT32_MAX_POOL: use fp64
+    return dispatch_shock<float>(p, b, dev, grid, stream);
+}
+
+cudaError_t launch_build_direction_table(float2* d_lut, cudaStream_t stream) {
+    build_direction_table_kernel<<<(DIR_COUNT + 255) / 256, 256, 0, stream>>>(d_lut);
+    return cudaGetLastError();
 }
 
 template <typename Real>
@@ -569,9 +700,24 @@ static cudaError_t debug_shocks_t(const mc_params& p, const void* d_pool, void* 
     return cudaGetLastError();
 }
 
-cudaError_t launch_debug_shocks(const mc_params& p, const void* d_pool, void* d_out, cudaStream_t stream) {
-    return p.dtype == MC_F64 ? debug_shocks_t<double>(p, d_pool, d_out, stream)
-                             : debug_shocks_t<float>(p, d_pool, d_out, stream);
+cudaError_t launch_debug_shocks(const mc_params& p, const void* d_pool, const float2* d_lut, void* d_out,
+                                cudaStream_t stream) {
+    if (p.dtype == MC_F64) return debug_shocks_t<double>(p, d_pool, d_out, stream);
+    SimBuffers b{};
+    b.d_pool = d_pool;
+    b.d_lut = d_lut;
+    const Sim32Args a = make_args32(p, b);
+    int grid = (int)((p.n_paths + 255) / 256 < 4096 ? (p.n_paths + 255) / 256 : 4096);
+    if (grid < 1) grid = 1;
+    if (p.shock == MC_SHOCK_NORMAL) {
+        if (!d_lut) return cudaErrorInvalidValue;
+        debug_shocks32_kernel<MC_SHOCK_NORMAL><<<grid, 256, DIR_COUNT * sizeof(float2), stream>>>(a, static_cast<float*>(d_out));
+    } else if (p.shock == MC_SHOCK_BOOTSTRAP && boot32_eligible(p)) {
+        debug_shocks32_kernel<MC_SHOCK_BOOTSTRAP><<<grid, 256, 0, stream>>>(a, static_cast<float*>(d_out));
+    } else {
+        return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
 }
 
 cudaError_t launch_debug_philox(const uint32_t* d_ctr, uint32_t n, uint32_t k0, uint32_t k1, uint32_t* d_out,

@@ -10,6 +10,7 @@ struct SimBuffers {
     void* d_paths;
     void* d_terminal;
     BlockPartial* d_partials;     // [max_grid]
+    const float2* d_lut;          // Box-Muller direction table (fp32 normal shocks), [4096]
 };
 
 constexpr int MAX_SIM_GRID = 1 << 16;     // per-block partials are reduced in fixed order afterwards
@@ -24,8 +25,10 @@ cudaError_t launch_simulation(const mc_params& p, const mc_portfolio* pf, const 
                               const DeviceInfo& dev, int* grid, cudaStream_t stream);
 
 // z[t, i] exactly as the simulator draws them (tests)
-cudaError_t launch_debug_shocks(const mc_params& p, const void* d_pool, void* d_out,
+cudaError_t launch_debug_shocks(const mc_params& p, const void* d_pool, const float2* d_lut, void* d_out,
                                 cudaStream_t stream);
+// fill the handle's 4096-entry (cos, sin) table of Box-Muller directions (once, at mc_create)
+cudaError_t launch_build_direction_table(float2* d_lut, cudaStream_t stream);
 cudaError_t launch_debug_philox(const uint32_t* d_ctr, uint32_t n, uint32_t k0, uint32_t k1,
                                 uint32_t* d_out, cudaStream_t stream);
 

@@ -1,0 +1,221 @@
+// mc_sim32.cuh -- the fp32 path-stepping kernel with shocks generated on the device (included by
+// mc_sim.cu after the block-reduction helpers).  This is the kernel every BASELINE config runs:
+//   NORMAL + CONST,  no store : fused GBM (configs 2, 4) -- log-price = sigma * sum of the normals
+//   NORMAL + CONST,  store    : materialised GBM paths (config 5), four paths per thread, st.global.v4
+//   BOOTSTRAP + GARCH         : the reference's own model (app.py:618-633)
+// Replaces app.py:618-633, which streams three [N] float64 arrays through memory per step.
+//
+// Shared memory holds the one table the shock source gathers from:
+//   NORMAL    : 4096 x (cos, sin) of the Box-Muller directions (32 KB, mc_rng.cuh)
+//   BOOTSTRAP : the pool as (z, alpha z^2 + beta) pairs, replicated 2^lc times so that the lanes of a
+//               half-warp (one LDS.64 wavefront) read different banks whatever indices they drew.
+//               With g = alpha z^2 + beta precomputed, the reference's step (app.py:623-633)
+//                   r = z sqrt(v);  y += r;  v = omega + alpha r^2 + beta v
+//               is   y = fma(z, sqrt(v), y);  v = fma(g, v, omega)   -- one MUFU and two FFMA.
+#pragma once
+
+namespace mc {
+
+struct Sim32Args {
+    unsigned long long n_paths, path_offset, ld_paths;
+    uint32_t n_steps, pool_len;
+    int table_lc;                  // BOOTSTRAP: log2(copies) of the shared table
+    float idx_scale, idx_bias;     // BOOTSTRAP: H 2^-23 and 2^23 - H + 1/2 (mc_rng.cuh: boot_index_bits)
+    RoundKeys rk;
+    const float2* lut;             // NORMAL: [DIR_COUNT] (cos, sin), built once per handle
+    const float* pool;             // BOOTSTRAP: [pool_len]
+    float* paths;
+    float* terminal;
+    float s0, var0, omega, alpha, beta, drift, sig;   // kernel units (log2)
+    double center;
+    BlockPartial* partials;
+};
+
+__device__ __forceinline__ float price_of(const Sim32Args& a, uint32_t steps_done, float y) {
+    return a.s0 * fast_ex2(fmaf((float)steps_done, a.drift, y));                 // app.py:629 in log2 space
+}
+
+// One Philox call's worth of steps for ONE path: K = 8 (normal) or 5 (bootstrap).  `limit` < K only in
+// the ragged last call (TAIL).  emit(k, y) sees the log-price after step k of this call.
+template <int SHOCK, int VAR, bool TAB, bool TAIL, typename Emit>
+__device__ __forceinline__ void advance(const Sim32Args& a, const u32x4& w, uint32_t table_base, int table_shift,
+                                        float sigr, int limit, float& y, float& v, Emit emit) {
+    if (SHOCK == MC_SHOCK_NORMAL) {
+        const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (TAIL && 2 * k >= limit) break;
+            float c, s;
+            direction_of(ww[k], table_base, c, s);
+            const float rs = rho20(ww[k]) * sigr;          // sigr = sqrt(2 ln 2) [* sigma]
+            if (VAR == MC_VAR_CONST) {
+                y = fmaf(rs, c, y);
+                emit(2 * k, y);
+                if (!TAIL || 2 * k + 1 < limit) { y = fmaf(rs, s, y); emit(2 * k + 1, y); }
+            } else {
+                float r = rs * c * fast_sqrt(v);                                  // app.py:623-626
+                y += r;
+                v = fmaf(a.alpha, r * r, fmaf(a.beta, v, a.omega));               // app.py:632-633
+                emit(2 * k, y);
+                if (!TAIL || 2 * k + 1 < limit) {
+                    r = rs * s * fast_sqrt(v);
+                    y += r;
+                    v = fmaf(a.alpha, r * r, fmaf(a.beta, v, a.omega));
+                    emit(2 * k + 1, y);
+                }
+            }
+        }
+    } else {
+        const uint32_t f[5] = {w.x, w.y, w.z, w.w, boot_field4(w)};
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            if (TAIL && k >= limit) break;
+            const uint32_t tb = boot_index_bits(f[k], a.idx_scale, a.idx_bias);   // bits(2^23 + idx + 1)
+            float z, g;
+            if (TAB) {
+                asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(z), "=f"(g) : "r"((tb << table_shift) + table_base));
+            } else {
+                z = __ldg(a.pool + ((tb & 0x007FFFFFu) - 1u));
+                g = fmaf(a.alpha, z * z, a.beta);
+            }
+            if (VAR == MC_VAR_CONST) {
+                y = fmaf(a.sig, z, y);
+            } else {
+                y = fmaf(z, fast_sqrt(v), y);                                     // app.py:623-629
+                v = fmaf(g, v, a.omega);                                          // app.py:632-633
+            }
+            emit(k, y);
+        }
+    }
+}
+
+// V paths per thread: 1, or 4 consecutive paths whose prices leave as one 16-byte store per step
+// (a warp then writes 512 contiguous bytes of a time-major row: measured 6.0 TB/s against 4.4 TB/s
+// for 4-byte stores at the config-5 shape, profiles/r01/microbench2_sm100a_v3.txt).
+template <int SHOCK, int VAR, bool STORE, int V, bool TAB>
+__global__ void __launch_bounds__(SHOCK == MC_SHOCK_NORMAL ? 512 : 1024) sim32_kernel(const __grid_constant__ Sim32Args a) {
+    extern __shared__ __align__(16) unsigned char smem_dyn[];
+    __shared__ BlockPartial s_warp[32];
+    constexpr int K = SHOCK == MC_SHOCK_NORMAL ? 8 : 5;
+    constexpr bool FUSED_SUM = SHOCK == MC_SHOCK_NORMAL && VAR == MC_VAR_CONST && !STORE;
+
+    uint32_t table_base = (uint32_t)__cvta_generic_to_shared(smem_dyn);
+    int table_shift = 0;
+    float2* s_tab = reinterpret_cast<float2*>(smem_dyn);
+    if (SHOCK == MC_SHOCK_NORMAL) {
+        for (int i = threadIdx.x; i < DIR_COUNT; i += blockDim.x) s_tab[i] = a.lut[i];
+    } else if (TAB) {
+        const int lc = a.table_lc;
+        for (uint32_t i = threadIdx.x; i < (a.pool_len << lc); i += blockDim.x) {
+            const float z = a.pool[i >> lc];
+            s_tab[i] = make_float2(z, fmaf(a.alpha, z * z, a.beta));
+        }
+        // entry idx of copy c sits at ((idx << lc) + c) * 8; (bits(t) << (lc+3)) = wrap + ((idx + 1) << (lc+3))
+        table_shift = lc + 3;
+        const uint32_t wrap = (uint32_t)(((unsigned long long)0x4B000000u << table_shift) & 0xFFFFFFFFull);
+        table_base += (threadIdx.x & ((1u << lc) - 1u)) * 8u - (1u << table_shift) - wrap;
+    }
+    __syncthreads();
+
+    BlockPartial acc = empty_partial();
+    const float sigr = (VAR == MC_VAR_CONST && !FUSED_SUM) ? a.sig * BM_RADIUS_SCALE_F
+                                                          : (FUSED_SUM ? 1.0f : BM_RADIUS_SCALE_F);
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x * V;
+    const uint32_t n_full = a.n_steps / K;
+    const int n_tail = (int)(a.n_steps - n_full * K);
+
+    for (unsigned long long i0 = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * V; i0 < a.n_paths;
+         i0 += stride) {
+        const bool full = V == 1 || i0 + V <= a.n_paths;          // all V paths of this thread exist
+        float y[V], v[V];
+#pragma unroll
+        for (int p = 0; p < V; ++p) { y[p] = 0.0f; v[p] = a.var0; }
+
+        auto store_row = [&](uint32_t row, const float (&px)[V]) {
+            float* dst = a.paths + (unsigned long long)row * a.ld_paths + i0;
+            if (V == 4 && full) {
+                *reinterpret_cast<float4*>(dst) = make_float4(px[0], px[1], px[2], px[3]);
+            } else {
+#pragma unroll
+                for (int p = 0; p < V; ++p)
+                    if (i0 + p < a.n_paths) dst[p] = px[p];
+            }
+        };
+        if (STORE) {
+            float px[V];
+#pragma unroll
+            for (int p = 0; p < V; ++p) px[p] = a.s0;
+            store_row(0u, px);                                     // app.py:613
+        }
+
+        uint32_t t = 0;
+        if (FUSED_SUM) {
+            // constant sigma, nothing stored: y_T = sigma sqrt(2 ln 2) * sum(rho * dir); one FFMA per normal
+            const unsigned long long gid = a.path_offset + i0;
+            const uint32_t c0 = (uint32_t)gid, c1 = (uint32_t)(gid >> 32);
+            float s = 0.0f;
+#pragma unroll 2
+            for (uint32_t j = 0; j < n_full; ++j) s = normals8_sum(philox4x32_10(c0, c1, j, 0u, a.rk), table_base, s);
+            y[0] = a.sig * BM_RADIUS_SCALE_F * s;
+            t = n_full * K;
+        } else {
+#pragma unroll 1
+            for (uint32_t j = 0; j < n_full; ++j) {
+                float px[STORE ? K : 1][V];
+#pragma unroll
+                for (int p = 0; p < V; ++p) {
+                    const unsigned long long gid = a.path_offset + i0 + p;
+                    const u32x4 w = philox4x32_10((uint32_t)gid, (uint32_t)(gid >> 32), j, 0u, a.rk);
+                    advance<SHOCK, VAR, TAB, false>(a, w, table_base, table_shift, sigr, K, y[p], v[p],
+                                                    [&](int k, float yk) { if constexpr (STORE) px[k][p] = price_of(a, t + k + 1, yk); });
+                }
+                if (STORE) {
+#pragma unroll
+                    for (int k = 0; k < K; ++k) store_row(t + k + 1, px[k]);
+                }
+                t += K;
+            }
+        }
+        if (n_tail) {      // ragged last call: n_steps not a multiple of K
+            float px[STORE ? K : 1][V];
+            const float sigr_tail = (VAR == MC_VAR_CONST) ? a.sig * BM_RADIUS_SCALE_F : BM_RADIUS_SCALE_F;
+#pragma unroll
+            for (int p = 0; p < V; ++p) {
+                const unsigned long long gid = a.path_offset + i0 + p;
+                const u32x4 w = philox4x32_10((uint32_t)gid, (uint32_t)(gid >> 32), n_full, 0u, a.rk);
+                advance<SHOCK, VAR, TAB, true>(a, w, table_base, table_shift, sigr_tail, n_tail, y[p], v[p],
+                                               [&](int k, float yk) { if constexpr (STORE) px[k][p] = price_of(a, t + k + 1, yk); });
+            }
+            if (STORE) {
+#pragma unroll
+                for (int k = 0; k < K - 1; ++k)
+                    if (k < n_tail) store_row(t + k + 1, px[k]);
+            }
+        }
+        float fin[V];
+#pragma unroll
+        for (int p = 0; p < V; ++p) fin[p] = price_of(a, a.n_steps, y[p]);
+        if (V == 4 && full) {
+            *reinterpret_cast<float4*>(a.terminal + i0) = make_float4(fin[0], fin[1], fin[2], fin[3]);   // app.py:636
+        } else {
+#pragma unroll
+            for (int p = 0; p < V; ++p)
+                if (i0 + p < a.n_paths) a.terminal[i0 + p] = fin[p];
+        }
+#pragma unroll
+        for (int p = 0; p < V; ++p)
+            if (i0 + p < a.n_paths) account<float>(acc, fin[p], a.center);
+    }
+    finish_block(acc, s_warp, a.partials);
+}
+
+// (cos, sin) of the 4096 Box-Muller directions, rounded once from fp64
+__global__ void build_direction_table_kernel(float2* lut) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= DIR_COUNT) return;
+    double s, c;
+    sincospi(2.0 * ((double)i / DIR_COUNT - 0.5), &s, &c);
+    lut[i] = make_float2((float)c, (float)s);
+}
+
+}  // namespace mc

@@ -7,14 +7,16 @@ conventions (montecarlo_b200/csrc/mc_rng.cuh) -- the reference has no counter
 based generator (it bootstraps with np.random.choice, app.py:620).
 
 Counter layout:  ctr = (path_lo, path_hi, call_index, stream), key = (seed_lo, seed_hi)
-  fp32 normals:  SIX per call (three Box-Muller pairs cut from the 128 bits):
-                 radius uniform k = 2 - bits(0x3f800000 | word_k[22:0])      k = 0,1,2
-                 angle A field = word_3 (top 23 bits used), B = byte_perm(w0,w1,0x3733),
-                 C = byte_perm(w2,w3,0x3433);  m = bits(0x3f800000 | (field >> 9))
-                 r = sqrt(-2 ln(radius uniform)), theta = 2*pi*m - 3*pi in [-pi, pi)
-                 z[2p] = r*cos(theta), z[2p+1] = r*sin(theta)   -> steps 6j..6j+5
+  fp32 normals:  EIGHT per call -- one Box-Muller pair per 32-bit word:
+                 radius uniform v1 = 1 - word[19:0] * 2^-20  in (0, 1]
+                 direction d = word[31:20] (12 bits), theta = 2*pi*(d/4096 - 1/2); the device reads
+                 (cos, sin) of it from a 4096-entry table rounded once from fp64
+                 r = sqrt(-2 ln v1);  z[2k] = r*cos(theta), z[2k+1] = r*sin(theta)   -> steps 8j..8j+7
   fp64 normals:  FOUR per call: v1 = (u+1) * 2^-32 in (0,1],  theta = 2*pi*(u2 * 2^-32) - pi
-  bootstrap   :  FOUR per call: idx = (u * H) >> 32   (mulhi)
+  fp64 bootstrap: FOUR per call: idx = (word * H) >> 32   (mulhi)
+  fp32 bootstrap (H <= 65536): FIVE per call from 23-bit fields (word_k[22:0], k = 0..3, and the top
+                 bytes of words 0,1,2): idx = bits(fl32(fma(2^23 + field, H*2^-23, 2^23 - H + 1/2)))
+                 - 0x4B000000 - 1 = floor(field*H/2^23), a tie (exact integer) rounding to even
 """
 from __future__ import annotations
 
@@ -62,38 +64,46 @@ def mantissa_float(u):
 
 
 def normals_per_call(dtype) -> int:
-    return 6 if np.dtype(dtype) == np.float32 else 4
+    return 8 if np.dtype(dtype) == np.float32 else 4
 
 
-def _byte_perm(x, y, selector):
-    """CUDA __byte_perm: result byte i = byte (selector nibble i) of the 8 bytes {x0..x3, y0..y3}."""
-    x = np.asarray(x, dtype=np.uint32).astype(np.uint64)
-    y = np.asarray(y, dtype=np.uint32).astype(np.uint64)
-    both = x | (y << np.uint64(32))
-    out = np.zeros_like(x)
-    for i in range(4):
-        sel = (selector >> (4 * i)) & 0x7
-        out |= ((both >> np.uint64(8 * sel)) & np.uint64(0xFF)) << np.uint64(8 * i)
-    return out.astype(np.uint32)
+DIR_BITS = 12
+BOOT32_MAX_POOL = 65536
 
 
-def _pair_f32(radius_word, angle_field):
-    m1 = ((np.asarray(radius_word, dtype=np.uint32) & np.uint32(0x007FFFFF)) | np.uint32(0x3F800000)).view(np.float32)
-    v1 = 2.0 - m1.astype(np.float64)
-    m2 = mantissa_float(angle_field).astype(np.float64)
-    # the device forms theta = fma(m2, 2pi_f32, -3pi_f32) in fp32; model it in fp64
-    theta = m2 * float(np.float32(2 * np.pi)) - float(np.float32(3 * np.pi))
+def direction_table():
+    """The device's (cos, sin) table: float32(cospi/sinpi(2*(d/4096 - 1/2))), d = 0..4095."""
+    d = np.arange(1 << DIR_BITS, dtype=np.float64)
+    theta = 2.0 * np.pi * (d / (1 << DIR_BITS) - 0.5)
+    c, s = np.cos(theta), np.sin(theta)
+    # exact zeros / ones where sincospi is exact (multiples of a quarter turn)
+    q = (1 << DIR_BITS) // 4
+    c[[q, 3 * q]] = 0.0
+    s[[0, 2 * q]] = 0.0
+    return c.astype(np.float32).astype(np.float64), s.astype(np.float32).astype(np.float64)
+
+
+_DIR = None
+
+
+def _pair_f32(word):
+    global _DIR
+    if _DIR is None:
+        _DIR = direction_table()
+    w = np.asarray(word, dtype=np.uint32)
+    v1 = 1.0 - (w & np.uint32(0xFFFFF)).astype(np.float64) * 2.0 ** -20
+    d = (w >> np.uint32(20)).astype(np.int64)
     r = np.sqrt(-2.0 * np.log(v1))
-    return r * np.cos(theta), r * np.sin(theta)
+    return r * _DIR[0][d], r * _DIR[1][d]
 
 
 def normals_from_words(w, dtype):
-    """All normals of one call (list of arrays): 6 for float32, 4 for float64."""
+    """All normals of one call (list of arrays): 8 for float32, 4 for float64."""
     if np.dtype(dtype) == np.float32:
-        za = _pair_f32(w[0], w[3])
-        zb = _pair_f32(w[1], _byte_perm(w[0], w[1], 0x3733))
-        zc = _pair_f32(w[2], _byte_perm(w[2], w[3], 0x3433))
-        return [za[0], za[1], zb[0], zb[1], zc[0], zc[1]]
+        out = []
+        for k in range(4):
+            out += list(_pair_f32(w[k]))
+        return out
     out = []
     for ua, ub in ((w[0], w[1]), (w[2], w[3])):
         v1 = (np.asarray(ua, dtype=np.float64) + 1.0) * 2.0 ** -32
@@ -123,16 +133,42 @@ def normal_shocks(seed: int, path_offset: int, n_paths: int, n_steps: int,
     return z[:, :n_assets]
 
 
-def bootstrap_indices(seed: int, path_offset: int, n_paths: int, n_steps: int, pool_len: int):
-    """idx[t, i] = mulhi(word, pool_len): the device's stand-in for
-    np.random.choice(std_returns, size=n_sims) (app.py:620)."""
+def indices_per_call(dtype, pool_len: int) -> int:
+    return 5 if (np.dtype(dtype) == np.float32 and pool_len <= BOOT32_MAX_POOL) else 4
+
+
+def _boot_fields(w):
+    """The five 23-bit fields of one call (fp32 kernels)."""
+    top = lambda x: (np.asarray(x, dtype=np.uint32) >> np.uint32(24)).astype(np.uint32)
+    f4 = top(w[0]) | (top(w[1]) << np.uint32(8)) | (top(w[2]) << np.uint32(16))
+    return [np.asarray(w[k], dtype=np.uint32) & np.uint32(0x7FFFFF) for k in range(4)] + [f4 & np.uint32(0x7FFFFF)]
+
+
+def _boot_index32(field, pool_len: int):
+    """floor(field*H/2^23) exactly as the device's single FFMA rounds it."""
+    g = 8388608.0 + field.astype(np.float64)                       # exact
+    scale = float(np.float32(pool_len) * np.float32(2.0 ** -23))     # exact in fp32
+    bias = float(np.float32(8388608.0 - pool_len + 0.5))             # exact in fp32
+    t = np.float32(g * scale + bias)                                 # exact in fp64, ONE rounding to fp32
+    return (t.view(np.uint32).astype(np.int64) - 0x4B000000) - 1
+
+
+def bootstrap_indices(seed: int, path_offset: int, n_paths: int, n_steps: int, pool_len: int,
+                      dtype=np.float64):
+    """idx[t, i]: the device's stand-in for np.random.choice(std_returns, size=n_sims) (app.py:620).
+    fp64 kernels: 4 per call, mulhi(word, H).  fp32 kernels: 5 per call from 23-bit fields."""
     pid = np.arange(path_offset, path_offset + n_paths, dtype=np.uint64)
-    n_calls = (n_steps + 3) // 4
-    idx = np.empty((n_calls * 4, n_paths), dtype=np.int64)
+    k = indices_per_call(dtype, pool_len)
+    n_calls = (n_steps + k - 1) // k
+    idx = np.empty((n_calls * k, n_paths), dtype=np.int64)
     for j in range(n_calls):
         w = path_words(seed, pid, j)
-        for k in range(4):
-            idx[4 * j + k] = (w[k].astype(np.uint64) * np.uint64(pool_len)) >> np.uint64(32)
+        if k == 4:
+            for q in range(4):
+                idx[4 * j + q] = (w[q].astype(np.uint64) * np.uint64(pool_len)) >> np.uint64(32)
+        else:
+            for q, f in enumerate(_boot_fields(w)):
+                idx[5 * j + q] = _boot_index32(f, pool_len)
     return idx[:n_steps]
 
 

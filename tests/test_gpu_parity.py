@@ -79,7 +79,7 @@ def test_device_bootstrap_run_matches_port(engine, dtype, n, t):
     spec = SimSpec(n_paths=n, n_steps=t, s0=s0, var0=port.initial_variance(0.02 * np.sqrt(252)), dtype=dtype,
                    seed=seed, store_paths=True, fan_chart=True, hist_bins=64)
     out = engine.simulate(spec, pool=pool)
-    idx = philox.bootstrap_indices(seed, 0, n, t, len(pool))
+    idx = philox.bootstrap_indices(seed, 0, n, t, len(pool), dtype=np.dtype(dtype))
     pool_dev = pool.astype(dtype).astype(np.float64)            # the device pool is stored in `dtype`
     ref = port.step_paths(pool_dev[idx], s0, spec.var0)
     paths = out.paths.cpu().numpy().astype(np.float64)

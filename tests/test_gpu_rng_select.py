@@ -30,8 +30,8 @@ def test_device_normals_match_bit_model(engine, dtype, tol):
     z = engine.debug_shocks(spec, path_offset=off).cpu().numpy().astype(np.float64)
     ref = philox.normal_shocks(seed, off, n, t, dtype=np.dtype(dtype))
     assert z.shape == ref.shape
-    # MUFU lg2/sqrt/sin/cos are approximate: the worst absolute error sits near z = 0 (lg2 of a
-    # uniform close to 1); on average the device normal is within 1e-6 of the fp64 bit model
+    # MUFU lg2/sqrt are approximate: the worst absolute error sits near z = 0 (lg2 of a uniform close
+    # to 1); on average the device normal is within 1e-6 of the fp64 bit model
     assert np.abs(z - ref).max() < tol
     assert np.abs(z - ref).mean() < (1e-6 if dtype == 'float32' else 1e-13)
     assert abs((z - ref).mean()) < (1e-7 if dtype == 'float32' else 1e-14)
@@ -43,7 +43,7 @@ def test_device_bootstrap_draws_match_bit_model(engine, dtype):
     pool = np.random.RandomState(1).normal(size=H)
     spec = SimSpec(n_paths=n, n_steps=t, s0=100.0, dtype=dtype, seed=seed, var0=4e-4)
     z = engine.debug_shocks(spec, pool=pool).cpu().numpy()
-    idx = philox.bootstrap_indices(seed, 0, n, t, H)
+    idx = philox.bootstrap_indices(seed, 0, n, t, H, dtype=np.dtype(dtype))
     assert np.array_equal(z, pool.astype(dtype)[idx])
 
 

@@ -88,6 +88,26 @@ def test_shard_invariance_of_the_bit_model():
     assert np.array_equal(full[:, 40:], part)
     idx = philox.bootstrap_indices(5, 0, 1000, 7, 1250)
     assert idx.min() >= 0 and idx.max() < 1250
+    assert np.array_equal(idx[:, 300:], philox.bootstrap_indices(5, 300, 700, 7, 1250))
+
+
+def test_fp32_bootstrap_index_is_the_exact_floor():
+    # the fp32 kernels compute floor(field * H / 2^23) with one FFMA (mc_rng.cuh: boot_index_bits);
+    # the model must equal the integer floor except on exact ties (field*H a multiple of 2^23)
+    rs = np.random.RandomState(0)
+    for h in (100, 1250, 1051, 4096, 65536):
+        f = rs.randint(0, 1 << 23, size=200_000).astype(np.uint32)
+        f[:4] = [0, 1, (1 << 23) - 1, 1 << 22]
+        exact = (f.astype(np.int64) * h) >> 23
+        got = philox._boot_index32(f, h)
+        tie = (f.astype(np.int64) * h) % (1 << 23) == 0
+        assert np.array_equal(got[~tie], exact[~tie])
+        assert np.all((got[tie] == exact[tie]) | (got[tie] == exact[tie] - 1))
+        assert got.min() >= -1 and got.max() < h
+    idx = philox.bootstrap_indices(5, 0, 20_000, 10, 1250, dtype=np.float32)
+    assert idx.min() >= 0 and idx.max() < 1250
+    counts = np.bincount(idx.ravel(), minlength=1250)
+    assert abs(counts.std() / np.sqrt(counts.mean()) - 1) < 0.1       # multinomial spread
 
 
 def test_gbm_closed_form():

@@ -5,7 +5,7 @@
 #include <cstdio>
 #include <cstdint>
 #include <cuda_runtime.h>
-#include "../montecarlo_b200/csrc/mc_rng.cuh"
+#include "rng_variants.cuh"
 
 using namespace mc;
 constexpr int ITERS = 4096;
