@@ -78,6 +78,8 @@ struct mc_handle {
     DevBuf<unsigned long long> stage;   // internal stage buffer (mc_run, mc_percentiles)
     PinnedBuf<unsigned char> h_stage;   // pinned staging for the D2H of results
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t ev_pending = nullptr;   // recorded after the D2H copy of `pending`
+    bool pending_unchecked = false;     // closing was enqueued before the host looked at `pending`
 
     // state of the run in flight
     bool active = false;
@@ -213,6 +215,7 @@ int mc_create(int device_ordinal, mc_handle** out) {
               h->lut.reserve(4096) == cudaSuccess && launch_build_direction_table(h->lut.p, nullptr) == cudaSuccess &&
               cudaStreamSynchronize(nullptr) == cudaSuccess;
     for (int i = 0; i < 3 && ok; ++i) ok = cudaEventCreate(&h->ev[i]) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&h->ev_pending, cudaEventDisableTiming) == cudaSuccess;
     if (!ok) {
         e = cudaGetLastError();
         mc_destroy(h);
@@ -229,6 +232,7 @@ int mc_destroy(mc_handle* h) {
     h->pct_t.release(); h->fan.release(); h->tail_scratch.release(); h->edges.release(); h->hist_total.release();
     h->stage.release(); h->h_stage.release(); h->pending.release(); h->h_pending.release();
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
+    if (h->ev_pending) cudaEventDestroy(h->ev_pending);
     delete h;
     return MC_OK;
 }
@@ -260,6 +264,7 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
     h->launches = 0;
     h->phase = 0;
     h->pass_idx = 0;
+    h->pending_unchecked = false;
     h->d_terminal = d_terminal;
     h->has_t = p->n_pcts > 0 && !(p->flags & MC_FLAG_NO_TERMINAL_SELECT);
     h->has_f = (p->flags & MC_FLAG_FAN_CHART) && p->n_path_pcts > 0;
@@ -379,6 +384,17 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
     *done = 0;
 
     if (h->phase == 2) {                      // gathered = final stage
+        if (h->pending_unchecked) {
+            // The closing stage was enqueued right behind the second narrowing pass without waiting for
+            // the device's "rows still undecided" counter (identical on every rank).  It has long arrived.
+            h->pending_unchecked = false;
+            MC_CUDA(h, cudaEventSynchronize(h->ev_pending));
+            if (*h->h_pending.p != 0) {       // a bracket missed or a heavy tie: narrow again, then close again
+                if (h->pass_idx >= SEL_MAX_PASSES) return fail(h, MC_ERR_STATE, "selection did not converge");
+                h->phase = 1;
+                return enqueue_pass(h, out, s);
+            }
+        }
         MC_CUDA(h, launch_merge_final(g, n_ranks, stride, p.hist_bins, h->res.p, h->hist_total.p, s));
         h->launches += 1;
         MC_CUDA(h, cudaEventRecord(h->ev[2], s));
@@ -413,15 +429,11 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
         MC_CUDA(h, launch_select_scan(h->prob_f, g + L.off_f, n_ranks, stride, h->pending.p, s));
         h->launches += 1;
     }
-    bool more = true;
-    if (h->pass_idx >= 2) {
-        // the second pass normally decides everything; ask the device (same answer on every rank)
-        MC_CUDA(h, cudaMemcpyAsync(h->h_pending.p, h->pending.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
-        MC_CUDA(h, cudaStreamSynchronize(s));
-        more = *h->h_pending.p != 0;
-        if (more && h->pass_idx >= SEL_MAX_PASSES) return fail(h, MC_ERR_STATE, "selection did not converge");
-    }
-    if (more) return enqueue_pass(h, out, s);
+    if (h->pass_idx < 2) return enqueue_pass(h, out, s);
+    // the second pass normally decides everything: go on to the closing stage and look at the counter later
+    MC_CUDA(h, cudaMemcpyAsync(h->h_pending.p, h->pending.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
+    MC_CUDA(h, cudaEventRecord(h->ev_pending, s));
+    h->pending_unchecked = true;
     return enqueue_closing(h, out, s);
 }
 

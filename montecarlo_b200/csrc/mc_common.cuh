@@ -19,8 +19,13 @@ constexpr int SEL_SAMPLE_MAX_F64 = 16384;       // ... fp64 keys (sorted in shar
 constexpr int SEL_MAX_PASSES = 12;              // hard stop of the narrowing loop (never reached: 64 bits / 10 + miss)
 
 // ---- order-preserving integer keys ------------------------------------------------
-// key(a) < key(b)  <=>  a < b  for all non-NaN floats (negative portfolio values included)
+// key(a) < key(b)  <=>  a < b  for all non-NaN floats (negative portfolio values included);
+// -0.0 is folded onto +0.0 (v + 0.0 in round-to-nearest) so that key order and IEEE comparison
+// agree everywhere -- the fp32 selection passes compare floats, the scans compare keys.
+constexpr uint32_t KEY32_NEG_INF = 0x007FFFFFu;   // key_of(-inf)
+constexpr uint32_t KEY32_POS_INF = 0xFF800000u;   // key_of(+inf)
 __host__ __device__ __forceinline__ uint32_t key_of(float v) {
+    v = v + 0.0f;
 #ifdef __CUDA_ARCH__
     const uint32_t b = __float_as_uint(v);
 #else
@@ -29,6 +34,7 @@ __host__ __device__ __forceinline__ uint32_t key_of(float v) {
     return b ^ ((b >> 31) ? 0xFFFFFFFFu : 0x80000000u);
 }
 __host__ __device__ __forceinline__ uint64_t key_of(double v) {
+    v = v + 0.0;
 #ifdef __CUDA_ARCH__
     const uint64_t b = (uint64_t)__double_as_longlong(v);
 #else

@@ -355,6 +355,212 @@ __global__ void __launch_bounds__(256) select_pass_kernel(const Real* __restrict
     }
 }
 
+// ------------------------------------------------------------------ fp32 narrowing passes
+// The generic pass above spends ~40 issue slots and one shared-memory read per value (2.0 TB/s on the
+// 17 GB fan-chart problem of BASELINE config 5).  fp32 rows get two leaner kernels whose hot loop has
+// no memory operand besides the streaming load:
+//   pass 1  bracket bounds live in registers AS FLOATS.  Per value and bracket: one compare, one
+//           predicated count (the exact population at or above the bracket's lower bound) and one select
+//           that carries the upper bound of the last bracket entered; `v <= that bound` then means "inside
+//           a bracket" and only those values (a few percent) touch shared memory.  IEEE order equals key
+//           order because key_of folds -0.0 onto +0.0.
+//   pass 2  `below` is known and the intervals are 1/1024 of a bracket wide: a byte map over <= 2048
+//           coarse key bins (one LDS.U8) rejects ~98 % of the values; the rest take the exact path.
+constexpr int FAST_THREADS = 256;
+constexpr int MAP_BINS_LOG2 = 11;
+constexpr int MAP_BYTES = (1 << MAP_BINS_LOG2) + 64;
+
+struct FastRow {
+    const uint32_t* s_lo; const uint32_t* s_hi; const int* s_shift; const int* s_mode;
+    unsigned int* s_bins; unsigned int* out_iv; size_t iv_slot; int n_iv;
+};
+
+// exact treatment of one value that may lie inside an interval
+__device__ __forceinline__ void fast_member(const FastRow& c, uint32_t key) {
+    int a = 0, b = c.n_iv;                     // j = #(lo[g] <= key), lo ascending
+    while (a < b) { const int mid = (a + b) >> 1; if (c.s_lo[mid] <= key) a = mid + 1; else b = mid; }
+    const int g = a - 1;
+    if (g < 0 || key > c.s_hi[g]) return;
+    const uint32_t off = key - c.s_lo[g];
+    if (c.s_mode[g] == IV_HIST) {
+        atomicAdd(&c.s_bins[g * SEL_BINS + (off >> c.s_shift[g])], 1u);
+    } else {
+        unsigned int* slot = c.out_iv + (size_t)g * c.iv_slot;
+        const unsigned int idx = atomicAdd(slot, 1u);
+        if (idx < (unsigned int)SEL_CAND) slot[2 + idx] = key;
+    }
+}
+
+// stream one block's share [beg, end) of a row through f(value); 16-byte loads when the row allows it
+template <typename F>
+__device__ __forceinline__ void fast_stream(const float* __restrict__ xr, unsigned long long beg, unsigned long long end,
+                                            bool vec, F f) {
+    const int tid = threadIdx.x;
+    if (vec) {       // beg is a multiple of 4 and xr + beg is 16-byte aligned
+        const float4* x4 = reinterpret_cast<const float4*>(xr + beg);
+        const unsigned long long n4 = (end - beg) >> 2;
+        unsigned long long i = tid;
+        for (; i + 3ull * FAST_THREADS < n4; i += 4ull * FAST_THREADS) {
+            float4 q[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) q[u] = __ldcs(x4 + i + (unsigned long long)u * FAST_THREADS);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { f(q[u].x); f(q[u].y); f(q[u].z); f(q[u].w); }
+        }
+        for (; i < n4; i += FAST_THREADS) { const float4 q = __ldcs(x4 + i); f(q.x); f(q.y); f(q.z); f(q.w); }
+        for (unsigned long long k = beg + (n4 << 2) + tid; k < end; k += FAST_THREADS) f(xr[k]);
+    } else {
+        unsigned long long i = beg + tid;
+        for (; i + 7ull * FAST_THREADS < end; i += 8ull * FAST_THREADS) {
+            float q[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) q[u] = xr[i + (unsigned long long)u * FAST_THREADS];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) f(q[u]);
+        }
+        for (; i < end; i += FAST_THREADS) f(xr[i]);
+    }
+}
+
+__device__ __forceinline__ void fast_block_range(unsigned long long n, unsigned long long* beg, unsigned long long* end) {
+    unsigned long long per = (n + gridDim.x - 1) / gridDim.x;
+    per = (per + 1023ull) & ~1023ull;                         // keeps every block's start 16-byte aligned
+    *beg = (unsigned long long)blockIdx.x * per;
+    *end = *beg + per < n ? *beg + per : n;
+    if (*beg > n) *beg = n;
+}
+
+template <int NB>
+__global__ void __launch_bounds__(FAST_THREADS) select_pass1_f32_kernel(const float* __restrict__ x, unsigned long long ld,
+                                                                        unsigned long long n, int vec,
+                                                                        const RowSel* __restrict__ states,
+                                                                        unsigned int* __restrict__ out, size_t row_slot,
+                                                                        size_t iv_slot, int n_iv_cap) {
+    extern __shared__ unsigned int s_bins[];
+    __shared__ uint32_t s_lo[MAX_IV], s_hi[MAX_IV];
+    __shared__ int s_shift[MAX_IV], s_mode[MAX_IV];
+    const unsigned long long row = blockIdx.y;
+    const RowSel& st = states[row];
+    const int n_iv = st.n_iv;
+    if (n_iv == 0) return;
+    const int tid = threadIdx.x;
+    if (tid < n_iv) {
+        s_lo[tid] = (uint32_t)st.lo[tid]; s_hi[tid] = (uint32_t)st.hi[tid];
+        s_shift[tid] = st.shift[tid]; s_mode[tid] = IV_HIST;
+    }
+    for (int i = tid; i < n_iv * SEL_BINS; i += FAST_THREADS) s_bins[i] = 0u;
+    __syncthreads();
+
+    unsigned int* out_row = out + row * row_slot;
+    FastRow c{s_lo, s_hi, s_shift, s_mode, s_bins, out_row + 2 * (size_t)n_iv_cap, iv_slot, n_iv};
+    float lo_f[NB], hi_f[NB], cnt[NB];      // per-thread counts stay below 2^24: exact in fp32
+#pragma unroll
+    for (int g = 0; g < NB; ++g) {
+        const bool used = g < n_iv;
+        const uint32_t kl = used ? s_lo[g] : 0u, kh = used ? s_hi[g] : 0u;
+        lo_f[g] = used ? value_of(kl < KEY32_NEG_INF ? KEY32_NEG_INF : kl) : __int_as_float(0x7FC00000);   // NaN: never >=
+        hi_f[g] = value_of(kh > KEY32_POS_INF ? KEY32_POS_INF : (kh < KEY32_NEG_INF ? KEY32_NEG_INF : kh));
+        cnt[g] = 0.0f;
+    }
+    unsigned long long beg, end;
+    fast_block_range(n, &beg, &end);
+    fast_stream(x + row * ld, beg, end, vec != 0, [&](float v) {
+        float top = -INFINITY;                       // upper bound of the last bracket whose lower bound v reached
+#pragma unroll
+        for (int g = 0; g < NB; ++g) {
+            // compare once; count on the FMA pipe (predicated FADD), carry the bound on the ALU pipe (FSEL)
+            asm("{\n\t.reg .pred p;\n\tsetp.ge.f32 p, %2, %3;\n\t@p add.f32 %0, %0, 0f3F800000;\n\tselp.f32 %1, %4, %1, p;\n\t}"
+                : "+f"(cnt[g]), "+f"(top) : "f"(v), "f"(lo_f[g]), "f"(hi_f[g]));
+        }
+        if (v <= top) fast_member(c, key_of(v));
+    });
+
+    unsigned long long* out_ge = reinterpret_cast<unsigned long long*>(out_row);
+#pragma unroll
+    for (int g = 0; g < NB; ++g) {
+        const unsigned int total = __reduce_add_sync(0xffffffffu, (unsigned int)cnt[g]);
+        if ((tid & 31) == 0 && g < n_iv && total) atomicAdd(&out_ge[g], (unsigned long long)total);
+    }
+    __syncthreads();
+    for (int i = tid; i < n_iv * SEL_BINS; i += FAST_THREADS) {
+        const unsigned int v = s_bins[i];
+        if (v) atomicAdd(&c.out_iv[(size_t)(i >> SEL_BIN_BITS) * iv_slot + 2 + (i & (SEL_BINS - 1))], v);
+    }
+}
+
+__global__ void __launch_bounds__(FAST_THREADS) select_pass2_f32_kernel(const float* __restrict__ x, unsigned long long ld,
+                                                                        unsigned long long n, int vec,
+                                                                        const RowSel* __restrict__ states,
+                                                                        unsigned int* __restrict__ out, size_t row_slot,
+                                                                        size_t iv_slot, int n_iv_cap) {
+    extern __shared__ unsigned int s_bins[];
+    __shared__ uint32_t s_lo[MAX_IV], s_hi[MAX_IV];
+    __shared__ int s_shift[MAX_IV], s_mode[MAX_IV];
+    __shared__ unsigned char s_map[MAP_BYTES];
+    const unsigned long long row = blockIdx.y;
+    const RowSel& st = states[row];
+    const int n_iv = st.n_iv;
+    if (n_iv == 0) return;
+    const int tid = threadIdx.x;
+    if (tid < n_iv) {
+        s_lo[tid] = (uint32_t)st.lo[tid]; s_hi[tid] = (uint32_t)st.hi[tid];
+        s_shift[tid] = st.shift[tid]; s_mode[tid] = st.mode[tid];
+    }
+    for (int i = tid; i < n_iv * SEL_BINS; i += FAST_THREADS) s_bins[i] = 0u;
+    for (int i = tid; i < MAP_BYTES; i += FAST_THREADS) s_map[i] = 0;
+    __syncthreads();
+    const uint32_t k0 = s_lo[0], k1 = s_hi[n_iv - 1];
+    const int cs = max(0, bit_length((unsigned long long)(k1 - k0)) - MAP_BINS_LOG2);
+    const uint32_t base = k0 >> cs;
+    if (tid < n_iv)
+        for (uint32_t b = (s_lo[tid] >> cs) - base; b <= (s_hi[tid] >> cs) - base; ++b) s_map[b] = 1;   // b <= 2048
+    __syncthreads();
+
+    unsigned int* out_row = out + row * row_slot;
+    FastRow c{s_lo, s_hi, s_shift, s_mode, s_bins, out_row + 2 * (size_t)n_iv_cap, iv_slot, n_iv};
+    unsigned long long beg, end;
+    fast_block_range(n, &beg, &end);
+    fast_stream(x + row * ld, beg, end, vec != 0, [&](float v) {
+        const uint32_t key = key_of(v);
+        const uint32_t idx = min((key >> cs) - base, (uint32_t)(MAP_BYTES - 1));     // keys below k0 wrap: clamped too
+        if (s_map[idx]) fast_member(c, key);
+    });
+    __syncthreads();
+    for (int i = tid; i < n_iv * SEL_BINS; i += FAST_THREADS) {
+        const unsigned int v = s_bins[i];
+        if (v) atomicAdd(&c.out_iv[(size_t)(i >> SEL_BIN_BITS) * iv_slot + 2 + (i & (SEL_BINS - 1))], v);
+    }
+}
+
+template <typename K>
+static cudaError_t launch_fast(K k, const SelectProblem& sp, void* d_out, int n_iv_smem, dim3 grid, cudaStream_t stream) {
+    const size_t smem = (size_t)n_iv_smem * SEL_BINS * sizeof(unsigned int);
+    if (smem > 40 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    const float* x = static_cast<const float*>(sp.x);
+    const int vec = (sp.ld % 4 == 0 && ((uintptr_t)x & 15u) == 0) ? 1 : 0;
+    k<<<grid, FAST_THREADS, smem, stream>>>(x, sp.ld, sp.n, vec, sp.d_states, static_cast<unsigned int*>(d_out),
+                                            row_slot_u32(sp.dtype, sp.plan.n_targets), iv_slot_u32(sp.dtype),
+                                            sp.plan.n_targets);
+    return cudaGetLastError();
+}
+
+static cudaError_t launch_pass_f32(const SelectProblem& sp, bool first, void* d_out, int sm_count, cudaStream_t s) {
+    // one row: two blocks per SM stream it; many rows: ~8 resident blocks per SM in total, whole chunks of 4 KB
+    unsigned long long chunks = sp.rows == 1 ? 2ull * sm_count : ((unsigned long long)sm_count * 8 + sp.rows - 1) / sp.rows;
+    const unsigned long long max_chunks = (sp.n + 4095ull) / 4096ull;
+    if (chunks > max_chunks) chunks = max_chunks;
+    if (chunks < 1) chunks = 1;
+    dim3 grid((unsigned)chunks, (unsigned)sp.rows);
+    const int np_ = sp.plan.n_pcts;
+    if (!first) return launch_fast(select_pass2_f32_kernel, sp, d_out, sp.plan.n_targets, grid, s);
+    if (np_ <= 5) return launch_fast(select_pass1_f32_kernel<5>, sp, d_out, np_, grid, s);
+    if (np_ <= 9) return launch_fast(select_pass1_f32_kernel<9>, sp, d_out, np_, grid, s);
+    return launch_fast(select_pass1_f32_kernel<16>, sp, d_out, np_, grid, s);
+}
+
 template <typename Real, int NIV>
 static cudaError_t launch_pass_t(const SelectProblem& sp, void* d_out, int n_iv_smem, dim3 grid, cudaStream_t stream) {
     auto k = select_pass_kernel<Real, NIV>;
@@ -384,6 +590,7 @@ cudaError_t launch_select_pass(const SelectProblem& sp, bool first_pass, void* d
     if (sp.rows > 65535) return cudaErrorInvalidValue;
     cudaError_t e = cudaMemsetAsync(d_out, 0, pass_words(sp) * sizeof(unsigned long long), stream);
     if (e != cudaSuccess || sp.n == 0) return e;
+    if (sp.dtype == MC_F32) return launch_pass_f32(sp, first_pass, d_out, sm_count, stream);
     unsigned long long chunks = ((unsigned long long)sm_count * 16 + sp.rows - 1) / sp.rows;
     const unsigned long long max_chunks = (sp.n + 256ull * PASS_UNROLL - 1) / (256ull * PASS_UNROLL);
     if (chunks > max_chunks) chunks = max_chunks;

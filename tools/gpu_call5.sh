@@ -1,0 +1,6 @@
+set -x
+for wl in c2 c5; do
+  timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_$wl.csv \
+      python bench.py --steps 2 --warmup 3 --no-extras --workload $wl > gpurun_out/ncu_$wl.log 2>&1
+  echo ncu-launches $wl rc=$?
+done
