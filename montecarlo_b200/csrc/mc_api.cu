@@ -68,6 +68,7 @@ struct mc_handle {
     DevBuf<DeviceResult> res;
     DevBuf<SelectPlan> plans;           // [2]: terminal, fan
     DevBuf<RowSel> states_t, states_f;
+    DevBuf<ScanScratch> scratch_t, scratch_f;
     DevBuf<unsigned int> pending;       // [1] rows with undecided targets after the latest scan
     PinnedBuf<unsigned int> h_pending;
     DevBuf<double> pct_t;               // [3 * MC_MAX_PCTS]
@@ -210,6 +211,7 @@ int mc_create(int device_ordinal, mc_handle** out) {
     h->dev.max_smem_optin = (int)prop.sharedMemPerBlockOptin;
     bool ok = h->partials.reserve(MAX_SIM_GRID) == cudaSuccess && h->res.reserve(1) == cudaSuccess &&
               h->plans.reserve(2) == cudaSuccess && h->states_t.reserve(1) == cudaSuccess &&
+              h->scratch_t.reserve(1) == cudaSuccess &&
               h->pct_t.reserve(3 * MC_MAX_PCTS) == cudaSuccess && h->tail_scratch.reserve(2 * 1024) == cudaSuccess &&
               h->pending.reserve(1) == cudaSuccess && h->h_pending.reserve(1) == cudaSuccess &&
               h->lut.reserve(4096) == cudaSuccess && launch_build_direction_table(h->lut.p, nullptr) == cudaSuccess &&
@@ -228,7 +230,7 @@ int mc_create(int device_ordinal, mc_handle** out) {
 int mc_destroy(mc_handle* h) {
     if (!h) return MC_OK;
     cudaSetDevice(h->device);
-    h->partials.release(); h->lut.release(); h->res.release(); h->plans.release(); h->states_t.release(); h->states_f.release();
+    h->partials.release(); h->lut.release(); h->res.release(); h->plans.release(); h->states_t.release(); h->states_f.release(); h->scratch_t.release(); h->scratch_f.release();
     h->pct_t.release(); h->fan.release(); h->tail_scratch.release(); h->edges.release(); h->hist_total.release();
     h->stage.release(); h->h_stage.release(); h->pending.release(); h->h_pending.release();
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
@@ -274,7 +276,7 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
         if (!build_select_plan(p->pcts, (int)p->n_pcts, p->n_paths_global, p->dtype, &h->prob_t.plan))
             return fail(h, MC_ERR_INVALID, "percentiles must be ascending and within [0, 100]");
         h->prob_t.x = d_terminal; h->prob_t.dtype = p->dtype; h->prob_t.rows = 1; h->prob_t.n = p->n_paths;
-        h->prob_t.ld = p->n_paths; h->prob_t.d_states = h->states_t.p;
+        h->prob_t.ld = p->n_paths; h->prob_t.d_states = h->states_t.p; h->prob_t.d_scratch = h->scratch_t.p;
         setup_sampling(h->prob_t, R, true);            // paths are iid: the first values are a random sample
         if ((rc = upload_plan(h, h->prob_t, 0, s))) return rc;
         if (p->tail_pct >= 0.0) {
@@ -288,9 +290,11 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
         const size_t rows = (size_t)p->n_steps + 1;
         if (rows > 65535) return fail(h, MC_ERR_INVALID, "fan chart supports at most 65534 steps");
         MC_CUDA(h, h->states_f.reserve(rows));
+        MC_CUDA(h, h->scratch_f.reserve(rows));
         MC_CUDA(h, h->fan.reserve(rows * p->n_path_pcts));
         h->prob_f.x = d_paths; h->prob_f.dtype = p->dtype; h->prob_f.rows = rows; h->prob_f.n = p->n_paths;
         h->prob_f.ld = p->paths_ld ? p->paths_ld : p->n_paths; h->prob_f.d_states = h->states_f.p;
+        h->prob_f.d_scratch = h->scratch_f.p;
         setup_sampling(h->prob_f, R, true);
         if ((rc = upload_plan(h, h->prob_f, 1, s))) return rc;
     }
@@ -555,8 +559,10 @@ int mc_percentiles(mc_handle* h, const void* d_x, int32_t dtype, uint64_t rows, 
     sp.x = d_x; sp.dtype = dtype; sp.rows = rows; sp.n = n; sp.ld = ld;
     setup_sampling(sp, 1, false);                      // arbitrary data: strided sample
     MC_CUDA(h, h->states_f.reserve(rows));
+    MC_CUDA(h, h->scratch_f.reserve(rows));
     MC_CUDA(h, h->fan.reserve(rows * n_pcts));
     sp.d_states = h->states_f.p;
+    sp.d_scratch = h->scratch_f.p;
     int rc = upload_plan(h, sp, 1, s);
     if (rc) return rc;
     const size_t w0 = STAGE0_HEADER + sample_words(sp), wk = pass_words(sp);

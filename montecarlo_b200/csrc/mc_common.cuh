@@ -119,4 +119,11 @@ struct RowSel {
     unsigned long long key[MAX_TARGETS];        // decided key of target j
 };
 
+// what the per-interval scan blocks hand to the per-row assembly (mc_select.cu)
+struct ScanScratch {
+    unsigned long long below[MAX_IV], total[MAX_IV];
+    unsigned long long nlo[MAX_TARGETS], nhi[MAX_TARGETS], nbelow[MAX_TARGETS], npop[MAX_TARGETS];
+    int code[MAX_TARGETS];
+};
+
 }  // namespace mc

@@ -633,168 +633,185 @@ cudaError_t launch_select_pass(const SelectProblem& sp, bool first_pass, void* d
 }
 
 // ------------------------------------------------------------------ scan: shrink every target's interval
-// One block of 1024 threads per row.  Intervals are visited in key order; a histogrammed
-// interval is prefix-summed over its 1024 bins (summed over ranks), a collected one is
-// sorted.  Each target then moves to the bin that holds its rank, is decided outright
-// (single-key bin, or position in the sorted candidates), or -- when its bracket missed --
-// moves to the gap beside the interval, whose population below is known exactly.
+// Two kernels.  (1) One block of 1024 threads per (row, interval): a histogrammed interval is prefix-summed
+// over its 1024 bins (summed over ranks), a collected one is sorted; each target of the interval then moves
+// to the bin that holds its rank, is decided outright (single-key bin, or position in the sorted
+// candidates), or -- when its bracket missed -- is flagged for the gap beside the interval.  (2) One thread
+// per row assembles the next RowSel: gaps get their exact population below from the neighbours' totals.
 constexpr int SCAN_THREADS = 1024;
 constexpr unsigned long long POP_UNKNOWN = ~0ull;
+enum { SC_NONE = 0, SC_BIN = 1, SC_DONE = 2, SC_GAP_LOW = 3, SC_GAP_HIGH = 4 };
 
 template <typename Key>
-__global__ void __launch_bounds__(SCAN_THREADS) select_scan_kernel(const SelectPlan* __restrict__ plan,
-                                                                   const unsigned int* __restrict__ g,
-                                                                   unsigned int n_ranks, size_t rank_stride_u32,
-                                                                   size_t row_slot, size_t iv_slot, int n_iv_cap,
-                                                                   RowSel* __restrict__ states,
-                                                                   unsigned int* __restrict__ pending) {
+__global__ void __launch_bounds__(SCAN_THREADS) select_scan_iv_kernel(const SelectPlan* __restrict__ plan,
+                                                                      const unsigned int* __restrict__ g,
+                                                                      unsigned int n_ranks, size_t rank_stride_u32,
+                                                                      size_t row_slot, size_t iv_slot, int n_iv_cap,
+                                                                      const RowSel* __restrict__ states,
+                                                                      ScanScratch* __restrict__ scratch) {
     __shared__ unsigned long long s_cum[SEL_BINS];
     __shared__ unsigned long long s_keys[SEL_CAND];
     __shared__ unsigned long long s_warp[SCAN_THREADS / 32];
-    __shared__ unsigned long long s_total[MAX_IV];
-    __shared__ unsigned long long s_nlo[MAX_TARGETS], s_nhi[MAX_TARGETS], s_nbelow[MAX_TARGETS], s_npop[MAX_TARGETS];
-    __shared__ int s_ndone[MAX_TARGETS];
-    __shared__ RowSel s_st, s_new;
     const unsigned long long row = blockIdx.x;
-    if (states[row].n_iv == 0) return;
+    const int gi = blockIdx.y;
+    const RowSel& st = states[row];
+    if (gi >= st.n_iv) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    {
-        const unsigned int* src = reinterpret_cast<const unsigned int*>(&states[row]);
-        unsigned int* dst = reinterpret_cast<unsigned int*>(&s_st);
-        for (int i = tid; i < (int)(sizeof(RowSel) / 4); i += SCAN_THREADS) dst[i] = src[i];
-    }
-    __syncthreads();
-    const int nt = plan->n_targets, n_iv = s_st.n_iv;
+    const int nt = plan->n_targets;
     const unsigned int* grow = g + row * row_slot;
-    if (!s_st.below_known && tid < n_iv) {
+    unsigned long long below = st.below[gi];
+    if (!st.below_known) {           // first scan: the pass counted the values at or above each lower bound
         unsigned long long ge = 0;
         for (unsigned int r = 0; r < n_ranks; ++r)
-            ge += reinterpret_cast<const unsigned long long*>(grow + r * rank_stride_u32)[tid];
-        s_st.below[tid] = plan->n_global - ge;
+            ge += reinterpret_cast<const unsigned long long*>(grow + r * rank_stride_u32)[gi];
+        below = plan->n_global - ge;
     }
-    __syncthreads();
-
-    for (int gi = 0; gi < n_iv; ++gi) {
-        const int mode = s_st.mode[gi];
-        const unsigned int* slot0 = grow + 2 * (size_t)n_iv_cap + (size_t)gi * iv_slot;
-        unsigned long long total;
-        if (mode == IV_HIST) {
-            unsigned long long c = 0;
-            for (unsigned int r = 0; r < n_ranks; ++r) c += slot0[r * rank_stride_u32 + 2 + tid];
-            unsigned long long incl = c;
+    const int mode = st.mode[gi];
+    const unsigned int* slot0 = grow + 2 * (size_t)n_iv_cap + (size_t)gi * iv_slot;
+    unsigned long long total;
+    if (mode == IV_HIST) {
+        unsigned long long c = 0;
+        for (unsigned int r = 0; r < n_ranks; ++r) c += slot0[r * rank_stride_u32 + 2 + tid];
+        unsigned long long incl = c;
 #pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
-                if (lane >= d) incl += o;
-            }
-            if (lane == 31) s_warp[warp] = incl;
-            __syncthreads();
-            unsigned long long off = 0;
-            for (int w = 0; w < warp; ++w) off += s_warp[w];
-            s_cum[tid] = off + incl;
-            __syncthreads();
-            total = s_cum[SEL_BINS - 1];
-        } else {
-            unsigned int base = 0, cnt_all = 0;
-            for (unsigned int r = 0; r < n_ranks; ++r) {
-                const unsigned int* slot = slot0 + r * rank_stride_u32;
-                unsigned int cr = slot[0];
-                if (cr > (unsigned int)SEL_CAND) cr = SEL_CAND;
-                if ((unsigned int)tid < cr && base + tid < (unsigned int)SEL_CAND)
-                    s_keys[base + tid] = (unsigned long long)reinterpret_cast<const Key*>(slot + 2)[tid];
-                base += cr;
-            }
-            cnt_all = base < (unsigned int)SEL_CAND ? base : SEL_CAND;
-            int P = 1;
-            while (P < (int)cnt_all) P <<= 1;
-            if (tid >= (int)cnt_all && tid < P) s_keys[tid] = ~0ull;
-            __syncthreads();
-            for (int k = 2; k <= P; k <<= 1) {
-                for (int j = k >> 1; j > 0; j >>= 1) {
-                    const int ixj = tid ^ j;
-                    if (tid < P && ixj > tid) {
-                        const unsigned long long a = s_keys[tid], b = s_keys[ixj];
-                        const bool up = (tid & k) == 0;
-                        if ((a > b) == up) { s_keys[tid] = b; s_keys[ixj] = a; }
-                    }
-                    __syncthreads();
-                }
-            }
-            total = cnt_all;
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += o;
         }
-        if (tid == 0) s_total[gi] = total;
-        if (tid < nt && s_st.target_iv[tid] == gi) {
-            const unsigned long long rank = plan->rank[tid], below = s_st.below[gi];
-            const unsigned long long lo = s_st.lo[gi], hi = s_st.hi[gi];
-            s_ndone[tid] = 0;
-            s_npop[tid] = POP_UNKNOWN;
-            if (rank < below) {                      // bracket missed: the value lies in the gap below
-                const bool first = gi == 0;
-                s_nlo[tid] = first ? 0ull : s_st.hi[gi - 1] + 1ull;
-                s_nhi[tid] = lo - 1ull;
-                s_nbelow[tid] = first ? 0ull : s_st.below[gi - 1] + s_total[gi - 1];
-            } else if (rank - below >= total) {      // ... in the gap above
-                s_nlo[tid] = hi + 1ull;
-                s_nhi[tid] = gi + 1 < n_iv ? s_st.lo[gi + 1] - 1ull : (unsigned long long)key_max<Key>();
-                s_nbelow[tid] = below + total;
-            } else if (mode == IV_HIST) {
-                const unsigned long long r = rank - below;
-                int a = 0, b = SEL_BINS - 1;          // first bin with cum > r
-                while (a < b) { const int mid = (a + b) >> 1; if (s_cum[mid] > r) b = mid; else a = mid + 1; }
-                const int sh = s_st.shift[gi];
-                const unsigned long long before = a ? s_cum[a - 1] : 0ull;
-                const unsigned long long nlo = lo + ((unsigned long long)a << sh);
-                const unsigned long long span = (1ull << sh) - 1ull;
-                s_nlo[tid] = nlo;
-                s_nhi[tid] = (hi - nlo < span) ? hi : nlo + span;
-                s_nbelow[tid] = below + before;
-                s_npop[tid] = s_cum[a] - before;
-                s_ndone[tid] = s_nlo[tid] == s_nhi[tid];
-            } else {
-                s_nlo[tid] = s_nhi[tid] = s_keys[rank - below];
-                s_ndone[tid] = 1;
-            }
-        }
+        if (lane == 31) s_warp[warp] = incl;
         __syncthreads();
-    }
-
-    if (tid == 0) {
-        int n_new = 0;
-        for (int j = 0; j < nt; ++j) {
-            s_new.key[j] = s_st.key[j];
-            if (s_st.target_iv[j] < 0) { s_new.target_iv[j] = -1; continue; }
-            if (s_ndone[j]) { s_new.key[j] = s_nlo[j]; s_new.target_iv[j] = -1; continue; }
-            if (!(n_new && s_new.lo[n_new - 1] == s_nlo[j] && s_new.hi[n_new - 1] == s_nhi[j])) {
-                s_new.lo[n_new] = s_nlo[j]; s_new.hi[n_new] = s_nhi[j]; s_new.below[n_new] = s_nbelow[j];
-                s_new.shift[n_new] = max(0, bit_length(s_nhi[j] - s_nlo[j]) - SEL_BIN_BITS);
-                s_new.mode[n_new] = s_npop[j] <= (unsigned long long)SEL_CAND ? IV_COLLECT : IV_HIST;
-                ++n_new;
-            }
-            s_new.target_iv[j] = n_new - 1;
+        unsigned long long off = 0;
+        for (int w = 0; w < warp; ++w) off += s_warp[w];
+        s_cum[tid] = off + incl;
+        __syncthreads();
+        total = s_cum[SEL_BINS - 1];
+    } else {
+        unsigned int base = 0;
+        for (unsigned int r = 0; r < n_ranks; ++r) {
+            const unsigned int* slot = slot0 + r * rank_stride_u32;
+            unsigned int cr = slot[0];
+            if (cr > (unsigned int)SEL_CAND) cr = SEL_CAND;
+            if ((unsigned int)tid < cr && base + tid < (unsigned int)SEL_CAND)
+                s_keys[base + tid] = (unsigned long long)reinterpret_cast<const Key*>(slot + 2)[tid];
+            base += cr;
         }
-        s_new.n_iv = n_new;
-        s_new.below_known = 1;
-        if (n_new) atomicAdd(pending, 1u);
+        const unsigned int cnt_all = base < (unsigned int)SEL_CAND ? base : SEL_CAND;
+        int P = 1;
+        while (P < (int)cnt_all) P <<= 1;
+        if (tid >= (int)cnt_all && tid < P) s_keys[tid] = ~0ull;
+        __syncthreads();
+        for (int k = 2; k <= P; k <<= 1) {
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                const int ixj = tid ^ j;
+                if (tid < P && ixj > tid) {
+                    const unsigned long long a = s_keys[tid], b2 = s_keys[ixj];
+                    const bool up = (tid & k) == 0;
+                    if ((a > b2) == up) { s_keys[tid] = b2; s_keys[ixj] = a; }
+                }
+                __syncthreads();
+            }
+        }
+        total = cnt_all;
     }
-    __syncthreads();
-    {
-        const unsigned int* src = reinterpret_cast<const unsigned int*>(&s_new);
-        unsigned int* dst = reinterpret_cast<unsigned int*>(&states[row]);
-        for (int i = tid; i < (int)(sizeof(RowSel) / 4); i += SCAN_THREADS) dst[i] = src[i];
+    ScanScratch& sc = scratch[row];
+    if (tid == 0) { sc.below[gi] = below; sc.total[gi] = total; }
+    if (tid < nt && st.target_iv[tid] == gi) {
+        const unsigned long long rank = plan->rank[tid];
+        const unsigned long long lo = st.lo[gi], hi = st.hi[gi];
+        int code;
+        unsigned long long nlo = 0, nhi = 0, nbelow = 0, npop = POP_UNKNOWN;
+        if (rank < below) {
+            code = SC_GAP_LOW;
+        } else if (rank - below >= total) {
+            code = SC_GAP_HIGH;
+        } else if (mode == IV_HIST) {
+            const unsigned long long r = rank - below;
+            int a = 0, b2 = SEL_BINS - 1;          // first bin with cum > r
+            while (a < b2) { const int mid = (a + b2) >> 1; if (s_cum[mid] > r) b2 = mid; else a = mid + 1; }
+            const int sh = st.shift[gi];
+            const unsigned long long before = a ? s_cum[a - 1] : 0ull;
+            nlo = lo + ((unsigned long long)a << sh);
+            const unsigned long long span = (1ull << sh) - 1ull;
+            nhi = (hi - nlo < span) ? hi : nlo + span;
+            nbelow = below + before;
+            npop = s_cum[a] - before;
+            code = nlo == nhi ? SC_DONE : SC_BIN;
+        } else {
+            nlo = nhi = s_keys[rank - below];
+            code = SC_DONE;
+        }
+        sc.nlo[tid] = nlo; sc.nhi[tid] = nhi; sc.nbelow[tid] = nbelow; sc.npop[tid] = npop; sc.code[tid] = code;
     }
+}
+
+__global__ void __launch_bounds__(128) select_scan_assemble_kernel(const SelectPlan* __restrict__ plan,
+                                                                   unsigned long long rows, unsigned long long key_max_v,
+                                                                   RowSel* __restrict__ states,
+                                                                   const ScanScratch* __restrict__ scratch,
+                                                                   unsigned int* __restrict__ pending) {
+    const unsigned long long row = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= rows) return;
+    RowSel& st = states[row];
+    const int n_iv = st.n_iv;
+    if (n_iv == 0) return;
+    const ScanScratch& sc = scratch[row];
+    const int nt = plan->n_targets;
+    RowSel nw;
+    int n_new = 0;
+    for (int j = 0; j < nt; ++j) {
+        nw.key[j] = st.key[j];
+        const int gi = st.target_iv[j];
+        if (gi < 0) { nw.target_iv[j] = -1; continue; }
+        const int code = sc.code[j];
+        if (code == SC_DONE) { nw.key[j] = sc.nlo[j]; nw.target_iv[j] = -1; continue; }
+        unsigned long long nlo, nhi, nbelow, npop = POP_UNKNOWN;
+        if (code == SC_GAP_LOW) {            // the bracket missed: the value lies in the gap below it ...
+            nlo = gi == 0 ? 0ull : st.hi[gi - 1] + 1ull;
+            nhi = st.lo[gi] - 1ull;
+            nbelow = gi == 0 ? 0ull : sc.below[gi - 1] + sc.total[gi - 1];
+        } else if (code == SC_GAP_HIGH) {    // ... or above it
+            nlo = st.hi[gi] + 1ull;
+            nhi = gi + 1 < n_iv ? st.lo[gi + 1] - 1ull : key_max_v;
+            nbelow = sc.below[gi] + sc.total[gi];
+        } else {
+            nlo = sc.nlo[j]; nhi = sc.nhi[j]; nbelow = sc.nbelow[j]; npop = sc.npop[j];
+        }
+        if (!(n_new && nw.lo[n_new - 1] == nlo && nw.hi[n_new - 1] == nhi)) {
+            nw.lo[n_new] = nlo; nw.hi[n_new] = nhi; nw.below[n_new] = nbelow;
+            nw.shift[n_new] = max(0, bit_length(nhi - nlo) - SEL_BIN_BITS);
+            nw.mode[n_new] = npop <= (unsigned long long)SEL_CAND ? IV_COLLECT : IV_HIST;
+            ++n_new;
+        }
+        nw.target_iv[j] = n_new - 1;
+    }
+    st.n_iv = n_new;
+    st.below_known = 1;
+    for (int i = 0; i < n_new; ++i) {
+        st.lo[i] = nw.lo[i]; st.hi[i] = nw.hi[i]; st.below[i] = nw.below[i];
+        st.shift[i] = nw.shift[i]; st.mode[i] = nw.mode[i];
+    }
+    for (int j = 0; j < nt; ++j) { st.key[j] = nw.key[j]; st.target_iv[j] = nw.target_iv[j]; }
+    if (n_new) atomicAdd(pending, 1u);
 }
 
 cudaError_t launch_select_scan(const SelectProblem& sp, const void* d_gathered_pass, unsigned int n_ranks,
                                size_t rank_stride_words, unsigned int* d_pending, cudaStream_t stream) {
     if (sp.plan.n_targets == 0 || sp.rows == 0) return cudaSuccess;
+    if (sp.rows > 65535 * 32ull || !sp.d_scratch) return cudaErrorInvalidValue;
     const unsigned int* g = static_cast<const unsigned int*>(d_gathered_pass);
     const size_t rs = row_slot_u32(sp.dtype, sp.plan.n_targets), is = iv_slot_u32(sp.dtype);
+    const dim3 grid((unsigned)sp.rows, (unsigned)sp.plan.n_targets);
     if (sp.dtype == MC_F64)
-        select_scan_kernel<uint64_t><<<(unsigned)sp.rows, SCAN_THREADS, 0, stream>>>(
-            sp.d_plan, g, n_ranks, rank_stride_words * 2, rs, is, sp.plan.n_targets, sp.d_states, d_pending);
+        select_scan_iv_kernel<uint64_t><<<grid, SCAN_THREADS, 0, stream>>>(
+            sp.d_plan, g, n_ranks, rank_stride_words * 2, rs, is, sp.plan.n_targets, sp.d_states, sp.d_scratch);
     else
-        select_scan_kernel<uint32_t><<<(unsigned)sp.rows, SCAN_THREADS, 0, stream>>>(
-            sp.d_plan, g, n_ranks, rank_stride_words * 2, rs, is, sp.plan.n_targets, sp.d_states, d_pending);
+        select_scan_iv_kernel<uint32_t><<<grid, SCAN_THREADS, 0, stream>>>(
+            sp.d_plan, g, n_ranks, rank_stride_words * 2, rs, is, sp.plan.n_targets, sp.d_states, sp.d_scratch);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    const unsigned long long kmax = sp.dtype == MC_F64 ? ~0ull : 0xFFFFFFFFull;
+    select_scan_assemble_kernel<<<(unsigned)((sp.rows + 127) / 128), 128, 0, stream>>>(sp.d_plan, sp.rows, kmax, sp.d_states,
+                                                                                      sp.d_scratch, d_pending);
     return cudaGetLastError();
 }
 
@@ -941,8 +958,7 @@ __global__ void __launch_bounds__(256) tail_hist_kernel(const Real* __restrict__
     double sum = 0.0;
     unsigned long long cnt = 0;
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const Real v = x[i];
+    auto visit = [&](Real v) {
         if (v <= thr) { sum += (double)v; ++cnt; }
         if (bins && v >= lo && v <= top) {
             int idx = (int)((v - lo) * inv_w);
@@ -951,7 +967,13 @@ __global__ void __launch_bounds__(256) tail_hist_kernel(const Real* __restrict__
             while (idx < last && v >= s_edge[idx + 1]) ++idx;
             atomicAdd(&s_counts[idx], 1u);
         }
+    };
+    unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < n; i += 4 * stride) {        // four loads in flight per thread
+        const Real a = x[i], b = x[i + stride], c = x[i + 2 * stride], d = x[i + 3 * stride];
+        visit(a); visit(b); visit(c); visit(d);
     }
+    for (; i < n; i += stride) visit(x[i]);
     if (want_tail) {
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) {

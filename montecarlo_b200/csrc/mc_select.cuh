@@ -17,6 +17,7 @@ struct SelectProblem {
     SelectPlan plan;          // host copy
     SelectPlan* d_plan;       // device copy
     RowSel* d_states;         // [rows]
+    ScanScratch* d_scratch;   // [rows]
 };
 
 // Build the plan for np.percentile(method='linear') over n_global values.

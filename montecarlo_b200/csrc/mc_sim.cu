@@ -382,15 +382,22 @@ __global__ void debug_philox_kernel(const uint32_t* ctr, uint32_t n, uint32_t k0
 }
 
 // per-block partials -> stage-0 header; one block, fixed summation order => deterministic
-__global__ void __launch_bounds__(256) reduce_partials_kernel(const BlockPartial* partials, int n,
-                                                              unsigned long long* words, unsigned long long w6,
-                                                              unsigned long long w7) {
-    __shared__ BlockPartial s[256];
+constexpr int REDUCE_THREADS = 1024;
+__global__ void __launch_bounds__(REDUCE_THREADS) reduce_partials_kernel(const BlockPartial* partials, int n,
+                                                                         unsigned long long* words, unsigned long long w6,
+                                                                         unsigned long long w7) {
+    __shared__ BlockPartial s[REDUCE_THREADS];
     BlockPartial acc = empty_partial();
-    for (int i = threadIdx.x; i < n; i += 256) combine(acc, partials[i]);
+    int i = threadIdx.x;
+    for (; i + 3 * REDUCE_THREADS < n; i += 4 * REDUCE_THREADS) {      // four loads in flight per thread
+        const BlockPartial a = partials[i], b = partials[i + REDUCE_THREADS], c = partials[i + 2 * REDUCE_THREADS],
+                           d = partials[i + 3 * REDUCE_THREADS];
+        combine(acc, a); combine(acc, b); combine(acc, c); combine(acc, d);
+    }
+    for (; i < n; i += REDUCE_THREADS) combine(acc, partials[i]);
     s[threadIdx.x] = acc;
     __syncthreads();
-    for (int w = 128; w > 0; w >>= 1) {
+    for (int w = REDUCE_THREADS / 2; w > 0; w >>= 1) {
         if ((int)threadIdx.x < w) combine(s[threadIdx.x], s[threadIdx.x + w]);
         __syncthreads();
     }
@@ -729,7 +736,7 @@ cudaError_t launch_debug_philox(const uint32_t* d_ctr, uint32_t n, uint32_t k0, 
 
 cudaError_t launch_reduce_partials(const BlockPartial* d_partials, int n_partials, unsigned long long* d_words,
                                    unsigned long long w6, unsigned long long w7, cudaStream_t stream) {
-    reduce_partials_kernel<<<1, 256, 0, stream>>>(d_partials, n_partials, d_words, w6, w7);
+    reduce_partials_kernel<<<1, REDUCE_THREADS, 0, stream>>>(d_partials, n_partials, d_words, w6, w7);
     return cudaGetLastError();
 }
 
