@@ -43,7 +43,17 @@ WORKLOADS = {
                                                   "10M paths x 252 steps fp32"),
 }
 # algorithmic work per path-step of the fused kernels -> path-steps per SM-clock
+# (fused GBM: 16 ALU lane-ops / 128 lanes = 2 MUFU / 16 lanes = 1/8 clk per path-step).
 STEPS_PER_SM_CLK = {"c2": 8.0, "c4": 8.0, "ref": 7.5, "c3": 0.33}
+# The kernels as built: what the binding pipe allows at the MEASURED issue rates of
+# sm_100a (tools/microbench*.cu: IMAD.WIDE 31.6 lanes/clk/SM, MUFU 15.9).  Philox-4x32-10 costs 20
+# IMAD.WIDE per call; a call feeds 8 normals (fp32), 5 bootstrap indices, or half a 16-asset step.
+OWN_BOUND_PER_SM_CLK = {"c2": 31.6 * 8 / 20, "c4": 31.6 * 8 / 20, "ref": 31.6 * 5 / 20, "c3": 128.0 / 310}
+OWN_BOUND_PIPE = {"c2": "IMAD.WIDE (Philox): 2.5 per normal at 31.6 lanes/clk/SM",
+                  "c4": "IMAD.WIDE (Philox): 2.5 per normal at 31.6 lanes/clk/SM",
+                  "ref": "IMAD.WIDE (Philox): 4 per bootstrap index at 31.6 lanes/clk/SM",
+                  "c3": "issue: ~310 instructions per 16-asset step (2 Philox calls, 8 Box-Muller pairs, "
+                        "152 FFMA) at 128 lane-instr/clk/SM"}
 
 
 class ClockSampler:
@@ -58,7 +68,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                          "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -244,13 +254,28 @@ def run_workload(workload, steps, warmup, world, rank, group, device, sample_clo
                 p5=last.pct.get("p5"))
 
 
+def measured_traffic(workload):
+    """DRAM bytes per launch of the workload's dominant kernel from the committed ncu --set full capture."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+            return json.load(fh).get(workload, {}).get("dram_bytes")
+    except (OSError, ValueError):
+        return None
+
+
 def roofline_for(workload, r, n_sm, clocks, peaks, peaks_kind):
+    out = _roofline_for(workload, r, n_sm, clocks, peaks, peaks_kind)
+    out["traffic"] = measured_traffic(workload)
+    return out
+
+
+def _roofline_for(workload, r, n_sm, clocks, peaks, peaks_kind):
     n, t, sim_s = r["n_local"], r["n_steps"], r["sim_ms"] * 1e-3
     if workload == "c5":
         bytes_ = 4.0 * n * (t + 1)            # 4 B written per stored price (SURVEY 8d)
         ach = bytes_ / sim_s / 1e9
         peak = float(peaks["hbm_gbs"])
-        return {"bound": "hbm", "kernel": "sim_kernel<float,NORMAL,CONST,STORE>", "achieved": ach, "peak": peak,
+        return {"bound": "hbm", "kernel": "sim32_kernel<NORMAL,CONST,STORE,V=4> (st.global.v4, time-major)", "achieved": ach, "peak": peak,
                 "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": f"{peaks_kind} copy bandwidth",
                 "algorithmic_bytes_per_launch": bytes_}
     mhz_max = float(peaks.get("sm_max_mhz", 1965.0))
@@ -258,12 +283,16 @@ def roofline_for(workload, r, n_sm, clocks, peaks, peaks_kind):
     per_clk = STEPS_PER_SM_CLK[workload]
     ach = n * t / sim_s
     peak = per_clk * n_sm * mhz * 1e6
+    own = OWN_BOUND_PER_SM_CLK[workload] * n_sm * mhz * 1e6
     lane_ops = {"c2": 16, "c4": 16, "ref": 17, "c3": 388}[workload]
-    return {"bound": "fp32-alu+mufu issue (not hbm, not tensor)", "kernel": "sim_kernel (fused RNG + step + moments)",
+    return {"bound": "fp32-alu+mufu issue (not hbm, not tensor)", "kernel": "sim32_kernel / portfolio_kernel (fused RNG + step + moments)",
             "achieved": ach / 1e9, "peak": peak / 1e9, "unit": "Gpath-steps/s", "frac": ach / peak,
             "traffic": None, "peak_source": f"SURVEY 8d: {per_clk} path-steps/SM-clk x {n_sm} SMs x {mhz:.0f} MHz "
                                             "(median SM clock sampled during the timed region)",
             "frac_at_max_clock": ach / (per_clk * n_sm * mhz_max * 1e6),
+            "own_pipe_bound": {"peak": own / 1e9, "frac": ach / own, "pipe": OWN_BOUND_PIPE[workload],
+                               "note": "SURVEY 8d assumed 2 MUFU per normal; the kernels as built take sin/cos from a "
+                                       "shared-memory table (1 MUFU per normal), so the measured-rate Philox multiply binds"},
             "fp32_lane_tflops": ach * lane_ops * 1e-12, "lane_ops_per_path_step": lane_ops}
 
 

@@ -19,6 +19,8 @@
 // pre-multiplies drift, omega and var0 by log2(e) or its square; GARCH is
 // homogeneous so the recursion is unchanged) so that price = s0 * ex2(y) is a
 // single MUFU.EX2.  The fp64 kernels work in natural units with exp().
+#include <cstdlib>
+
 #include "mc_rng.cuh"
 #include "mc_sim.cuh"
 
@@ -465,7 +467,8 @@ static cudaError_t pick_grid(Kernel kernel, int block, size_t smem, const Device
         // More blocks than fit at once: let the hardware block scheduler balance the load.  Warps of a
         // resident block do not finish together (the issue arbiter is not fair), so a persistent grid
         // drains unevenly; ~24 waves of short blocks keep every SM full until the last few percent.
-        unsigned long long per_thread = n / ((unsigned long long)block * resident * 24ull);
+        static const unsigned long long waves = getenv("MC_WAVES") ? strtoull(getenv("MC_WAVES"), nullptr, 10) : 24ull;
+        unsigned long long per_thread = n / ((unsigned long long)block * resident * waves);
         if (per_thread < 1) per_thread = 1;
         g = (n + block * per_thread - 1) / (block * per_thread);
         if (g > MAX_SIM_GRID) g = MAX_SIM_GRID;
@@ -567,7 +570,8 @@ static cudaError_t launch32_t(Sim32Args& a, const DeviceInfo& dev, int* grid, cu
     size_t smem;
     if (SHOCK == MC_SHOCK_NORMAL) {
         smem = (size_t)DIR_COUNT * sizeof(float2);
-        block = items >= 512ull * dev.sm_count ? 512 : 128;
+        static const int nb = getenv("MC_NBLOCK") ? atoi(getenv("MC_NBLOCK")) : 512;
+        block = items >= 512ull * dev.sm_count ? nb : 128;
     } else {
         block = items >= 1024ull * dev.sm_count ? 1024 : 256;
         smem = TAB ? ((size_t)a.pool_len << a.table_lc) * sizeof(float2) : 0;
