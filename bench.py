@@ -68,12 +68,17 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except OSError:
             self.proc = None
+
+    def wait_first(self, timeout_s):
+        t_end = time.perf_counter() + timeout_s
+        while self.proc is not None and not self.rows and time.perf_counter() < t_end:
+            time.sleep(0.02)
 
     def _read(self):
         for line in self.proc.stdout:
@@ -206,13 +211,16 @@ def run_workload(workload, steps, warmup, world, rank, group, device, sample_clo
         out = eng.simulate(spec, pool=pool_dev, group=group)
         return out
 
-    for _ in range(warmup):
-        one_step()
-        api_call(workload, world, group)
+    # nvidia-smi takes a while to come up (NVML init stalls CUDA calls meanwhile): start it before the
+    # warm-up and do not enter the timed region until its first sample has arrived
     sampler = ClockSampler(device) if (rank == 0 and sample_clocks) else None
     if sampler:
         sampler.start()
-        time.sleep(0.3)
+    for _ in range(warmup):
+        one_step()
+        api_call(workload, world, group)
+    if sampler:
+        sampler.wait_first(10.0)
     barrier()
     t0 = time.perf_counter()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
@@ -239,7 +247,7 @@ def run_workload(workload, steps, warmup, world, rank, group, device, sample_clo
         ta = time.perf_counter()
         api_call(workload, world, group)
         e2e_s += time.perf_counter() - ta
-    clocks = sampler.stop(t0, t1) if sampler else None
+    clocks = sampler.stop(t0, time.perf_counter()) if sampler else None      # device-timed + end-to-end loops
     tm = torch.tensor([dev_ms, e2e_s * 1e3, sum(sim_ms)], dtype=torch.float64, device=eng.device)
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX, group=group)
