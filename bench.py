@@ -170,8 +170,8 @@ def api_call(workload, world, group):
     import pandas as pd
     returns, rvol = synthetic_history()
     df = pd.DataFrame({"log_ret": returns, "rvol_20": rvol})
-    return mc.garch_monte_carlo(df, n, t, S0, seed=SEED, dtype="float32", return_paths=False, hist_bins=2048,
-                                group=group)
+    return mc.garch_monte_carlo(df, n, t, S0, seed=SEED, dtype="float32", return_paths=False, fan_chart=False,
+                                hist_bins=2048, group=group)
 
 
 def io_bytes(workload, spec, pool):

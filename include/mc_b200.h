@@ -171,6 +171,22 @@ int mc_fetch_result(mc_handle* h, mc_result* h_result, uint64_t* h_hist, double*
                     void* stream);
 
 /*
+ * Fan chart without keeping the paths (app.py:643-645 at any n_sims).  A path range that
+ * does not fit in HBM is cut into chunks that take turns in ONE [n_steps+1, chunk] buffer; each chunk runs
+ * as a virtual rank of the staged protocol (one handle per chunk, n_ranks = ranks x chunks).  Paths are
+ * a pure function of (seed, global path id), so before a stage that reads the rows again the chunk is
+ * simply simulated again into the shared buffer:
+ *
+ *   if (mc_stage_reads_paths(h) == 1) mc_stage_resimulate(h, stream);
+ *   mc_stage_next(h, ...);
+ *
+ * mc_stage_reads_paths: 1 if the next mc_stage_next of the run in flight streams the stored paths,
+ * 0 if not, negative on error (it may wait for the device's "rows undecided" counter).
+ */
+int mc_stage_reads_paths(mc_handle* h);
+int mc_stage_resimulate(mc_handle* h, void* stream);
+
+/*
  * Building blocks exposed for tests and for the callers either side of the path.
  */
 /* z[t, i] (dtype) for paths path_offset.. : the shocks the simulator would draw */

@@ -21,6 +21,7 @@ FLAG_STORE_PATHS, FLAG_FAN_CHART, FLAG_NO_TERMINAL_SELECT = 1, 2, 4
 EXPORTS = (
     "mc_abi_version", "mc_create", "mc_destroy", "mc_last_error", "mc_run",
     "mc_stage_begin", "mc_stage_words", "mc_stage_max_words", "mc_stage_next", "mc_fetch_result",
+    "mc_stage_reads_paths", "mc_stage_resimulate",
     "mc_debug_shocks", "mc_debug_philox", "mc_percentiles", "mc_histogram",
 )
 
@@ -86,6 +87,10 @@ def _declare(lib):
     lib.mc_run.argtypes = [vp, PP, PF, vp, vp, vp, vp, PR, vp, vp, vp]
     lib.mc_stage_begin.restype = C.c_int
     lib.mc_stage_begin.argtypes = [vp, PP, PF, vp, vp, vp, vp, vp, u64, vp]
+    lib.mc_stage_reads_paths.restype = C.c_int
+    lib.mc_stage_reads_paths.argtypes = [vp]
+    lib.mc_stage_resimulate.restype = C.c_int
+    lib.mc_stage_resimulate.argtypes = [vp, vp]
     lib.mc_stage_words.restype = C.c_int64
     lib.mc_stage_words.argtypes = [vp]
     lib.mc_stage_max_words.restype = C.c_int64

@@ -23,6 +23,20 @@ from .spec import (MIN_HISTORY, REF_ALPHA, REF_BETA, REF_OMEGA, REF_PATH_PCTS, R
 HOST_PATHS_LIMIT = 1 << 26
 # full paths are only materialised when (T+1)*N*itemsize fits this budget
 DEVICE_PATHS_LIMIT_BYTES = 64 << 30
+# when the paths are not kept, the fan chart (app.py:643-645) is computed by regeneration: chunks of paths
+# take turns in one device buffer of at most this many bytes
+FAN_BUFFER_BYTES = 8 << 30
+
+
+def _fan_plan(store: bool, want: bool, n_sims: int, n_days: int, dtype: str):
+    """-> (store_paths flag for the kernels, fan_chart flag, chunk size for regeneration or 0)."""
+    if not want:
+        return store, False, 0
+    if store:
+        return True, True, 0
+    itemsize = 8 if dtype == "float64" else 4
+    chunk = max(4096, (FAN_BUFFER_BYTES // ((n_days + 1) * itemsize)) // 4 * 4)
+    return True, True, int(chunk)
 
 
 def _history_inputs(df):
@@ -95,7 +109,7 @@ def garch_monte_carlo(df, n_sims: int, n_days: int, current_price: float, progre
                       omega: float = REF_OMEGA, alpha: float = REF_ALPHA, beta: float = REF_BETA,
                       shock: str = "bootstrap", injected_shocks=None,
                       hist_bins: int = 0, hist_range=None, device: Optional[int] = None,
-                      group=None) -> Optional[Dict]:
+                      group=None, fan_chart: Optional[bool] = None) -> Optional[Dict]:
     """Monte Carlo with volatility clustering: bootstrap shocks + GARCH(1,1) variance,
     exactly the model of app.py:592-657, computed on a B200.
 
@@ -103,7 +117,9 @@ def garch_monte_carlo(df, n_sims: int, n_days: int, current_price: float, progre
     reference), `dtype` ('float64' default = the reference's precision, or 'float32'),
     `return_paths` ('auto' | 'numpy' | 'device' | False), `shock` ('bootstrap' |
     'normal' | 'injected' with `injected_shocks[T, N]`), `hist_bins`/`hist_range`
-    (adds a 'histogram' key), `group` (torch.distributed group: shard paths over its ranks).
+    (adds a 'histogram' key), `group` (torch.distributed group: shard paths over its ranks),
+    `fan_chart` (None: always produce `path_percentiles` -- from the stored paths, or, when the paths
+    are not kept, by simulating chunks of them again; False: skip it).
     """
     from .engine import get_engine
     returns, rvol_last = _history_inputs(df)
@@ -117,13 +133,17 @@ def garch_monte_carlo(df, n_sims: int, n_days: int, current_price: float, progre
     store, how = _decide_paths(n_sims, n_days, dtype, return_paths)
     if group is not None and how == "numpy" and return_paths in (None, "auto"):
         how = "device"                                 # shards stay on their home GPU
+    # the dashboard reads path_percentiles (app.py:972-981): there by default, whether or not paths are kept
+    want_fan = (store or injected_shocks is None) if fan_chart is None else bool(fan_chart)
+    keep, fan, chunk = _fan_plan(store, want_fan, n_sims, n_days, dtype)
     spec = SimSpec(n_paths=n_sims, n_steps=n_days, s0=float(current_price), shock=shock, var_model="garch",
                    var0=current_var, omega=omega, alpha=alpha, beta=beta, dtype=dtype,
-                   seed=_new_seed() if seed is None else int(seed), store_paths=store, fan_chart=store,
+                   seed=_new_seed() if seed is None else int(seed), store_paths=keep, fan_chart=fan,
+                   fan_chunk_paths=chunk,
                    pcts=REF_TERMINAL_PCTS, path_pcts=REF_PATH_PCTS, tail_pct=REF_TAIL_PCT,
                    hist_bins=hist_bins, hist_range=hist_range)
     out = get_engine(device).simulate(spec, pool=pool if shock == "bootstrap" else None,
-                                      shocks=injected_shocks, group=group)
+                                      shocks=injected_shocks, group=group, keep_paths=store)
     return _result_dict(out, float(current_price), how)
 
 
@@ -142,12 +162,14 @@ def simulate_gbm(n_sims: int, n_days: int, current_price: float, mu: float, sigm
         hist_range = (current_price * math.exp(-w), current_price * math.exp(w))
     elif hist_range == "auto":
         hist_range = None
+    want_fan = store if fan_chart is None else bool(fan_chart)      # GBM default: only from stored paths
+    keep, fan, chunk = _fan_plan(store, want_fan, int(n_sims), int(n_days), dtype)
     spec = SimSpec.gbm(int(n_sims), int(n_days), float(current_price), mu, sigma, dt, dtype=dtype, seed=int(seed),
-                       shock="injected" if injected_shocks is not None else "normal", store_paths=store,
-                       fan_chart=store if fan_chart is None else (fan_chart and store),
+                       shock="injected" if injected_shocks is not None else "normal", store_paths=keep,
+                       fan_chart=fan, fan_chunk_paths=chunk,
                        pcts=tuple(pcts), path_pcts=tuple(path_pcts), tail_pct=tail_pct,
                        hist_bins=hist_bins, hist_range=hist_range)
-    out = get_engine(device).simulate(spec, shocks=injected_shocks, group=group)
+    out = get_engine(device).simulate(spec, shocks=injected_shocks, group=group, keep_paths=store)
     return _result_dict(out, float(current_price), how)
 
 

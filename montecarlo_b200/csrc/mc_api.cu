@@ -15,6 +15,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "mc_select.cuh"
 #include "mc_sim.cuh"
@@ -93,6 +94,10 @@ struct mc_handle {
     size_t next_words = 0;  // words of the stage buffer most recently written
     unsigned launches = 0;
     void* d_terminal = nullptr;
+    // what mc_stage_resimulate needs to run the simulation of the run in flight again
+    SimBuffers sim_buffers{};
+    bool has_pf = false;
+    std::vector<double> pf_chol, pf_sigma, pf_drift, pf_s0, pf_w;
 };
 
 namespace {
@@ -312,6 +317,16 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
     b.d_pool = d_pool; b.d_shocks = d_shocks; b.d_paths = d_paths; b.d_terminal = d_terminal;
     b.d_partials = h->partials.p;
     b.d_lut = h->lut.p;
+    h->sim_buffers = b;
+    h->has_pf = p->n_assets > 1 && pf;
+    if (h->has_pf) {
+        const size_t d = p->n_assets;
+        h->pf_chol.assign(pf->h_chol, pf->h_chol + d * d);
+        h->pf_sigma.assign(pf->h_sigma_step, pf->h_sigma_step + d);
+        h->pf_drift.assign(pf->h_drift_step, pf->h_drift_step + d);
+        h->pf_s0.assign(pf->h_s0, pf->h_s0 + d);
+        h->pf_w.assign(pf->h_weights, pf->h_weights + d);
+    }
     int grid = 0;
     if (p->n_paths) {
         MC_CUDA(h, launch_simulation(*p, pf, b, h->dev, &grid, s));
@@ -494,6 +509,39 @@ int mc_stage_next(mc_handle* h, const void* d_gathered, uint32_t n_ranks, void* 
     if (!h) return MC_ERR_INVALID;
     std::lock_guard<std::mutex> lock(h->mu);
     return stage_next_locked(h, d_gathered, n_ranks, d_stage_out, done, static_cast<cudaStream_t>(stream));
+}
+
+int mc_stage_reads_paths(mc_handle* h) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (!h->active) return fail(h, MC_ERR_STATE, "no staged run in flight");
+    if (!h->has_f) return 0;
+    if (h->phase == 0) return 1;                              // brackets, then the first pass
+    if (h->phase == 1) return h->pass_idx < 2 ? 1 : 0;        // scan, then pass 2 -- or the closing stage
+    if (h->pending_unchecked) {                               // final stage, unless rows are still undecided
+        MC_CUDA(h, cudaSetDevice(h->device));
+        MC_CUDA(h, cudaEventSynchronize(h->ev_pending));
+        return *h->h_pending.p != 0 ? 1 : 0;
+    }
+    return 0;
+}
+
+int mc_stage_resimulate(mc_handle* h, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (!h->active) return fail(h, MC_ERR_STATE, "no staged run in flight");
+    MC_CUDA(h, cudaSetDevice(h->device));
+    if (h->p.n_paths == 0) return MC_OK;
+    mc_portfolio pf{};
+    if (h->has_pf) {
+        pf.h_chol = h->pf_chol.data(); pf.h_sigma_step = h->pf_sigma.data(); pf.h_drift_step = h->pf_drift.data();
+        pf.h_s0 = h->pf_s0.data(); pf.h_weights = h->pf_w.data();
+    }
+    int grid = 0;
+    MC_CUDA(h, launch_simulation(h->p, h->has_pf ? &pf : nullptr, h->sim_buffers, h->dev, &grid,
+                                 static_cast<cudaStream_t>(stream)));
+    h->launches += 1;
+    return MC_OK;
 }
 
 int mc_fetch_result(mc_handle* h, mc_result* r, uint64_t* h_hist, double* h_fan, void* stream) {

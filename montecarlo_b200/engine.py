@@ -193,6 +193,10 @@ class Engine:
             rows = spec.n_steps * (spec.portfolio.arrays()["d"] if spec.portfolio is not None else 1)
             if shocks_t.numel() != rows * n_local:
                 raise ValueError(f"injected shocks must have shape [{rows}, {n_local}] on this rank")
+        if spec.fan_chart and spec.fan_chunk_paths and n_local > spec.fan_chunk_paths:
+            if shocks_t is not None:
+                raise ValueError("fan chart by regeneration needs device-generated shocks")
+            return self._simulate_regenerating(spec, pool_t, group, world, rank, offset, n_local, dt)
         with torch.cuda.device(self.device):
             terminal = torch.empty(n_local, dtype=dt, device=self.device)
             paths = torch.empty((spec.n_steps + 1, n_local), dtype=dt, device=self.device) if spec.store_paths else None
@@ -213,6 +217,73 @@ class Engine:
                 run_stages(backend, group)
                 self.check(self.lib.mc_fetch_result(self.handle, C.byref(res), hist_p, fan_p, self.stream_ptr()))
         return self._pack(spec, res, hist, fan, terminal, paths if keep_paths else None, offset)
+
+    def _simulate_regenerating(self, spec, pool_t, group, world, rank, offset, n_local, dt) -> RunOutput:
+        """Fan chart (app.py:643-645) for a path range whose [(T+1), N] matrix does not fit: chunks of
+        `spec.fan_chunk_paths` paths take turns in one buffer.  Every chunk is a virtual rank of the staged
+        protocol (own handle; n_ranks = ranks x chunks) and is simulated AGAIN -- same seed, same global path
+        ids, hence the same values -- before each stage that streams its rows."""
+        import torch.distributed as dist
+        chunk = int(spec.fan_chunk_paths)
+        n_chunks = (n_local + chunk - 1) // chunk
+        if world > 1:       # every rank must run the same number of virtual ranks
+            t = torch.tensor([n_chunks], device=self.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+            n_chunks = int(t.item())
+        vworld = world * n_chunks
+        engines = getattr(self, "_chunk_engines", [])
+        while len(engines) < n_chunks:
+            engines.append(self if not engines else Engine(self.device_index))
+        self._chunk_engines = engines
+        with torch.cuda.device(self.device):
+            terminal = torch.empty(n_local, dtype=dt, device=self.device)
+            buf = torch.empty((spec.n_steps + 1, min(chunk, n_local)), dtype=dt, device=self.device)
+            pf = make_portfolio(spec)
+            backs = []
+            for c in range(n_chunks):
+                lo = min(c * chunk, n_local)
+                cnt = min(chunk, n_local - lo)
+                params = make_params(spec, path_offset=offset + lo, n_local=cnt, paths_ld=buf.shape[1], n_ranks=vworld)
+                backs.append(_CudaStageBackend(engines[c], params, pf, pool_t, None, buf, terminal[lo:lo + cnt], 1))
+            launches = 0
+            for b in backs:                      # simulate + moments + pilot sample, chunk by chunk
+                b.begin()
+            done = False
+            while not done:
+                words = backs[0].stage_words()
+                local = torch.cat([b.stage_view(words) for b in backs])
+                if world > 1:
+                    gathered = torch.empty(vworld * words, dtype=torch.int64, device=self.device)
+                    dist.all_gather_into_tensor(gathered, local, group=group)
+                else:
+                    gathered = local
+                flags = []
+                for b in backs:
+                    e = b.e
+                    reads = e.lib.mc_stage_reads_paths(e.handle)
+                    if reads < 0:
+                        e.check(reads)
+                    if reads:
+                        e.check(e.lib.mc_stage_resimulate(e.handle, e.stream_ptr()))
+                    flags.append(b.next(gathered, vworld))
+                done = all(flags)
+                if any(flags) and not done:
+                    raise RuntimeError("virtual ranks disagree on the stage count")
+            res = L.McResult()
+            hist = np.zeros(spec.hist_bins, dtype=np.uint64) if spec.hist_bins else None
+            fan = np.zeros((len(spec.path_pcts), spec.n_steps + 1))
+            hist_p = C.c_void_p(hist.ctypes.data) if hist is not None else C.c_void_p(0)
+            sim_ms = 0.0
+            for i, b in enumerate(backs):        # every handle holds the same merged result; sum the sim times
+                r_i = L.McResult()
+                b.e.check(b.e.lib.mc_fetch_result(b.e.handle, C.byref(r_i if i else res), hist_p if i == 0 else C.c_void_p(0),
+                                                  C.c_void_p(fan.ctypes.data) if i == 0 else C.c_void_p(0), b.e.stream_ptr()))
+                r = r_i if i else res
+                sim_ms += float(r.sim_ms)
+                launches += int(r.launches)
+            res.sim_ms = sim_ms
+            res.launches = launches
+        return self._pack(spec, res, hist, fan, terminal, None, offset)
 
     def _pack(self, spec, res, hist, fan, terminal, paths, offset) -> RunOutput:
         names = [f"p{p:g}" for p in spec.pcts]

@@ -74,6 +74,7 @@ class SimSpec:
     seed: int = 0
     store_paths: bool = False
     fan_chart: bool = False
+    fan_chunk_paths: int = 0        # > 0: fan chart by regeneration, this many paths share one buffer at a time
     pcts: Tuple[float, ...] = REF_TERMINAL_PCTS
     path_pcts: Tuple[float, ...] = REF_PATH_PCTS
     tail_pct: Optional[float] = REF_TAIL_PCT

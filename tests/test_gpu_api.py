@@ -201,3 +201,75 @@ def test_full_size_c5_materialised_fan_chart():
         got = [res["path_percentiles"][f"p{p}"][row] for p in port.REF_PATH_PCTS]
         assert list(ref) == got
     assert torch.equal(paths[-1], res["final_prices"])
+
+
+@pytest.mark.parametrize("mode,dtype", [("garch", "float32"), ("garch", "float64"), ("gbm", "float32")])
+def test_fan_chart_by_regeneration_equals_stored_paths(engine, mode, dtype):
+    """the fan chart (app.py:643-645) without keeping the paths.  Chunks of the path range
+    take turns in one buffer and are simulated again before every stage that reads them; the result must
+    be the very same order statistics as from the fully stored matrix."""
+    n, t, s0 = 20_011, 37, 100.0
+    pool = None
+    if mode == "garch":
+        pool = port.bootstrap_pool(np.random.RandomState(5).standard_t(4, 1250) * 0.014)
+        kw = dict(n_paths=n, n_steps=t, s0=s0, var0=port.initial_variance(0.02 * np.sqrt(252)), dtype=dtype, seed=31,
+                  store_paths=True, fan_chart=True, hist_bins=64)
+        full, chunked = SimSpec(**kw), SimSpec(fan_chunk_paths=3000, **kw)
+    else:
+        kw = dict(dtype=dtype, seed=31, store_paths=True, fan_chart=True, hist_bins=64, hist_range=(50.0, 200.0))
+        full = SimSpec.gbm(n, t, s0, 0.05, 0.2, 1 / 252, **kw)
+        chunked = SimSpec.gbm(n, t, s0, 0.05, 0.2, 1 / 252, fan_chunk_paths=3000, **kw)
+    a = engine.simulate(full, pool=pool)
+    b = engine.simulate(chunked, pool=pool)
+    assert b.paths is None and a.paths is not None
+    assert torch.equal(a.terminal, b.terminal)
+    for k in a.fan:
+        assert np.array_equal(a.fan[k], b.fan[k]), k
+    ref_fan = np.percentile(a.paths.cpu().numpy().astype(np.float64), port.REF_PATH_PCTS, axis=1)
+    assert np.array_equal(np.stack([b.fan[f"p{p}"] for p in port.REF_PATH_PCTS]), ref_fan)
+    assert a.pct == b.pct and a.n == b.n and a.n_above == b.n_above
+    assert a.tail_count == b.tail_count and np.array_equal(a.hist, b.hist)
+    assert abs(a.mean - b.mean) < 1e-12 * abs(a.mean) and abs(a.std - b.std) < 1e-10 * a.std
+    assert abs(a.tail_sum - b.tail_sum) < 1e-12 * abs(a.tail_sum)
+
+
+def test_drop_in_without_paths_still_has_the_fan_chart():
+    df = _frame()
+    kept = garch_monte_carlo(df, 30_000, 25, 100.0, seed=3, dtype="float32", return_paths="numpy")
+    import montecarlo_b200.api as api
+    old = api.FAN_BUFFER_BYTES
+    api.FAN_BUFFER_BYTES = 26 * 4 * 8192          # 8192 paths per chunk
+    try:
+        lean = garch_monte_carlo(df, 30_000, 25, 100.0, seed=3, dtype="float32", return_paths=False)
+    finally:
+        api.FAN_BUFFER_BYTES = old
+    assert lean["paths"] is None
+    for k in ("p5", "p25", "p50", "p75", "p95"):                                   # app.py:972-981
+        assert np.array_equal(lean["path_percentiles"][k], kept["path_percentiles"][k])
+    assert lean["percentiles"] == kept["percentiles"]
+    assert garch_monte_carlo(df, 1000, 5, 100.0, seed=3, return_paths=False, fan_chart=False)["path_percentiles"] is None
+
+
+def test_concurrent_callers_from_threads():
+    """The app runs sessions in threads (app.py:1392): concurrent calls must not interfere."""
+    import threading
+    df = _frame()
+    expect = {s: garch_monte_carlo(df, 4000, 30, 100.0, seed=s, dtype="float32") for s in range(6)}
+    got, errs = {}, []
+
+    def work(s):
+        try:
+            for _ in range(3):
+                got[s] = garch_monte_carlo(df, 4000, 30, 100.0, seed=s, dtype="float32")
+        except Exception as exc:       # pragma: no cover
+            errs.append(exc)
+
+    threads = [threading.Thread(target=work, args=(s,)) for s in range(6)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errs
+    for s in range(6):
+        assert np.array_equal(got[s]["paths"], expect[s]["paths"])
+        assert got[s]["percentiles"] == expect[s]["percentiles"] and got[s]["cvar_95"] == expect[s]["cvar_95"]
