@@ -39,6 +39,9 @@ WORKLOADS = {
                                                  "per-step fan chart (BASELINE configs[4])"),
     "c3": dict(paths=1_000_000, steps=252, desc="16-asset Cholesky portfolio 1M paths x 252 steps fp32, "
                                                 "VaR/CVaR (BASELINE configs[2])"),
+    "c4fan": dict(paths=12_500_000, steps=2520, desc="config-4 shape WITH the per-step fan chart (app.py:643-645): 126 GB "
+                                                     "of paths per GPU never exist; 8 GB chunks are simulated three times "
+                                                     "(SURVEY 8f N1)"),
     "ref": dict(paths=10_000_000, steps=252, desc="reference model (bootstrap + GARCH(1,1), app.py:618-633) "
                                                   "10M paths x 252 steps fp32"),
 }
@@ -139,6 +142,11 @@ def make_spec(workload, world):
     elif workload == "c5":
         spec = SimSpec.gbm(n, t, S0, MU, SIGMA, DT, seed=SEED, hist_bins=2048, hist_range=hist_range(t),
                            store_paths=True, fan_chart=True)
+    elif workload == "c4fan":
+        from montecarlo_b200.api import _fan_plan
+        _, _, chunk = _fan_plan(False, True, n, t, "float32")
+        spec = SimSpec.gbm(n, t, S0, MU, SIGMA, DT, seed=SEED, hist_bins=2048, hist_range=hist_range(t),
+                           store_paths=True, fan_chart=True, fan_chunk_paths=chunk)
     elif workload == "c3":
         d = 16
         corr = np.full((d, d), 0.3) + 0.7 * np.eye(d)
@@ -162,6 +170,9 @@ def api_call(workload, world, group):
         return mc.simulate_gbm(n, t, S0, MU, SIGMA, dt=DT, seed=SEED, hist_bins=2048, group=group)
     if workload == "c5":
         return mc.simulate_gbm(n, t, S0, MU, SIGMA, dt=DT, seed=SEED, hist_bins=2048, return_paths="device", group=group)
+    if workload == "c4fan":
+        return mc.simulate_gbm(n, t, S0, MU, SIGMA, dt=DT, seed=SEED, hist_bins=2048, return_paths=False, fan_chart=True,
+                               group=group)
     if workload == "c3":
         d = 16
         corr = np.full((d, d), 0.3) + 0.7 * np.eye(d)
@@ -279,6 +290,14 @@ def roofline_for(workload, r, n_sm, clocks, peaks, peaks_kind):
 
 def _roofline_for(workload, r, n_sm, clocks, peaks, peaks_kind):
     n, t, sim_s = r["n_local"], r["n_steps"], r["sim_ms"] * 1e-3
+    if workload == "c4fan":
+        # whole job: every stored price is written three times (pilot + two narrowing passes) and read twice
+        bytes_ = 5 * 4.0 * n * (t + 1)
+        ach = bytes_ / (r["ms_per_step"] * 1e-3) / 1e9
+        peak = float(peaks["hbm_gbs"])
+        return {"bound": "hbm", "kernel": "whole job: 3 x sim32_kernel<STORE,V=4> + select_pass1/2_f32 per 8 GB chunk",
+                "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                "peak_source": f"{peaks_kind} copy bandwidth", "algorithmic_bytes_per_job": bytes_}
     if workload == "c5":
         bytes_ = 4.0 * n * (t + 1)            # 4 B written per stored price
         ach = bytes_ / sim_s / 1e9
@@ -305,7 +324,7 @@ def _roofline_for(workload, r, n_sm, clocks, peaks, peaks_kind):
 
 
 # --------------------------------------------------------------------------- CPU arms
-CPU_KIND = {"c2": "gbm", "c4": "gbm", "c5": "gbm", "c3": "gbm", "ref": "garch"}
+CPU_KIND = {"c2": "gbm", "c4": "gbm", "c5": "gbm", "c3": "gbm", "ref": "garch", "c4fan": "gbm"}
 
 
 def cpu_baseline_leg(workload, target_seconds=8.0):
@@ -397,11 +416,12 @@ def main():
     if rank == 0 and world == 1 and not args.no_extras:
         line["cpu_baseline"] = cpu_baseline_leg(args.workload)
         extras = {}
-        for wl in ("c4", "c5", "c3", "ref", "c2"):
+        for wl in ("c4", "c5", "c3", "ref", "c4fan", "c2"):
             if wl == args.workload:
                 continue
             try:
-                x = run_workload(wl, 3, 3, 1, 0, None, local_rank, sample_clocks=True)
+                x = run_workload(wl, 3 if wl != "c4fan" else 2, 3 if wl != "c4fan" else 1, 1, 0, None, local_rank,
+                                 sample_clocks=True)
                 extras[wl] = {"workload": WORKLOADS[wl]["desc"], "value": x["value"], "ms_per_step": x["ms_per_step"],
                               "e2e": x["e2e"]["value"], "sim_kernel_ms": x["sim_ms"], "clocks": x["clocks"],
                               "roofline": roofline_for(wl, x, n_sm, x["clocks"], peaks, peaks_kind)}
