@@ -13,7 +13,7 @@ What the oracle restates (reference = /root/reference/app.py):
                     have no counterpart in the reference.
 * ``philox``     -- bit model of the on-device generator (Philox-4x32-10, the
                     uniform bit-stuffing, Box-Muller, bootstrap index).
-* ``select_model`` -- host model of the multi-rank radix-select protocol.
+* ``select_model`` -- NumPy stage backend (exact radix select) for the multi-rank stage protocol.
 * ``ref_loader`` -- AST extraction of the unmodified reference function; usable
                     only where /root/reference exists (this container), used by
                     ``make_golden.py`` to pin the restatement.

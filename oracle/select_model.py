@@ -1,12 +1,14 @@
 """Host model of the multi-rank reduction protocol (TEST INFRASTRUCTURE, see oracle/__init__).
 
-A NumPy stand-in for the device stages of montecarlo_b200/csrc/mc_api.cu so that the
-orchestration loop `montecarlo_b200.engine.run_stages` (all-gather of one small stage
-buffer per stage) can be exercised on CPU with the gloo backend, world_size > 1.
-It follows the same algorithm -- moments about s0, multi-target radix select on
-order-preserving keys (digits 12/10/10 for fp32 keys), NumPy `_lerp`, tail sums,
-fixed-bin histogram -- with one int64 word per counter (the device packs two uint32
-per word; the protocol is the same).  The reductions it models are app.py:636-656.
+A NumPy stage backend so that the product's orchestration loop
+`montecarlo_b200.engine.run_stages` (begin -> [stage_words, all-gather of one small stage
+buffer, next] until done) can be exercised on CPU with the gloo backend, world_size > 1.
+The stage CONTRACT is the device's (montecarlo_b200/csrc/mc_api.cu: every rank computes the
+same decisions from the gathered buffers; only counters and candidate keys cross ranks); the
+selection inside is the simpler exact method the device used first -- a multi-target radix
+select on order-preserving keys (digits 12/10/10 for fp32 keys) -- where the device now
+narrows pilot brackets (mc_select.cu).  Both are exact, so both must reproduce NumPy: moments
+about s0, np.percentile's `_lerp`, tail sums, fixed-bin histogram (app.py:636-656).
 """
 from __future__ import annotations
 
