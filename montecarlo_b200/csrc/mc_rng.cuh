@@ -113,22 +113,23 @@ __device__ __forceinline__ void box_muller(uint32_t ua, uint32_t ub, double& z0,
 //     on the heavy FMA pipe): 6.0 - 6.7;
 //   * reading (cos, sin) of the 12-bit direction from a 4096-entry table in shared memory (one LDS.64,
 //     random banks, ~6 wavefronts) takes the two MUFU.SIN/COS off the XU pipe altogether: 8.4 - 8.5.
-// Word layout:  radius uniform = word[19:0]  (20 bits)  v1 = 1 - k 2^-20 in (0, 1],  |z| <= 5.27
-//               direction      = word[31:20] (12 bits)  theta = 2 pi (d / 4096 - 1/2)
+// Word layout:  radius uniform = word[31:12] (20 bits)  v1 = 1 - k 2^-20 in (0, 1],  |z| <= 5.27
+//               direction      = word[11:0]  (12 bits)  theta = 2 pi (d / 4096 - 1/2)
+// (the radius field sits on top so that ONE funnel shift drops it into a float's mantissa)
 // The fields are disjoint, so radius and direction are independent; 4096 equispaced directions integrate
 // every smooth functional of (z0, z1) exactly (trapezoid rule on a periodic integrand).
 constexpr int DIR_BITS = 12;
 constexpr int DIR_COUNT = 1 << DIR_BITS;                 // float2 (cos, sin) entries: 32 KB
 
 __device__ __forceinline__ float radius_uniform20(uint32_t w) {           // (0, 1], multiples of 2^-20
-    return fmaf(__uint_as_float((w & 0x000FFFFFu) | 0x3F800000u), -8.0f, 9.0f);
+    return fmaf(__uint_as_float(__funnelshift_r(w, 0x3F8u, 12)), -8.0f, 9.0f);     // bits 0x3F800000 | w[31:12]
 }
 // Box-Muller radius without its constant: rho = sqrt(-lg2 v1), r = sqrt(2 ln 2) rho
 __device__ __forceinline__ float rho20(uint32_t w) { return fast_sqrt(-fast_lg2(radius_uniform20(w))); }
 
 // (cos, sin) of the word's direction; lut_base = shared-window byte address of the table
 __device__ __forceinline__ void direction_of(uint32_t w, uint32_t lut_base, float& c, float& s) {
-    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(c), "=f"(s) : "r"(lut_base + ((w >> 17) & 0x7FF8u)));
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(c), "=f"(s) : "r"(lut_base + ((w << 3) & 0x7FF8u)));
 }
 
 __device__ __forceinline__ void normals8(const u32x4& w, uint32_t lut_base, float (&z)[8]) {
@@ -178,14 +179,19 @@ __device__ __forceinline__ uint32_t bootstrap_index(uint32_t u, uint32_t pool_le
 //     t  = fma(g, H 2^-23, 2^23 - H + 1/2)       = 2^23 + field H 2^-23 + 1/2      (ONE rounding, ulp 1)
 //        = 2^23 + idx + 1            (a tie -- field H 2^-23 an exact integer -- rounds to even)
 // so bits(t) - 0x4B000000 = idx + 1, and (bits(t) << s) wraps the exponent bits out of a byte offset.
-// Fields 0-3 are word[22:0]; field 4 is the top bytes of words 0, 1, 2.  Per-index probabilities differ
-// by at most H 2^-23 (1.5e-4 at the reference's H ~ 1250); pools longer than 65536 use the IMAD.HI path.
+// Fields 0-3 are word[31:9] (one funnel shift builds g); field 4 is the low bytes of words 0, 1, 2 (23 of
+// those 24 bits).  Per-index probabilities differ by at most H 2^-23 (1.5e-4 at the reference's H ~ 1250);
+// pools longer than 65536 use the fp64 kernels' IMAD.HI path.
 constexpr uint32_t BOOT32_MAX_POOL = 65536u;
-__device__ __forceinline__ uint32_t boot_field4(const u32x4& w) {
-    return __byte_perm(__byte_perm(w.x, w.y, 0x0073), w.z, 0x7710);
+__device__ __forceinline__ float boot_g(uint32_t word) {                       // fields 0-3
+    return __uint_as_float(__funnelshift_r(word, 0x96u, 9));                   // bits 0x4B000000 | word[31:9]
 }
-__device__ __forceinline__ uint32_t boot_index_bits(uint32_t field_word, float scale, float bias) {
-    return __float_as_uint(fmaf(__uint_as_float((field_word & 0x007FFFFFu) | 0x4B000000u), scale, bias));
+__device__ __forceinline__ float boot_g4(const u32x4& w) {                      // field 4
+    const uint32_t b = __byte_perm(__byte_perm(w.x, w.y, 0x0040), w.z, 0x7410);   // [w0.b0, w1.b0, w2.b0, -]
+    return __uint_as_float((b & 0x007FFFFFu) | 0x4B000000u);
+}
+__device__ __forceinline__ uint32_t boot_index_bits(float g, float scale, float bias) {
+    return __float_as_uint(fmaf(g, scale, bias));
 }
 
 }  // namespace mc

@@ -364,10 +364,10 @@ __global__ void debug_shocks32_kernel(const Sim32Args a, float* out) {
             if (SHOCK == MC_SHOCK_NORMAL) {
                 normals8(w, lut_base, z);
             } else {
-                const uint32_t f[5] = {w.x, w.y, w.z, w.w, boot_field4(w)};
+                const float gf[5] = {boot_g(w.x), boot_g(w.y), boot_g(w.z), boot_g(w.w), boot_g4(w)};
 #pragma unroll
                 for (int k = 0; k < 5; ++k)
-                    z[k] = a.pool[(boot_index_bits(f[k], a.idx_scale, a.idx_bias) & 0x007FFFFFu) - 1u];
+                    z[k] = a.pool[(boot_index_bits(gf[k], a.idx_scale, a.idx_bias) & 0x007FFFFFu) - 1u];
             }
 #pragma unroll
             for (int k = 0; k < K; ++k)
@@ -562,7 +562,7 @@ static Sim32Args make_args32(const mc_params& p, const SimBuffers& b) {
     return a;
 }
 
-template <int SHOCK, int VAR, bool STORE, int V, bool TAB>
+template <int SHOCK, int VAR, bool STORE, int V, int TAB>
 static cudaError_t launch32_t(Sim32Args& a, const DeviceInfo& dev, int* grid, cudaStream_t stream) {
     auto kernel = sim32_kernel<SHOCK, VAR, STORE, V, TAB>;
     const unsigned long long items = (a.n_paths + V - 1) / V;      // threads' worth of work
@@ -574,7 +574,7 @@ static cudaError_t launch32_t(Sim32Args& a, const DeviceInfo& dev, int* grid, cu
         block = items >= 512ull * dev.sm_count ? nb : 128;
     } else {
         block = items >= 1024ull * dev.sm_count ? 1024 : 256;
-        smem = TAB ? ((size_t)a.pool_len << a.table_lc) * sizeof(float2) : 0;
+        smem = TAB != TAB_GLOBAL ? ((size_t)a.pool_len << a.table_lc) * sizeof(float2) : 0;
     }
     cudaError_t e = pick_grid(kernel, block, smem, dev, items, grid);
     if (e != cudaSuccess) return e;
@@ -582,7 +582,7 @@ static cudaError_t launch32_t(Sim32Args& a, const DeviceInfo& dev, int* grid, cu
     return cudaGetLastError();
 }
 
-template <int SHOCK, int VAR, bool TAB>
+template <int SHOCK, int VAR, int TAB>
 static cudaError_t launch32_store(Sim32Args& a, const mc_params& p, const DeviceInfo& dev, int* grid, cudaStream_t s) {
     if (!(p.flags & MC_FLAG_STORE_PATHS)) return launch32_t<SHOCK, VAR, false, 1, TAB>(a, dev, grid, s);
     // 16-byte stores need rows and base pointers that keep every group of four paths aligned
@@ -592,7 +592,7 @@ static cudaError_t launch32_store(Sim32Args& a, const mc_params& p, const Device
                : launch32_t<SHOCK, VAR, true, 1, TAB>(a, dev, grid, s);
 }
 
-template <int SHOCK, bool TAB>
+template <int SHOCK, int TAB>
 static cudaError_t launch32_var(Sim32Args& a, const mc_params& p, const DeviceInfo& dev, int* grid, cudaStream_t s) {
     return p.var_model == MC_VAR_CONST ? launch32_store<SHOCK, MC_VAR_CONST, TAB>(a, p, dev, grid, s)
                                        : launch32_store<SHOCK, MC_VAR_GARCH, TAB>(a, p, dev, grid, s);
@@ -603,17 +603,18 @@ static cudaError_t launch_sim32(const mc_params& p, const SimBuffers& b, const D
     Sim32Args a = make_args32(p, b);
     if (p.shock == MC_SHOCK_NORMAL) {
         if (!b.d_lut) return cudaErrorInvalidValue;
-        return launch32_var<MC_SHOCK_NORMAL, true>(a, p, dev, grid, s);
+        return launch32_var<MC_SHOCK_NORMAL, TAB_SMEM>(a, p, dev, grid, s);
     }
     // bootstrap: widest replication (<= 8 copies: a half-warp's LDS.64 then rarely collides) that fits
     const size_t budget = (size_t)dev.max_smem_optin - 4 * 1024;
     int lc = 3;
     while (lc >= 0 && ((size_t)p.pool_len << lc) * sizeof(float2) > budget) --lc;
-    if (lc < 0) return launch32_var<MC_SHOCK_BOOTSTRAP, false>(a, p, dev, grid, s);   // gather from global/L1
+    if (lc < 0) return launch32_var<MC_SHOCK_BOOTSTRAP, TAB_GLOBAL>(a, p, dev, grid, s);   // gather from global/L1
     if (p.n_paths < 1024ull * dev.sm_count)        // small request: cheaper table fill, more blocks per SM
         while (lc > 0 && ((size_t)p.pool_len << lc) * sizeof(float2) > 40 * 1024) --lc;
     a.table_lc = lc;
-    return launch32_var<MC_SHOCK_BOOTSTRAP, true>(a, p, dev, grid, s);
+    return lc == 3 ? launch32_var<MC_SHOCK_BOOTSTRAP, TAB_SMEM8>(a, p, dev, grid, s)
+                   : launch32_var<MC_SHOCK_BOOTSTRAP, TAB_SMEM>(a, p, dev, grid, s);
 }
 
 template <typename Real, int D, bool INJECTED, bool STORE>

@@ -37,7 +37,9 @@ __device__ __forceinline__ float price_of(const Sim32Args& a, uint32_t steps_don
 
 // One Philox call's worth of steps for ONE path: K = 8 (normal) or 5 (bootstrap).  `limit` < K only in
 // the ragged last call (TAIL).  emit(k, y) sees the log-price after step k of this call.
-template <int SHOCK, int VAR, bool TAB, bool TAIL, typename Emit>
+enum { TAB_GLOBAL = 0, TAB_SMEM = 1, TAB_SMEM8 = 2 };     // where the bootstrap table lives / how it is addressed
+
+template <int SHOCK, int VAR, int TAB, bool TAIL, typename Emit>
 __device__ __forceinline__ void advance(const Sim32Args& a, const u32x4& w, uint32_t table_base, int table_shift,
                                         float sigr, int limit, float& y, float& v, Emit emit) {
     if (SHOCK == MC_SHOCK_NORMAL) {
@@ -66,13 +68,15 @@ __device__ __forceinline__ void advance(const Sim32Args& a, const u32x4& w, uint
             }
         }
     } else {
-        const uint32_t f[5] = {w.x, w.y, w.z, w.w, boot_field4(w)};
+        const float gf[5] = {boot_g(w.x), boot_g(w.y), boot_g(w.z), boot_g(w.w), boot_g4(w)};
 #pragma unroll
         for (int k = 0; k < 5; ++k) {
             if (TAIL && k >= limit) break;
-            const uint32_t tb = boot_index_bits(f[k], a.idx_scale, a.idx_bias);   // bits(2^23 + idx + 1)
+            const uint32_t tb = boot_index_bits(gf[k], a.idx_scale, a.idx_bias);  // bits(2^23 + idx + 1)
             float z, g;
-            if (TAB) {
+            if (TAB == TAB_SMEM8) {          // eight copies: the shift is an immediate and folds into one LEA
+                asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(z), "=f"(g) : "r"((tb << 6) + table_base));
+            } else if (TAB == TAB_SMEM) {
                 asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(z), "=f"(g) : "r"((tb << table_shift) + table_base));
             } else {
                 z = __ldg(a.pool + ((tb & 0x007FFFFFu) - 1u));
@@ -92,7 +96,7 @@ __device__ __forceinline__ void advance(const Sim32Args& a, const u32x4& w, uint
 // V paths per thread: 1, or 4 consecutive paths whose prices leave as one 16-byte store per step
 // (a warp then writes 512 contiguous bytes of a time-major row: measured 6.0 TB/s against 4.4 TB/s
 // for 4-byte stores at the config-5 shape, profiles/r01/microbench2_sm100a_v3.txt).
-template <int SHOCK, int VAR, bool STORE, int V, bool TAB>
+template <int SHOCK, int VAR, bool STORE, int V, int TAB>
 __global__ void __launch_bounds__(SHOCK == MC_SHOCK_NORMAL ? 512 : 1024) sim32_kernel(const __grid_constant__ Sim32Args a) {
     extern __shared__ __align__(16) unsigned char smem_dyn[];
     __shared__ BlockPartial s_warp[32];
@@ -104,8 +108,8 @@ __global__ void __launch_bounds__(SHOCK == MC_SHOCK_NORMAL ? 512 : 1024) sim32_k
     float2* s_tab = reinterpret_cast<float2*>(smem_dyn);
     if (SHOCK == MC_SHOCK_NORMAL) {
         for (int i = threadIdx.x; i < DIR_COUNT; i += blockDim.x) s_tab[i] = a.lut[i];
-    } else if (TAB) {
-        const int lc = a.table_lc;
+    } else if (TAB != TAB_GLOBAL) {
+        const int lc = TAB == TAB_SMEM8 ? 3 : a.table_lc;
         for (uint32_t i = threadIdx.x; i < (a.pool_len << lc); i += blockDim.x) {
             const float z = a.pool[i >> lc];
             s_tab[i] = make_float2(z, fmaf(a.alpha, z * z, a.beta));

@@ -8,14 +8,14 @@ based generator (it bootstraps with np.random.choice, app.py:620).
 
 Counter layout:  ctr = (path_lo, path_hi, call_index, stream), key = (seed_lo, seed_hi)
   fp32 normals:  EIGHT per call -- one Box-Muller pair per 32-bit word:
-                 radius uniform v1 = 1 - word[19:0] * 2^-20  in (0, 1]
-                 direction d = word[31:20] (12 bits), theta = 2*pi*(d/4096 - 1/2); the device reads
+                 radius uniform v1 = 1 - word[31:12] * 2^-20  in (0, 1]
+                 direction d = word[11:0] (12 bits), theta = 2*pi*(d/4096 - 1/2); the device reads
                  (cos, sin) of it from a 4096-entry table rounded once from fp64
                  r = sqrt(-2 ln v1);  z[2k] = r*cos(theta), z[2k+1] = r*sin(theta)   -> steps 8j..8j+7
   fp64 normals:  FOUR per call: v1 = (u+1) * 2^-32 in (0,1],  theta = 2*pi*(u2 * 2^-32) - pi
   fp64 bootstrap: FOUR per call: idx = (word * H) >> 32   (mulhi)
-  fp32 bootstrap (H <= 65536): FIVE per call from 23-bit fields (word_k[22:0], k = 0..3, and the top
-                 bytes of words 0,1,2): idx = bits(fl32(fma(2^23 + field, H*2^-23, 2^23 - H + 1/2)))
+  fp32 bootstrap (H <= 65536): FIVE per call from 23-bit fields (word_k[31:9], k = 0..3, and 23 bits of
+                 the low bytes of words 0,1,2): idx = bits(fl32(fma(2^23 + field, H*2^-23, 2^23 - H + 1/2)))
                  - 0x4B000000 - 1 = floor(field*H/2^23), a tie (exact integer) rounding to even
 """
 from __future__ import annotations
@@ -91,8 +91,8 @@ def _pair_f32(word):
     if _DIR is None:
         _DIR = direction_table()
     w = np.asarray(word, dtype=np.uint32)
-    v1 = 1.0 - (w & np.uint32(0xFFFFF)).astype(np.float64) * 2.0 ** -20
-    d = (w >> np.uint32(20)).astype(np.int64)
+    v1 = 1.0 - (w >> np.uint32(12)).astype(np.float64) * 2.0 ** -20
+    d = (w & np.uint32(0xFFF)).astype(np.int64)
     r = np.sqrt(-2.0 * np.log(v1))
     return r * _DIR[0][d], r * _DIR[1][d]
 
@@ -139,9 +139,9 @@ def indices_per_call(dtype, pool_len: int) -> int:
 
 def _boot_fields(w):
     """The five 23-bit fields of one call (fp32 kernels)."""
-    top = lambda x: (np.asarray(x, dtype=np.uint32) >> np.uint32(24)).astype(np.uint32)
-    f4 = top(w[0]) | (top(w[1]) << np.uint32(8)) | (top(w[2]) << np.uint32(16))
-    return [np.asarray(w[k], dtype=np.uint32) & np.uint32(0x7FFFFF) for k in range(4)] + [f4 & np.uint32(0x7FFFFF)]
+    low = lambda x: (np.asarray(x, dtype=np.uint32) & np.uint32(0xFF)).astype(np.uint32)
+    f4 = low(w[0]) | (low(w[1]) << np.uint32(8)) | (low(w[2]) << np.uint32(16))
+    return [np.asarray(w[k], dtype=np.uint32) >> np.uint32(9) for k in range(4)] + [f4 & np.uint32(0x7FFFFF)]
 
 
 def _boot_index32(field, pool_len: int):
