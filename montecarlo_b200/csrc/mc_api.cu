@@ -68,6 +68,9 @@ struct mc_handle {
     DevBuf<float2> lut;                 // Box-Muller direction table of the fp32 normal shocks (mc_rng.cuh)
     DevBuf<DeviceResult> res;
     DevBuf<SelectPlan> plans;           // [2]: terminal, fan
+    SelectPlan plan_shadow[2];          // what plans[slot] holds on the device ...
+    bool plan_valid[2] = {false, false};
+    cudaStream_t plan_stream[2] = {nullptr, nullptr};   // ... once this stream has reached the upload
     DevBuf<RowSel> states_t, states_f;
     DevBuf<ScanScratch> scratch_t, scratch_f;
     DevBuf<unsigned int> pending;       // [1] rows with undecided targets after the latest scan
@@ -180,8 +183,13 @@ int validate(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const voi
 
 int upload_plan(mc_handle* h, SelectProblem& sp, int slot, cudaStream_t s) {
     sp.d_plan = h->plans.p + slot;
+    // repeated calls with the same targets on the same stream (the dashboard's case) leave the device copy as it is
+    if (h->plan_valid[slot] && h->plan_stream[slot] == s && memcmp(&h->plan_shadow[slot], &sp.plan, sizeof(SelectPlan)) == 0) return MC_OK;
     // pageable host -> device async copy is staged by the runtime before returning
     MC_CUDA(h, cudaMemcpyAsync(sp.d_plan, &sp.plan, sizeof(SelectPlan), cudaMemcpyHostToDevice, s));
+    memcpy(&h->plan_shadow[slot], &sp.plan, sizeof(SelectPlan));
+    h->plan_valid[slot] = true;
+    h->plan_stream[slot] = s;
     return MC_OK;
 }
 

@@ -1,0 +1,57 @@
+// mc_launch.cuh -- per-process caches for the two runtime queries every launch used to repeat
+// (cudaFuncSetAttribute for > 48 KB of dynamic shared memory, cudaOccupancyMaxActiveBlocksPerMultiprocessor).
+// The reference's own call sizes (1,000 x 20 ... 10,000 x 252, app.py:1189-1195) are launch-latency bound:
+// the device needs ~0.2 ms, so host microseconds per launch matter.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
+namespace mc {
+
+struct LaunchCache {
+    std::mutex mu;
+    std::map<std::tuple<int, const void*>, size_t> smem_limit;                 // (device, kernel) -> bytes enabled
+    std::map<std::tuple<int, const void*, int, size_t>, int> blocks_per_sm;   // (device, kernel, block, smem)
+    static LaunchCache& get() { static LaunchCache c; return c; }
+};
+
+// make `smem` bytes of dynamic shared memory launchable for `func` on the current device
+template <typename K>
+inline cudaError_t ensure_dynamic_smem(K func, size_t smem, size_t static_smem = 0) {
+    if (smem + static_smem <= 48 * 1024) return cudaSuccess;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    LaunchCache& c = LaunchCache::get();
+    std::lock_guard<std::mutex> lock(c.mu);
+    size_t& have = c.smem_limit[std::make_tuple(dev, reinterpret_cast<const void*>(func))];
+    if (have >= smem) return cudaSuccess;
+    e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) have = smem;
+    return e;
+}
+
+template <typename K>
+inline cudaError_t resident_blocks_per_sm(K func, int block, size_t smem, int* per_sm) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    LaunchCache& c = LaunchCache::get();
+    const auto key = std::make_tuple(dev, reinterpret_cast<const void*>(func), block, smem);
+    {
+        std::lock_guard<std::mutex> lock(c.mu);
+        auto it = c.blocks_per_sm.find(key);
+        if (it != c.blocks_per_sm.end()) { *per_sm = it->second; return cudaSuccess; }
+    }
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(per_sm, func, block, smem);
+    if (e == cudaSuccess) {
+        std::lock_guard<std::mutex> lock(c.mu);
+        c.blocks_per_sm[key] = *per_sm;
+    }
+    return e;
+}
+
+}  // namespace mc

@@ -25,6 +25,7 @@
 // contraction so results are bit-identical to np.percentile on the same values.
 #include <math.h>
 
+#include "mc_launch.cuh"
 #include "mc_select.cuh"
 
 namespace mc {
@@ -568,7 +569,7 @@ template <typename K>
 static cudaError_t launch_fast(K k, const SelectProblem& sp, void* d_out, int n_iv_smem, dim3 grid, cudaStream_t stream) {
     const size_t smem = (size_t)n_iv_smem * SEL_BINS * sizeof(unsigned int);
     if (smem > 20 * 1024) {      // the kernels also hold up to ~21 KB of static shared memory (queue / map)
-        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = ensure_dynamic_smem(k, smem, 28 * 1024);
         if (e != cudaSuccess) return e;
     }
     const float* x = static_cast<const float*>(sp.x);
@@ -598,7 +599,7 @@ static cudaError_t launch_pass_t(const SelectProblem& sp, void* d_out, int n_iv_
     auto k = select_pass_kernel<Real, NIV>;
     const size_t smem = (size_t)n_iv_smem * SEL_BINS * sizeof(unsigned int);
     if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = ensure_dynamic_smem(k, smem);
         if (e != cudaSuccess) return e;
     }
     k<<<grid, 256, smem, stream>>>(static_cast<const Real*>(sp.x), sp.ld, sp.n, sp.d_states,
@@ -1031,12 +1032,12 @@ cudaError_t launch_tail_hist(const void* x, int dtype, unsigned long long n, boo
     const size_t smem = bins ? ((size_t)bins + 2) * esz + (size_t)bins * 4 : 0;
     if (dtype == MC_F64) {
         auto k = tail_hist_kernel<double>;
-        if (smem > 48 * 1024 && (e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+        if ((e = ensure_dynamic_smem(k, smem)) != cudaSuccess) return e;
         k<<<(unsigned)blocks, 256, smem, stream>>>(static_cast<const double*>(x), n, d_res, want_tail ? 1 : 0, bins,
                                                    d_edges, d_edges_f, d_scratch, d_words + 2);
     } else {
         auto k = tail_hist_kernel<float>;
-        if (smem > 48 * 1024 && (e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+        if ((e = ensure_dynamic_smem(k, smem)) != cudaSuccess) return e;
         k<<<(unsigned)blocks, 256, smem, stream>>>(static_cast<const float*>(x), n, d_res, want_tail ? 1 : 0, bins,
                                                    d_edges, d_edges_f, d_scratch, d_words + 2);
     }

@@ -21,6 +21,7 @@
 // single MUFU.EX2.  The fp64 kernels work in natural units with exp().
 #include <cstdlib>
 
+#include "mc_launch.cuh"
 #include "mc_rng.cuh"
 #include "mc_sim.cuh"
 
@@ -450,13 +451,10 @@ static SimArgs<Real> make_args(const mc_params& p, const SimBuffers& b) {
 template <typename Kernel>
 static cudaError_t pick_grid(Kernel kernel, int block, size_t smem, const DeviceInfo& dev,
                              unsigned long long n, int* grid) {
-    cudaError_t e;
-    if (smem > 48 * 1024) {
-        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-    }
+    cudaError_t e = ensure_dynamic_smem(kernel, smem);
+    if (e != cudaSuccess) return e;
     int per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem);
+    e = resident_blocks_per_sm(kernel, block, smem, &per_sm);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) return cudaErrorLaunchOutOfResources;
     const unsigned long long resident = (unsigned long long)dev.sm_count * per_sm;

@@ -1,0 +1,13 @@
+import os, sys, cProfile, pstats
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, pandas as pd, torch
+from montecarlo_b200 import garch_monte_carlo
+rs = np.random.RandomState(0)
+df = pd.DataFrame({"log_ret": rs.normal(0.0, 0.02, 1250), "rvol_20": 0.02 * np.sqrt(252)})
+for _ in range(5):
+    garch_monte_carlo(df, 1000, 20, 100.0, seed=1)
+pr = cProfile.Profile(); pr.enable()
+for _ in range(200):
+    garch_monte_carlo(df, 1000, 20, 100.0, seed=1)
+pr.disable()
+pstats.Stats(pr).sort_stats("cumulative").print_stats(28)
