@@ -201,6 +201,31 @@ int mc_percentiles(mc_handle* h, const void* d_x, int32_t dtype, uint64_t rows, 
 int mc_histogram(mc_handle* h, const void* d_x, int32_t dtype, uint64_t n, uint32_t bins,
                  double lo, double hi, uint64_t* h_counts, void* stream);
 
+/*
+ * Input producers: what the routine reads, from raw close prices, for n_series price histories
+ * in one launch.  Replaces, per history, the pandas producers of the two columns the routine reads --
+ * `log_ret` (app.py:224) and `rvol_20` (app.py:233, sample std of the last 20 log returns x sqrt(252)) --, the
+ * row dropping of app.py:392-393 (rows before `first_row` go: the reference's 200-day average, app.py:252, makes
+ * that 199; rows before 20 always go, they have no rvol_20), and the routine's own first lines: `returns`
+ * (app.py:592), `current_var` (app.py:606), `std_returns` (app.py:609); s0 is the call site's `current_price`
+ * (app.py:1213).  All arithmetic is fp64; the pool is written in `pool_dtype` (what mc_run wants as d_pool).
+ *   d_close   [n_series, close_ld] fp64, history b holds d_lengths[b] prices (all n_obs when d_lengths is NULL)
+ *   d_pool    [n_series, pool_ld]: pool b = d_pool + b * pool_ld, d_inputs[b].pool_len entries
+ *   d_inputs  [n_series] (device memory); pool_len < 100 is the reference's "return None" case (app.py:594-595)
+ * Asynchronous on `stream`; nothing is copied to the host.
+ */
+#define MC_INPUT_NAN 1u          /* flags: a log return was NaN (non-positive or NaN price); the reference would drop the row */
+typedef struct mc_series_inputs {
+    double s0;                   /* close[last] */
+    double var0;                 /* initial daily variance, mc_params.var0 */
+    double pool_std;             /* np.std(returns), ddof = 0 */
+    uint64_t pool_len;
+    uint64_t flags;
+} mc_series_inputs;
+int mc_prepare_inputs(mc_handle* h, const double* d_close, const uint32_t* d_lengths, uint32_t n_series,
+                      uint32_t n_obs, uint64_t close_ld, uint32_t first_row, int32_t pool_dtype, void* d_pool,
+                      uint64_t pool_ld, mc_series_inputs* d_inputs, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -22,7 +22,7 @@ EXPORTS = (
     "mc_abi_version", "mc_create", "mc_destroy", "mc_last_error", "mc_run",
     "mc_stage_begin", "mc_stage_words", "mc_stage_max_words", "mc_stage_next", "mc_fetch_result",
     "mc_stage_reads_paths", "mc_stage_resimulate",
-    "mc_debug_shocks", "mc_debug_philox", "mc_percentiles", "mc_histogram",
+    "mc_debug_shocks", "mc_debug_philox", "mc_percentiles", "mc_histogram", "mc_prepare_inputs",
 )
 
 
@@ -68,6 +68,15 @@ class McResult(C.Structure):
     ]
 
 
+class McSeriesInputs(C.Structure):
+    """mc_series_inputs (include/mc_b200.h): what app.py:592/606/609/1213 derive from one price history."""
+    _fields_ = [("s0", C.c_double), ("var0", C.c_double), ("pool_std", C.c_double),
+                ("pool_len", C.c_uint64), ("flags", C.c_uint64)]
+
+
+INPUT_NAN = 1
+SERIES_INPUTS_DTYPE = [("s0", "<f8"), ("var0", "<f8"), ("pool_std", "<f8"), ("pool_len", "<u8"), ("flags", "<u8")]
+
 _lock = threading.Lock()
 _lib = None
 
@@ -107,6 +116,8 @@ def _declare(lib):
     lib.mc_percentiles.argtypes = [vp, vp, i32, u64, u64, u64, C.POINTER(dbl), u32, vp, vp]
     lib.mc_histogram.restype = C.c_int
     lib.mc_histogram.argtypes = [vp, vp, i32, u64, u32, dbl, dbl, vp, vp]
+    lib.mc_prepare_inputs.restype = C.c_int
+    lib.mc_prepare_inputs.argtypes = [vp, vp, vp, u32, u32, u64, u32, i32, vp, u64, vp, vp]
 
 
 def load_library(path: str | None = None):

@@ -127,9 +127,19 @@ def garch_monte_carlo(df, n_sims: int, n_days: int, current_price: float, progre
         return None
     if progress_callback:                              # app.py:597-598
         progress_callback("Running Monte Carlo simulation...")
-    n_sims, n_days = int(n_sims), int(n_days)
     current_var = rvol_last ** 2 / 252                 # app.py:606
     pool = bootstrap_pool(returns)                     # app.py:609
+    return _reference_model(pool, current_var, current_price, n_sims, n_days, seed=seed, dtype=dtype,
+                            return_paths=return_paths, omega=omega, alpha=alpha, beta=beta, shock=shock,
+                            injected_shocks=injected_shocks, hist_bins=hist_bins, hist_range=hist_range,
+                            device=device, group=group, fan_chart=fan_chart)
+
+
+def _reference_model(pool, current_var, current_price, n_sims, n_days, *, seed, dtype, return_paths, omega, alpha,
+                     beta, shock, injected_shocks, hist_bins, hist_range, device, group, fan_chart) -> Dict:
+    """app.py:612-657 on the device, from the routine's derived inputs (host array or device tensor pool)."""
+    from .engine import get_engine
+    n_sims, n_days = int(n_sims), int(n_days)
     store, how = _decide_paths(n_sims, n_days, dtype, return_paths)
     if group is not None and how == "numpy" and return_paths in (None, "auto"):
         how = "device"                                 # shards stay on their home GPU
@@ -137,7 +147,7 @@ def garch_monte_carlo(df, n_sims: int, n_days: int, current_price: float, progre
     want_fan = (store or injected_shocks is None) if fan_chart is None else bool(fan_chart)
     keep, fan, chunk = _fan_plan(store, want_fan, n_sims, n_days, dtype)
     spec = SimSpec(n_paths=n_sims, n_steps=n_days, s0=float(current_price), shock=shock, var_model="garch",
-                   var0=current_var, omega=omega, alpha=alpha, beta=beta, dtype=dtype,
+                   var0=float(current_var), omega=omega, alpha=alpha, beta=beta, dtype=dtype,
                    seed=_new_seed() if seed is None else int(seed), store_paths=keep, fan_chart=fan,
                    fan_chunk_paths=chunk,
                    pcts=REF_TERMINAL_PCTS, path_pcts=REF_PATH_PCTS, tail_pct=REF_TAIL_PCT,
@@ -145,6 +155,46 @@ def garch_monte_carlo(df, n_sims: int, n_days: int, current_price: float, progre
     out = get_engine(device).simulate(spec, pool=pool if shock == "bootstrap" else None,
                                       shocks=injected_shocks, group=group, keep_paths=store)
     return _result_dict(out, float(current_price), how)
+
+
+SMA_WARMUP_ROWS = 199      # close.rolling(200).mean() (app.py:252) is NaN on rows 0..198; app.py:393 drops those rows
+
+
+def garch_monte_carlo_from_close(close, n_sims: int, n_days: int, progress_callback=None, *, lengths=None,
+                                 first_row: int = SMA_WARMUP_ROWS, seed: Optional[int] = None,
+                                 dtype: str = "float64", return_paths="auto", omega: float = REF_OMEGA,
+                                 alpha: float = REF_ALPHA, beta: float = REF_BETA, hist_bins: int = 0,
+                                 hist_range=None, device: Optional[int] = None, fan_chart: Optional[bool] = None):
+    """The routine straight from close prices, without pandas: the device derives `log_ret`,
+    `rvol_20`, `std_returns`, `current_var` and `current_price` (app.py:224, 233, 392-393, 592, 606, 609, 1213)
+    for every price history in one launch, then runs the model of app.py:612-657 per history.
+
+    `close`: one history (1-D -> one result) or [n_series, n_obs] (-> list of results; `lengths[b]` prices are
+    valid in row b).  An entry is None where the reference returns None (fewer than 100 returns left,
+    app.py:594-595).  Seeds: history b uses `seed + b`.  Raises ValueError for NaN / non-positive prices (the
+    reference would silently drop such rows)."""
+    from . import _lib as L
+    from .engine import get_engine
+    single = getattr(close, "ndim", None) == 1 or (hasattr(close, "dim") and close.dim() == 1)
+    eng = get_engine(device)
+    pool, info = eng.prepare_inputs(close, lengths, first_row, dtype)
+    if np.any(info["flags"] & L.INPUT_NAN):
+        raise ValueError("close prices must be positive and finite")
+    base = _new_seed() if seed is None else int(seed)
+    results = []
+    for b in range(len(info)):
+        n = int(info["pool_len"][b])
+        if n < MIN_HISTORY:                            # app.py:594-595
+            results.append(None)
+            continue
+        if progress_callback:                          # app.py:597-598
+            progress_callback("Running Monte Carlo simulation...")
+        results.append(_reference_model(pool[b, :n], float(info["var0"][b]), float(info["s0"][b]), n_sims, n_days,
+                                        seed=(base + b) & 0xFFFFFFFFFFFFFFFF, dtype=dtype, return_paths=return_paths,
+                                        omega=omega, alpha=alpha, beta=beta, shock="bootstrap", injected_shocks=None,
+                                        hist_bins=hist_bins, hist_range=hist_range, device=device, group=None,
+                                        fan_chart=fan_chart))
+    return results[0] if single else results
 
 
 def simulate_gbm(n_sims: int, n_days: int, current_price: float, mu: float, sigma: float, *,

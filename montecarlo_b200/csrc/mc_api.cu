@@ -17,6 +17,7 @@
 #include <string>
 #include <vector>
 
+#include "mc_inputs.cuh"
 #include "mc_select.cuh"
 #include "mc_sim.cuh"
 
@@ -659,6 +660,23 @@ int mc_histogram(mc_handle* h, const void* d_x, int32_t dtype, uint64_t n, uint3
                                 h->stage.p, h->dev.sm_count, s));
     MC_CUDA(h, cudaMemcpyAsync(h_counts, h->stage.p + 2, (size_t)bins * 8, cudaMemcpyDeviceToHost, s));
     MC_CUDA(h, cudaStreamSynchronize(s));
+    return MC_OK;
+}
+
+int mc_prepare_inputs(mc_handle* h, const double* d_close, const uint32_t* d_lengths, uint32_t n_series, uint32_t n_obs,
+                      uint64_t close_ld, uint32_t first_row, int32_t pool_dtype, void* d_pool, uint64_t pool_ld,
+                      mc_series_inputs* d_inputs, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (n_series && (!d_close || !d_pool || !d_inputs)) return fail(h, MC_ERR_INVALID, "mc_prepare_inputs: NULL buffer");
+    if (pool_dtype != MC_F32 && pool_dtype != MC_F64) return fail(h, MC_ERR_INVALID, "mc_prepare_inputs: bad pool dtype");
+    if (close_ld < n_obs) return fail(h, MC_ERR_INVALID, "mc_prepare_inputs: close_ld < n_obs");
+    const uint32_t start = first_row > 20u ? first_row : 20u;
+    if (n_obs > start && pool_ld < (uint64_t)(n_obs - start))
+        return fail(h, MC_ERR_INVALID, "mc_prepare_inputs: pool_ld < n_obs - max(first_row, 20)");
+    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_CUDA(h, launch_prepare_inputs(d_close, d_lengths, n_series, n_obs, close_ld, first_row, pool_dtype, d_pool, pool_ld,
+                                     d_inputs, static_cast<cudaStream_t>(stream)));
     return MC_OK;
 }
 

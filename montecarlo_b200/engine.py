@@ -322,6 +322,36 @@ class Engine:
                                          C.c_void_p(out.ctypes.data), self.stream_ptr()))
         return out.astype(np.int64)
 
+    def prepare_inputs(self, close, lengths=None, first_row: int = 199, dtype: str = "float64"):
+        """What the routine reads, from close prices [n_series, n_obs] (host array or device tensor), on the
+        device (producers app.py:224, 233, 392-393, 592, 606, 609).  Returns (pool, info): `pool`
+        a device tensor [n_series, pool_ld] in `dtype`, `info` a host structured array with the fields of
+        `mc_series_inputs` (one small device->host copy, the only synchronisation)."""
+        close_t = self.to_device(close, torch.float64)
+        if close_t.dim() == 1:
+            close_t = close_t.view(1, -1)
+        if close_t.stride(1) != 1:
+            close_t = close_t.contiguous()
+        n_series, n_obs = close_t.shape
+        len_t = None
+        if lengths is not None:
+            len_t = self.to_device(np.ascontiguousarray(lengths, dtype=np.int32) if not isinstance(lengths, torch.Tensor)
+                                   else lengths, torch.int32)
+            if len_t.numel() != n_series:
+                raise ValueError("lengths must have one entry per series")
+        pool_ld = max(1, n_obs - max(int(first_row), 20))
+        pool_ld = (pool_ld + 3) // 4 * 4
+        dt = torch.float64 if dtype == "float64" else torch.float32
+        with torch.cuda.device(self.device):
+            pool = torch.empty((n_series, pool_ld), dtype=dt, device=self.device)
+            info_t = torch.empty((n_series, C.sizeof(L.McSeriesInputs) // 8), dtype=torch.int64, device=self.device)
+            self.check(self.lib.mc_prepare_inputs(self.handle, C.c_void_p(close_t.data_ptr()), _CudaStageBackend._ptr(len_t),
+                                                  n_series, n_obs, close_t.stride(0), int(first_row),
+                                                  L.F64 if dtype == "float64" else L.F32, C.c_void_p(pool.data_ptr()),
+                                                  pool_ld, C.c_void_p(info_t.data_ptr()), self.stream_ptr()))
+            info = info_t.cpu().numpy().view(np.dtype(L.SERIES_INPUTS_DTYPE)).reshape(n_series)
+        return pool, info
+
     def debug_shocks(self, spec: SimSpec, pool=None, path_offset=0, n_local=None) -> torch.Tensor:
         dt = self._torch_dtype(spec)
         pool_t = self.to_device(pool, dt) if pool is not None else None

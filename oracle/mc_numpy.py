@@ -26,6 +26,29 @@ def bootstrap_pool(returns):
     return r / (r.std() + 1e-10)
 
 
+SMA_WARMUP_ROWS = 199     # close.rolling(200).mean() (app.py:252) is NaN on rows 0..198; app.py:393 drops them
+
+
+def history_inputs(close, first_row=SMA_WARMUP_ROWS):
+    """What the routine reads, from a close-price history, with the reference's own pandas
+    calls: log_ret (app.py:224), rvol_20 (app.py:233), rows >= first_row kept (app.py:392-393), then
+    returns (app.py:592), current_var (app.py:606), std_returns (app.py:609), current_price (app.py:1213).
+    Returns None when nothing is left, else dict(returns, pool, pool_std, var0, s0, rvol_last)."""
+    import pandas as pd
+    close = pd.Series(np.asarray(close, dtype=np.float64))
+    log_ret = np.log(close / close.shift(1))
+    rvol_20 = log_ret.rolling(20).std() * np.sqrt(252)
+    frame = pd.DataFrame({"Close": close, "log_ret": log_ret, "rvol_20": rvol_20})
+    frame = frame.replace([np.inf, -np.inf], 0).iloc[first_row:].dropna()
+    if len(frame) == 0:
+        return None
+    returns = frame["log_ret"].dropna().values
+    rvol_last = float(frame["rvol_20"].iloc[-1])
+    std = np.std(returns)
+    return dict(returns=returns, pool=returns / (std + 1e-10), pool_std=float(std), rvol_last=rvol_last,
+                var0=initial_variance(rvol_last), s0=float(frame["Close"].iloc[-1]))
+
+
 def initial_variance(rvol_last):
     """annualised vol -> daily variance (app.py:606)."""
     return float(rvol_last) ** 2 / 252

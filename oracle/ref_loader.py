@@ -35,6 +35,22 @@ def load_reference_function(path: str = DEFAULT_REFERENCE, np_module=np):
     return ns["garch_monte_carlo"]
 
 
+def load_reference_features(path: str = DEFAULT_REFERENCE):
+    """The unmodified `add_all_features` (app.py:210-395) with the indicator helpers it calls
+    (`compute_rsi`, `compute_atr`, `compute_macd`, app.py:180-208): the producer of the two columns the
+    routine reads, `log_ret` (app.py:224) and `rvol_20` (app.py:233), and of the row dropping (app.py:392-393)."""
+    import typing
+
+    import pandas as pd
+    with open(path, "r") as fh:
+        tree = ast.parse(fh.read(), filename=path)
+    nodes = [n for n in tree.body if isinstance(n, ast.FunctionDef)
+             and (n.name.startswith("compute_") or n.name == "add_all_features")]
+    ns = {"np": np, "pd": pd, "Optional": Optional, "Dict": Dict, "Tuple": typing.Tuple, "List": typing.List}
+    exec(compile(ast.Module(body=nodes, type_ignores=[]), path, "exec"), ns)
+    return ns["add_all_features"]
+
+
 class _ChoiceProxy:
     """Stands in for `np.random` inside the reference so that a supplied matrix of
     shocks (or pool indices) is what `np.random.choice` (app.py:620) returns."""
@@ -74,3 +90,15 @@ def synthetic_frame(n_rows: int = 1250, seed: int = 0, heavy_tail: bool = False)
     else:
         r = rs.normal(0.0, 0.02, n_rows)
     return pd.DataFrame({"log_ret": r, "rvol_20": np.full(n_rows, 0.02 * np.sqrt(252))})
+
+
+def synthetic_ohlcv(n_rows: int = 1260, seed: int = 11, s0: float = 120.0, heavy_tail: bool = False):
+    """Five years of business days, the shape `get_stock_data(ticker, period="5y")` hands over (app.py:1207)."""
+    import pandas as pd
+    rs = np.random.RandomState(seed)
+    r = rs.standard_t(4, n_rows) * 0.012 if heavy_tail else rs.normal(3e-4, 0.017, n_rows)
+    close = s0 * np.exp(np.cumsum(r))
+    spread = np.abs(rs.normal(0.0, 0.006, n_rows))
+    idx = pd.bdate_range("2020-01-01", periods=n_rows)
+    return pd.DataFrame({"Open": close * (1 - 0.3 * spread), "High": close * (1 + spread), "Low": close * (1 - spread),
+                         "Close": close, "Volume": rs.randint(1_000_000, 9_000_000, n_rows).astype(np.float64)}, index=idx)
