@@ -226,6 +226,39 @@ int mc_prepare_inputs(mc_handle* h, const double* d_close, const uint32_t* d_len
                       uint32_t n_obs, uint64_t close_ld, uint32_t first_row, int32_t pool_dtype, void* d_pool,
                       uint64_t pool_ld, mc_series_inputs* d_inputs, void* stream);
 
+/*
+ * The reference's model (bootstrap shocks + GARCH(1,1), app.py:612-657, fp64) for n_series price histories
+ * in one pass: ONE simulation launch over (paths x histories), one exact selection over the [n_series, n_paths]
+ * terminal matrix, one reduction launch, and (with MC_FLAG_FAN_CHART) one selection over the
+ * n_series * (n_steps + 1) rows of the stored paths -- instead of ~20 launches per history.  Pools and
+ * per-history scalars come from mc_prepare_inputs and are read from device memory.  History b draws from the
+ * Philox key seed + b and steps exactly like mc_run in fp64, so its paths, percentiles and fan chart are
+ * bit-identical to a single mc_run with that seed.  A history with fewer than `min_history` returns (100 in the
+ * reference, app.py:594-595) or a NaN flag is skipped: h_results[b].n == 0.
+ *   d_paths     [n_series, n_steps + 1, n_paths] fp64 (MC_FLAG_STORE_PATHS) or NULL
+ *   d_terminal  [n_series, n_paths] fp64
+ *   h_results   [n_series] (host); pct/pct_lo/pct_hi as in mc_run; sim_ms/total_ms/launches describe the batch
+ *   h_fan       [n_series, n_steps + 1, n_path_pcts] fp64 (host) or NULL
+ */
+typedef struct mc_batch_params {
+    uint32_t struct_size;        /* sizeof(mc_batch_params) */
+    uint32_t version;            /* MC_ABI_VERSION */
+    uint64_t n_paths;            /* per history */
+    uint64_t seed;
+    uint32_t n_steps;
+    uint32_t n_series;
+    uint32_t min_history;
+    uint32_t flags;              /* MC_FLAG_STORE_PATHS | MC_FLAG_FAN_CHART */
+    double omega, alpha, beta;   /* app.py:601-603 */
+    uint32_t n_pcts, n_path_pcts;
+    double pcts[MC_MAX_PCTS];
+    double path_pcts[MC_MAX_PATH_PCTS];
+    double tail_pct;             /* < 0: none */
+} mc_batch_params;
+int mc_run_batch(mc_handle* h, const mc_batch_params* p, const void* d_pool, uint64_t pool_ld,
+                 const mc_series_inputs* d_inputs, void* d_paths, void* d_terminal, mc_result* h_results,
+                 double* h_fan, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

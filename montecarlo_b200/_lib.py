@@ -23,6 +23,7 @@ EXPORTS = (
     "mc_stage_begin", "mc_stage_words", "mc_stage_max_words", "mc_stage_next", "mc_fetch_result",
     "mc_stage_reads_paths", "mc_stage_resimulate",
     "mc_debug_shocks", "mc_debug_philox", "mc_percentiles", "mc_histogram", "mc_prepare_inputs",
+    "mc_run_batch",
 )
 
 
@@ -74,6 +75,19 @@ class McSeriesInputs(C.Structure):
                 ("pool_len", C.c_uint64), ("flags", C.c_uint64)]
 
 
+class McBatchParams(C.Structure):
+    """mc_batch_params (include/mc_b200.h)."""
+    _fields_ = [
+        ("struct_size", C.c_uint32), ("version", C.c_uint32),
+        ("n_paths", C.c_uint64), ("seed", C.c_uint64),
+        ("n_steps", C.c_uint32), ("n_series", C.c_uint32), ("min_history", C.c_uint32), ("flags", C.c_uint32),
+        ("omega", C.c_double), ("alpha", C.c_double), ("beta", C.c_double),
+        ("n_pcts", C.c_uint32), ("n_path_pcts", C.c_uint32),
+        ("pcts", C.c_double * MC_MAX_PCTS), ("path_pcts", C.c_double * MC_MAX_PATH_PCTS),
+        ("tail_pct", C.c_double),
+    ]
+
+
 INPUT_NAN = 1
 SERIES_INPUTS_DTYPE = [("s0", "<f8"), ("var0", "<f8"), ("pool_std", "<f8"), ("pool_len", "<u8"), ("flags", "<u8")]
 
@@ -118,6 +132,8 @@ def _declare(lib):
     lib.mc_histogram.argtypes = [vp, vp, i32, u64, u32, dbl, dbl, vp, vp]
     lib.mc_prepare_inputs.restype = C.c_int
     lib.mc_prepare_inputs.argtypes = [vp, vp, vp, u32, u32, u64, u32, i32, vp, u64, vp, vp]
+    lib.mc_run_batch.restype = C.c_int
+    lib.mc_run_batch.argtypes = [vp, C.POINTER(McBatchParams), vp, u64, vp, vp, vp, vp, vp, vp]
 
 
 def load_library(path: str | None = None):

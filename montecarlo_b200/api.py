@@ -164,14 +164,17 @@ def garch_monte_carlo_from_close(close, n_sims: int, n_days: int, progress_callb
                                  first_row: int = SMA_WARMUP_ROWS, seed: Optional[int] = None,
                                  dtype: str = "float64", return_paths="auto", omega: float = REF_OMEGA,
                                  alpha: float = REF_ALPHA, beta: float = REF_BETA, hist_bins: int = 0,
-                                 hist_range=None, device: Optional[int] = None, fan_chart: Optional[bool] = None):
+                                 hist_range=None, device: Optional[int] = None, fan_chart: Optional[bool] = None,
+                                 batched: Optional[bool] = None):
     """The routine straight from close prices, without pandas: the device derives `log_ret`,
     `rvol_20`, `std_returns`, `current_var` and `current_price` (app.py:224, 233, 392-393, 592, 606, 609, 1213)
     for every price history in one launch, then runs the model of app.py:612-657 per history.
 
     `close`: one history (1-D -> one result) or [n_series, n_obs] (-> list of results; `lengths[b]` prices are
     valid in row b).  An entry is None where the reference returns None (fewer than 100 returns left,
-    app.py:594-595).  Seeds: history b uses `seed + b`.  Raises ValueError for NaN / non-positive prices (the
+    app.py:594-595).  Seeds: history b uses `seed + b`.  `batched` (default: 2-D fp64 input): all histories go
+    through ONE simulation launch and one selection per result kind (`mc_run_batch`) instead of one run per
+    history; the results are bit-identical either way.  Raises ValueError for NaN / non-positive prices (the
     reference would silently drop such rows)."""
     from . import _lib as L
     from .engine import get_engine
@@ -181,20 +184,52 @@ def garch_monte_carlo_from_close(close, n_sims: int, n_days: int, progress_callb
     if np.any(info["flags"] & L.INPUT_NAN):
         raise ValueError("close prices must be positive and finite")
     base = _new_seed() if seed is None else int(seed)
+    n_sims, n_days = int(n_sims), int(n_days)
+    live = [int(n) >= MIN_HISTORY for n in info["pool_len"]]       # app.py:594-595
+    if progress_callback:                                          # app.py:597-598, once per history that runs
+        for ok in live:
+            if ok:
+                progress_callback("Running Monte Carlo simulation...")
+    if batched is None:       # the batched run is fp64, no histogram, fan chart from stored paths
+        keeps_paths = _decide_paths(n_sims, n_days, dtype, return_paths)[0]
+        batched = not single and dtype == "float64" and hist_bins == 0 and (keeps_paths or fan_chart is False)
+    if batched:
+        if dtype != "float64" or hist_bins:
+            raise ValueError("the batched run is fp64 without histogram")
+        res = _run_batches(eng, pool, info, n_sims, n_days, base, omega, alpha, beta, return_paths, fan_chart)
+        return res[0] if single else res
     results = []
     for b in range(len(info)):
-        n = int(info["pool_len"][b])
-        if n < MIN_HISTORY:                            # app.py:594-595
+        if not live[b]:
             results.append(None)
             continue
-        if progress_callback:                          # app.py:597-598
-            progress_callback("Running Monte Carlo simulation...")
+        n = int(info["pool_len"][b])
         results.append(_reference_model(pool[b, :n], float(info["var0"][b]), float(info["s0"][b]), n_sims, n_days,
                                         seed=(base + b) & 0xFFFFFFFFFFFFFFFF, dtype=dtype, return_paths=return_paths,
                                         omega=omega, alpha=alpha, beta=beta, shock="bootstrap", injected_shocks=None,
                                         hist_bins=hist_bins, hist_range=hist_range, device=device, group=None,
                                         fan_chart=fan_chart))
     return results[0] if single else results
+
+
+BATCH_PATHS_BYTES = 8 << 30       # histories are simulated together while their stored paths fit this
+
+
+def _run_batches(eng, pool, info, n_sims, n_days, base, omega, alpha, beta, return_paths, fan_chart):
+    store, how = _decide_paths(n_sims, n_days, "float64", return_paths)
+    want_fan = store if fan_chart is None else bool(fan_chart)
+    if want_fan and not store:
+        raise ValueError("the batched run takes the fan chart from stored paths: pass return_paths='device'")
+    per_series = (n_days + 1) * n_sims * 8 if store else n_sims * 8
+    step = max(1, min(len(info), BATCH_PATHS_BYTES // per_series))
+    results = []
+    for b0 in range(0, len(info), step):
+        sl = slice(b0, min(len(info), b0 + step))
+        outs = eng.simulate_batch(pool[sl], info[sl], n_sims, n_days, (base + b0) & 0xFFFFFFFFFFFFFFFF,
+                                  omega=omega, alpha=alpha, beta=beta, pcts=REF_TERMINAL_PCTS,
+                                  path_pcts=REF_PATH_PCTS, tail_pct=REF_TAIL_PCT, store_paths=store, fan_chart=want_fan)
+        results += [None if o is None else _result_dict(o, o.spec.s0, how) for o in outs]
+    return results
 
 
 def simulate_gbm(n_sims: int, n_days: int, current_price: float, mu: float, sigma: float, *,

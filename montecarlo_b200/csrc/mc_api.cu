@@ -82,6 +82,8 @@ struct mc_handle {
     DevBuf<double> edges;
     DevBuf<unsigned long long> hist_total;
     DevBuf<unsigned long long> stage;   // internal stage buffer (mc_run, mc_percentiles)
+    DevBuf<double> batch_pct;           // mc_run_batch: [3][n_series][n_pcts]
+    DevBuf<mc_result> batch_res;        // mc_run_batch: [n_series]
     PinnedBuf<unsigned char> h_stage;   // pinned staging for the D2H of results
     cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t ev_pending = nullptr;   // recorded after the D2H copy of `pending`
@@ -194,6 +196,47 @@ int upload_plan(mc_handle* h, SelectProblem& sp, int slot, cudaStream_t s) {
     return MC_OK;
 }
 
+// np.percentile(x[r, :], pcts) for `rows` rows of a device matrix, results left on the device:
+// d_out[rows][n_pcts] (and the two order statistics each one interpolates, if wanted).  Synchronises the
+// stream once per narrowing pass after the first (the host reads the count of undecided rows).
+int select_rows(mc_handle* h, const void* d_x, int dtype, uint64_t rows, uint64_t n, uint64_t ld, const double* pcts,
+                uint32_t n_pcts, bool iid_columns, double* d_out, double* d_lo, double* d_hi, unsigned* launches,
+                cudaStream_t s) {
+    SelectProblem sp{};
+    if (!build_select_plan(pcts, (int)n_pcts, n, dtype, &sp.plan))
+        return fail(h, MC_ERR_INVALID, "percentiles must be ascending and within [0, 100]");
+    sp.x = d_x; sp.dtype = dtype; sp.rows = rows; sp.n = n; sp.ld = ld;
+    setup_sampling(sp, 1, iid_columns);                // arbitrary data: strided sample
+    MC_CUDA(h, h->states_f.reserve(rows));
+    MC_CUDA(h, h->scratch_f.reserve(rows));
+    sp.d_states = h->states_f.p;
+    sp.d_scratch = h->scratch_f.p;
+    int rc = upload_plan(h, sp, 1, s);
+    if (rc) return rc;
+    const size_t w0 = STAGE0_HEADER + sample_words(sp), wk = pass_words(sp);
+    MC_CUDA(h, h->stage.reserve(w0 > wk ? w0 : wk));
+    unsigned long long* st = h->stage.p;
+    unsigned count = 0;
+    MC_CUDA(h, launch_reduce_partials(h->partials.p, 0, st, 0, sp.m_local, s));
+    MC_CUDA(h, launch_select_sample(sp, st + STAGE0_HEADER, s));
+    MC_CUDA(h, launch_select_brackets(sp, st, STAGE0_HEADER, 7, 1, w0, h->dev.max_smem_optin, s));
+    count += 3;
+    for (int pass = 0;; ++pass) {
+        MC_CUDA(h, launch_select_pass(sp, pass == 0, st, h->dev.sm_count, s));
+        MC_CUDA(h, cudaMemsetAsync(h->pending.p, 0, sizeof(unsigned int), s));
+        MC_CUDA(h, launch_select_scan(sp, st, 1, wk, h->pending.p, s));
+        count += 3;
+        if (pass == 0) continue;
+        MC_CUDA(h, cudaMemcpyAsync(h->h_pending.p, h->pending.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
+        MC_CUDA(h, cudaStreamSynchronize(s));
+        if (*h->h_pending.p == 0) break;
+        if (pass + 1 >= SEL_MAX_PASSES) return fail(h, MC_ERR_STATE, "selection did not converge");
+    }
+    MC_CUDA(h, launch_select_finish(sp, d_out, d_lo, d_hi, s));
+    if (launches) *launches += count + 1;
+    return MC_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -246,6 +289,7 @@ int mc_destroy(mc_handle* h) {
     cudaSetDevice(h->device);
     h->partials.release(); h->lut.release(); h->res.release(); h->plans.release(); h->states_t.release(); h->states_f.release(); h->scratch_t.release(); h->scratch_f.release();
     h->pct_t.release(); h->fan.release(); h->tail_scratch.release(); h->edges.release(); h->hist_total.release();
+    h->batch_pct.release(); h->batch_res.release();
     h->stage.release(); h->h_stage.release(); h->pending.release(); h->h_pending.release();
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->ev_pending) cudaEventDestroy(h->ev_pending);
@@ -610,35 +654,9 @@ int mc_percentiles(mc_handle* h, const void* d_x, int32_t dtype, uint64_t rows, 
         return fail(h, MC_ERR_INVALID, "bad mc_percentiles arguments");
     if (h->active) return fail(h, MC_ERR_STATE, "a staged run is in flight on this handle");
     MC_CUDA(h, cudaSetDevice(h->device));
-    SelectProblem sp{};
-    if (!build_select_plan(pcts, (int)n_pcts, n, dtype, &sp.plan))
-        return fail(h, MC_ERR_INVALID, "percentiles must be ascending and within [0, 100]");
-    sp.x = d_x; sp.dtype = dtype; sp.rows = rows; sp.n = n; sp.ld = ld;
-    setup_sampling(sp, 1, false);                      // arbitrary data: strided sample
-    MC_CUDA(h, h->states_f.reserve(rows));
-    MC_CUDA(h, h->scratch_f.reserve(rows));
     MC_CUDA(h, h->fan.reserve(rows * n_pcts));
-    sp.d_states = h->states_f.p;
-    sp.d_scratch = h->scratch_f.p;
-    int rc = upload_plan(h, sp, 1, s);
+    int rc = select_rows(h, d_x, dtype, rows, n, ld, pcts, n_pcts, false, h->fan.p, nullptr, nullptr, nullptr, s);
     if (rc) return rc;
-    const size_t w0 = STAGE0_HEADER + sample_words(sp), wk = pass_words(sp);
-    MC_CUDA(h, h->stage.reserve(w0 > wk ? w0 : wk));
-    unsigned long long* st = h->stage.p;
-    MC_CUDA(h, launch_reduce_partials(h->partials.p, 0, st, 0, sp.m_local, s));
-    MC_CUDA(h, launch_select_sample(sp, st + STAGE0_HEADER, s));
-    MC_CUDA(h, launch_select_brackets(sp, st, STAGE0_HEADER, 7, 1, w0, h->dev.max_smem_optin, s));
-    for (int pass = 0;; ++pass) {
-        MC_CUDA(h, launch_select_pass(sp, pass == 0, st, h->dev.sm_count, s));
-        MC_CUDA(h, cudaMemsetAsync(h->pending.p, 0, sizeof(unsigned int), s));
-        MC_CUDA(h, launch_select_scan(sp, st, 1, wk, h->pending.p, s));
-        if (pass == 0) continue;
-        MC_CUDA(h, cudaMemcpyAsync(h->h_pending.p, h->pending.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
-        MC_CUDA(h, cudaStreamSynchronize(s));
-        if (*h->h_pending.p == 0) break;
-        if (pass + 1 >= SEL_MAX_PASSES) return fail(h, MC_ERR_STATE, "selection did not converge");
-    }
-    MC_CUDA(h, launch_select_finish(sp, h->fan.p, nullptr, nullptr, s));
     MC_CUDA(h, cudaMemcpyAsync(h_out, h->fan.p, rows * n_pcts * sizeof(double), cudaMemcpyDeviceToHost, s));
     MC_CUDA(h, cudaStreamSynchronize(s));
     return MC_OK;
@@ -677,6 +695,88 @@ int mc_prepare_inputs(mc_handle* h, const double* d_close, const uint32_t* d_len
     MC_CUDA(h, cudaSetDevice(h->device));
     MC_CUDA(h, launch_prepare_inputs(d_close, d_lengths, n_series, n_obs, close_ld, first_row, pool_dtype, d_pool, pool_ld,
                                      d_inputs, static_cast<cudaStream_t>(stream)));
+    return MC_OK;
+}
+
+int mc_run_batch(mc_handle* h, const mc_batch_params* p, const void* d_pool, uint64_t pool_ld,
+                 const mc_series_inputs* d_inputs, void* d_paths, void* d_terminal, mc_result* h_results,
+                 double* h_fan, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (!p) return fail(h, MC_ERR_INVALID, "params is NULL");
+    if (p->struct_size != sizeof(mc_batch_params) || p->version != MC_ABI_VERSION)
+        return fail(h, MC_ERR_VERSION, "mc_batch_params struct_size/version mismatch");
+    if (h->active) return fail(h, MC_ERR_STATE, "a staged run is in flight on this handle");
+    const bool store = p->flags & MC_FLAG_STORE_PATHS, fan = (p->flags & MC_FLAG_FAN_CHART) && p->n_path_pcts;
+    if (p->n_series == 0 || p->n_series > 65535) return fail(h, MC_ERR_INVALID, "n_series must be 1..65535");
+    if (p->n_paths == 0 || p->n_paths >= (1ull << 32)) return fail(h, MC_ERR_INVALID, "n_paths out of range");
+    if (p->n_steps == 0 || p->n_steps > 1000000u) return fail(h, MC_ERR_INVALID, "n_steps out of range");
+    if (!d_pool || !d_inputs || !d_terminal || !h_results) return fail(h, MC_ERR_INVALID, "mc_run_batch: NULL buffer");
+    if (store && !d_paths) return fail(h, MC_ERR_INVALID, "d_paths is NULL");
+    if (fan && (!store || !h_fan)) return fail(h, MC_ERR_INVALID, "fan chart needs stored paths and h_fan");
+    if (p->n_pcts > MC_MAX_PCTS || p->n_path_pcts > MC_MAX_PATH_PCTS) return fail(h, MC_ERR_INVALID, "too many percentiles");
+    int tail_idx = -1;
+    if (p->tail_pct >= 0.0) {
+        for (unsigned k = 0; k < p->n_pcts; ++k) if (p->pcts[k] == p->tail_pct) tail_idx = (int)k;
+        if (tail_idx < 0) return fail(h, MC_ERR_INVALID, "tail_pct must be one of pcts");
+    }
+    MC_CUDA(h, cudaSetDevice(h->device));
+    const size_t B = p->n_series, np = p->n_pcts ? p->n_pcts : 1;
+    MC_CUDA(h, h->batch_pct.reserve(3 * B * np));
+    MC_CUDA(h, h->batch_res.reserve(B));
+    unsigned launches = 0;
+
+    MC_CUDA(h, cudaEventRecord(h->ev[0], s));
+    BatchSimArgs a{};
+    a.n_paths = p->n_paths; a.ld_terminal = p->n_paths; a.ld_paths = p->n_paths; a.pool_ld = pool_ld; a.seed = p->seed;
+    a.n_steps = p->n_steps; a.n_series = p->n_series; a.min_history = p->min_history;
+    a.omega = p->omega; a.alpha = p->alpha; a.beta = p->beta;
+    a.pool = static_cast<const double*>(d_pool); a.inputs = d_inputs;
+    a.paths = static_cast<double*>(d_paths); a.terminal = static_cast<double*>(d_terminal);
+    MC_CUDA(h, launch_batch_simulation(a, store, h->dev.sm_count, s));
+    ++launches;
+    MC_CUDA(h, cudaEventRecord(h->ev[1], s));
+
+    double* d_pct = h->batch_pct.p;
+    double* d_lo = d_pct + B * np;
+    double* d_hi = d_lo + B * np;
+    int rc;
+    if (p->n_pcts) {
+        if ((rc = select_rows(h, d_terminal, MC_F64, B, p->n_paths, p->n_paths, p->pcts, p->n_pcts, true, d_pct, d_lo,
+                              d_hi, &launches, s)))
+            return rc;
+    }
+    MC_CUDA(h, launch_batch_stats(a.terminal, p->n_paths, p->n_paths, p->n_series, d_inputs, p->min_history, d_pct, d_lo,
+                                  d_hi, (int)p->n_pcts, tail_idx, h->batch_res.p, s));
+    ++launches;
+    MC_CUDA(h, cudaMemcpyAsync(h_results, h->batch_res.p, B * sizeof(mc_result), cudaMemcpyDeviceToHost, s));
+    if (fan) {
+        // rows of the fan-chart problem: (history, step) pairs, at most 65535 per selection
+        const size_t rows_per = (size_t)p->n_steps + 1;
+        if (rows_per > 65535) return fail(h, MC_ERR_INVALID, "fan chart supports at most 65534 steps");
+        const size_t series_per_call = 65535 / rows_per;
+        MC_CUDA(h, h->fan.reserve(series_per_call * rows_per * p->n_path_pcts));
+        for (size_t b0 = 0; b0 < B; b0 += series_per_call) {
+            const size_t nb = (B - b0 < series_per_call) ? B - b0 : series_per_call;
+            const double* x = a.paths + b0 * rows_per * p->n_paths;
+            if ((rc = select_rows(h, x, MC_F64, nb * rows_per, p->n_paths, p->n_paths, p->path_pcts, p->n_path_pcts, true,
+                                  h->fan.p, nullptr, nullptr, &launches, s)))
+                return rc;
+            MC_CUDA(h, cudaMemcpyAsync(h_fan + b0 * rows_per * p->n_path_pcts, h->fan.p,
+                                       nb * rows_per * p->n_path_pcts * sizeof(double), cudaMemcpyDeviceToHost, s));
+            if (b0 + series_per_call < B) MC_CUDA(h, cudaStreamSynchronize(s));    // h->fan is reused
+        }
+    }
+    MC_CUDA(h, cudaEventRecord(h->ev[2], s));
+    MC_CUDA(h, cudaStreamSynchronize(s));
+    float sim_ms = 0.f, total_ms = 0.f;
+    MC_CUDA(h, cudaEventElapsedTime(&sim_ms, h->ev[0], h->ev[1]));
+    MC_CUDA(h, cudaEventElapsedTime(&total_ms, h->ev[0], h->ev[2]));
+    for (size_t b = 0; b < B; ++b) {
+        h_results[b].sim_ms = sim_ms; h_results[b].total_ms = total_ms;
+        h_results[b].launches = launches; h_results[b].reserved = 0;
+    }
     return MC_OK;
 }
 

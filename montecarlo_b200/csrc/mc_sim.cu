@@ -226,6 +226,81 @@ __global__ void __launch_bounds__(MAXB) sim_kernel(const __grid_constant__ SimAr
     finish_block(acc, s_warp, a.partials);
 }
 
+// ------------------------------------------------------------------ many price histories, one launch
+// the reference's model (bootstrap + GARCH, fp64) for n_series histories whose pools and
+// scalars were produced on the device (mc_inputs.cu).  blockIdx.y = history; the per-history scalars are read
+// from device memory, so nothing goes through the host between the producers and this kernel.  History b
+// uses Philox key seed + b and the arithmetic of sim_kernel<double, BOOTSTRAP, GARCH> (same draw/step
+// functions): its paths are bit-identical to a single call with that seed.
+template <bool STORE>
+__global__ void __launch_bounds__(BATCH_BLOCK) batch_sim_kernel(const BatchSimArgs b) {
+    extern __shared__ __align__(16) unsigned char smem_dyn[];
+    double* s_pool = reinterpret_cast<double*>(smem_dyn);
+    const uint32_t series = blockIdx.y;
+    const mc_series_inputs in = b.inputs[series];
+    const bool live = in.pool_len >= b.min_history && in.flags == 0;
+    double* terminal = b.terminal + (size_t)series * b.ld_terminal;
+    double* paths = STORE ? b.paths + (size_t)series * (b.n_steps + 1ull) * b.ld_paths : nullptr;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    const unsigned long long first = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (!live) {       // the reference returns None (app.py:594-595): rows of zeros keep the reductions defined
+        for (unsigned long long i = first; i < b.n_paths; i += stride) {
+            terminal[i] = 0.0;
+            if (STORE) for (uint32_t t = 0; t <= b.n_steps; ++t) paths[(unsigned long long)t * b.ld_paths + i] = 0.0;
+        }
+        return;
+    }
+    SimArgs<double> a;
+    const unsigned long long key = b.seed + series;
+    a.rk = expand_key((uint32_t)key, (uint32_t)(key >> 32));
+    a.pool = b.pool + (size_t)series * b.pool_ld;
+    a.pool_len = (uint32_t)in.pool_len;
+    a.pool_log2_copies = b.pool_in_smem ? 0 : -1;
+    a.n_steps = b.n_steps;
+    a.omega = b.omega; a.alpha = b.alpha; a.beta = b.beta;
+    if (b.pool_in_smem) {
+        for (uint32_t i = threadIdx.x; i < a.pool_len; i += blockDim.x) s_pool[i] = a.pool[i];
+        __syncthreads();
+    }
+    const double s0 = in.s0;
+    const uint32_t n_full = b.n_steps / 4;
+    for (unsigned long long i = first; i < b.n_paths; i += stride) {
+        const uint32_t c0 = (uint32_t)i, c1 = (uint32_t)(i >> 32);
+        double y = 0.0, v = in.var0;
+        if (STORE) paths[i] = s0;                                   // app.py:613
+        uint32_t t = 0;
+        for (uint32_t j = 0; j <= n_full; ++j) {
+            if (t >= b.n_steps) break;
+            double z[8];
+            draw<double, MC_SHOCK_BOOTSTRAP>(a, s_pool, i, c0, c1, j, t, z);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (t + k < b.n_steps) {
+                    step<double, MC_VAR_GARCH>(a, z[k], 0.0, y, v);
+                    if (STORE) paths[(unsigned long long)(t + k + 1) * b.ld_paths + i] = s0 * exp(y);
+                }
+            }
+            t += 4;
+        }
+        terminal[i] = s0 * exp(y);                                  // app.py:636
+    }
+}
+
+cudaError_t launch_batch_simulation(const BatchSimArgs& args, bool store, int sm_count, cudaStream_t stream) {
+    if (args.n_series == 0 || args.n_paths == 0) return cudaSuccess;
+    BatchSimArgs b = args;
+    const size_t smem = (size_t)args.pool_ld * sizeof(double);
+    b.pool_in_smem = smem <= 40 * 1024 ? 1 : 0;
+    unsigned long long gx = (args.n_paths + BATCH_BLOCK - 1) / BATCH_BLOCK;
+    const unsigned long long cap = (unsigned long long)sm_count * 32;      // beyond that, threads loop over paths
+    if (gx * args.n_series > cap) gx = (cap + args.n_series - 1) / args.n_series;
+    if (gx < 1) gx = 1;
+    const dim3 grid((unsigned)gx, args.n_series);
+    if (store) batch_sim_kernel<true><<<grid, BATCH_BLOCK, b.pool_in_smem ? smem : 0, stream>>>(b);
+    else       batch_sim_kernel<false><<<grid, BATCH_BLOCK, b.pool_in_smem ? smem : 0, stream>>>(b);
+    return cudaGetLastError();
+}
+
 }  // namespace mc
 #include "mc_sim32.cuh"
 namespace mc {

@@ -38,4 +38,25 @@ cudaError_t launch_reduce_partials(const BlockPartial* d_partials, int n_partial
                                    unsigned long long* d_stage_words, unsigned long long w6,
                                    unsigned long long w7, cudaStream_t stream);
 
+// ---- many price histories in one launch (mc_run_batch) ---------------------------------
+constexpr int BATCH_BLOCK = 128;
+struct BatchSimArgs {
+    unsigned long long n_paths, ld_terminal, ld_paths, pool_ld, seed;
+    uint32_t n_steps, n_series, min_history;
+    int pool_in_smem;                     // set by the launcher
+    double omega, alpha, beta;
+    const double* pool;                   // [n_series, pool_ld]
+    const mc_series_inputs* inputs;       // [n_series] (device)
+    double* paths;                        // [n_series, n_steps + 1, ld_paths] or NULL
+    double* terminal;                     // [n_series, ld_terminal]
+};
+cudaError_t launch_batch_simulation(const BatchSimArgs& args, bool store, int sm_count, cudaStream_t stream);
+
+// per history: moments about s0, exceedance count, tail (count, sum) at the percentile `tail_idx`, and the
+// percentiles themselves, written as one mc_result per history (device memory)
+cudaError_t launch_batch_stats(const double* d_terminal, unsigned long long n, unsigned long long ld,
+                               uint32_t n_series, const mc_series_inputs* d_inputs, uint32_t min_history,
+                               const double* d_pct, const double* d_lo, const double* d_hi, int n_pcts,
+                               int tail_idx, mc_result* d_results, cudaStream_t stream);
+
 }  // namespace mc

@@ -352,6 +352,50 @@ class Engine:
             info = info_t.cpu().numpy().view(np.dtype(L.SERIES_INPUTS_DTYPE)).reshape(n_series)
         return pool, info
 
+    def simulate_batch(self, pool: torch.Tensor, info: np.ndarray, n_paths: int, n_steps: int, seed: int, *,
+                       omega: float, alpha: float, beta: float, pcts, path_pcts, tail_pct, store_paths: bool,
+                       fan_chart: bool, min_history: int = 100):
+        """`mc_run_batch`: the reference's model (fp64) for every price history of `prepare_inputs` in one
+        simulation launch.  Returns a list with one RunOutput per history (None where it was skipped)."""
+        if pool.dtype != torch.float64:
+            raise ValueError("the batched run is fp64 (the reference's precision)")
+        n_series = int(pool.shape[0])
+        p = L.McBatchParams()
+        p.struct_size, p.version = C.sizeof(L.McBatchParams), L.MC_ABI_VERSION
+        p.n_paths, p.seed, p.n_steps, p.n_series = int(n_paths), int(seed) & 0xFFFFFFFFFFFFFFFF, int(n_steps), n_series
+        p.min_history = int(min_history)
+        p.flags = (L.FLAG_STORE_PATHS if store_paths else 0) | (L.FLAG_FAN_CHART if fan_chart else 0)
+        p.omega, p.alpha, p.beta = float(omega), float(alpha), float(beta)
+        p.n_pcts, p.n_path_pcts = len(pcts), len(path_pcts) if fan_chart else 0
+        for i, v in enumerate(pcts):
+            p.pcts[i] = float(v)
+        for i, v in enumerate(path_pcts if fan_chart else ()):
+            p.path_pcts[i] = float(v)
+        p.tail_pct = -1.0 if tail_pct is None else float(tail_pct)
+        with torch.cuda.device(self.device):
+            info_t = torch.from_numpy(info.view(np.int64).reshape(n_series, -1)).to(self.device)
+            terminal = torch.empty((n_series, n_paths), dtype=torch.float64, device=self.device)
+            paths = torch.empty((n_series, n_steps + 1, n_paths), dtype=torch.float64, device=self.device) if store_paths else None
+            results = (L.McResult * n_series)()
+            fan = np.zeros((n_series, n_steps + 1, len(path_pcts))) if fan_chart else None
+            self.check(self.lib.mc_run_batch(self.handle, C.byref(p), C.c_void_p(pool.data_ptr()), pool.stride(0),
+                                             C.c_void_p(info_t.data_ptr()), _CudaStageBackend._ptr(paths),
+                                             C.c_void_p(terminal.data_ptr()), C.cast(results, C.c_void_p),
+                                             C.c_void_p(fan.ctypes.data) if fan is not None else C.c_void_p(0),
+                                             self.stream_ptr()))
+        outs = []
+        for b in range(n_series):
+            if results[b].n == 0:
+                outs.append(None)
+                continue
+            spec = SimSpec(n_paths=n_paths, n_steps=n_steps, s0=float(info["s0"][b]), var0=float(info["var0"][b]),
+                           omega=omega, alpha=alpha, beta=beta, dtype="float64", seed=(int(seed) + b) & 0xFFFFFFFFFFFFFFFF,
+                           store_paths=store_paths, fan_chart=fan_chart, pcts=tuple(pcts), path_pcts=tuple(path_pcts),
+                           tail_pct=tail_pct, pool_len=int(info["pool_len"][b]))
+            outs.append(self._pack(spec, results[b], None, np.ascontiguousarray(fan[b].T) if fan is not None else None,
+                                   terminal[b], paths[b] if paths is not None else None, 0))
+        return outs
+
     def debug_shocks(self, spec: SimSpec, pool=None, path_offset=0, n_local=None) -> torch.Tensor:
         dt = self._torch_dtype(spec)
         pool_t = self.to_device(pool, dt) if pool is not None else None

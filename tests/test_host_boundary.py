@@ -41,16 +41,18 @@ def test_struct_layout_matches_c(tmp_path):
     from montecarlo_b200 import _lib
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "mc_b200.h"\n'
-                   'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(mc_params), sizeof(mc_result),'
+                   'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(mc_params), sizeof(mc_result),'
                    'sizeof(mc_portfolio), offsetof(mc_params, pcts), offsetof(mc_params, tail_pct),'
-                   'offsetof(mc_result, tail_count), sizeof(mc_series_inputs), offsetof(mc_series_inputs, pool_len));'
+                   'offsetof(mc_result, tail_count), sizeof(mc_series_inputs), offsetof(mc_series_inputs, pool_len),'
+                   'sizeof(mc_batch_params), offsetof(mc_batch_params, tail_pct));'
                    'return 0;}\n')
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
     got = [C.sizeof(_lib.McParams), C.sizeof(_lib.McResult), C.sizeof(_lib.McPortfolio),
            _lib.McParams.pcts.offset, _lib.McParams.tail_pct.offset, _lib.McResult.tail_count.offset,
-           C.sizeof(_lib.McSeriesInputs), _lib.McSeriesInputs.pool_len.offset]
+           C.sizeof(_lib.McSeriesInputs), _lib.McSeriesInputs.pool_len.offset,
+           C.sizeof(_lib.McBatchParams), _lib.McBatchParams.tail_pct.offset]
     assert [int(v) for v in out] == got
     import numpy as np
     assert np.dtype(_lib.SERIES_INPUTS_DTYPE).itemsize == C.sizeof(_lib.McSeriesInputs)

@@ -115,3 +115,40 @@ def test_from_close_rejects_bad_prices():
     close[400] = float("nan")
     with pytest.raises(ValueError):
         garch_monte_carlo_from_close(close, 100, 5, seed=1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_sims,n_days", [(1000, 20), (777, 33), (5000, 60)])
+def test_batched_run_is_bit_identical_to_one_run_per_history(fixture, n_sims, n_days):
+    """mc_run_batch: one simulation launch over (paths x histories) -- same paths, percentiles and fan chart
+    as one mc_run per history with seed + b; moments agree to rounding (different summation order)."""
+    from montecarlo_b200 import garch_monte_carlo_from_close
+    g = fixture
+    loop = garch_monte_carlo_from_close(g["close"], n_sims, n_days, lengths=g["lengths"], seed=5, batched=False)
+    batch = garch_monte_carlo_from_close(g["close"], n_sims, n_days, lengths=g["lengths"], seed=5, batched=True)
+    assert [r is None for r in batch] == [r is None for r in loop] == [False, False, False, True, True, False]
+    for a, b in zip(loop, batch):
+        if a is None:
+            continue
+        assert np.array_equal(a["paths"], b["paths"]) and np.array_equal(a["final_prices"], b["final_prices"])
+        assert a["percentiles"] == b["percentiles"]
+        for k in a["path_percentiles"]:
+            assert np.array_equal(a["path_percentiles"][k], b["path_percentiles"][k])
+        assert a["prob_profit"] == b["prob_profit"]
+        for k in ("expected_return", "expected_vol", "var_95", "cvar_95"):
+            assert abs(a[k] - b[k]) <= 1e-10 * max(1.0, abs(a[k])), k
+        exp = port.summarize(b["paths"], float(b["paths"][0, 0]))      # the reference's reductions on these paths
+        for k in ("expected_return", "expected_vol", "prob_profit", "var_95", "cvar_95"):
+            assert abs(b[k] - exp[k]) <= 1e-9 * max(1.0, abs(exp[k])), k
+
+
+@pytest.mark.gpu
+def test_batched_run_many_histories_without_paths():
+    from montecarlo_b200 import garch_monte_carlo_from_close
+    close = np.stack([ref_loader.synthetic_ohlcv(700, 300 + b, 10.0 + b)["Close"].values for b in range(64)])
+    res = garch_monte_carlo_from_close(close, 4096, 20, seed=9, return_paths=False, fan_chart=False)
+    assert len(res) == 64 and all(r is not None and r["paths"] is None for r in res)
+    one = garch_monte_carlo_from_close(close[17], 4096, 20, seed=9 + 17, return_paths=False, fan_chart=False)
+    assert one["percentiles"] == res[17]["percentiles"]
+    assert np.array_equal(one["final_prices"].cpu().numpy(), res[17]["final_prices"].cpu().numpy())
+    assert res[0]["timing"]["launches"] < 30                  # for all 64 histories together
