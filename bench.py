@@ -222,20 +222,22 @@ def run_workload(workload, steps, warmup, world, rank, group, device, sample_clo
         out = eng.simulate(spec, pool=pool_dev, group=group)
         return out
 
-    # nvidia-smi takes a while to come up (NVML init stalls CUDA calls meanwhile): start it before the
-    # warm-up and do not enter the timed region until its first sample has arrived
-    sampler = ClockSampler(device) if (rank == 0 and sample_clocks) else None
+    # nvidia-smi takes a while to come up (NVML init stalls CUDA calls meanwhile): start it and wait for its first
+    # sample BEFORE the warm-up, so that the GPU goes from the warm-up straight into the timed region
+    sampler = ClockSampler(device) if (rank == 0 and sample_clocks and not os.environ.get("MC_BENCH_NO_CLOCKS")) else None
     if sampler:
         sampler.start()
-    for _ in range(warmup):
-        one_step()
-        api_call(workload, world, group)
-    if sampler:
         sampler.wait_first(10.0)
+    last = None
+    for _ in range(warmup):
+        # `last` stays referenced across the call exactly as in the timed loop, so the caching allocator already
+        # owns both result buffers that then alternate (else the second timed step pays a cudaMalloc)
+        last = one_step()
+        api_call(workload, world, group)
     barrier()
     t0 = time.perf_counter()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
-    sim_ms, launches, last = [], 0, None
+    sim_ms, launches = [], 0
     for a, b in ev:
         flush.zero_()                     # L2 flush between timed iterations (untimed)
         torch.cuda.synchronize(eng.device)
@@ -247,6 +249,8 @@ def run_workload(workload, steps, warmup, world, rank, group, device, sample_clo
     barrier()
     t1 = time.perf_counter()
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    if os.environ.get("MC_BENCH_DEBUG") and rank == 0:
+        print("per-step ms:", [round(a.elapsed_time(b), 3) for a, b in ev], "sim:", [round(v, 3) for v in sim_ms], file=sys.stderr)
     # end to end: public API, host inputs, wall clock around the call (it synchronises)
     barrier()
     e2e_s = 0.0
