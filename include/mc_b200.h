@@ -235,11 +235,30 @@ int mc_prepare_inputs(mc_handle* h, const double* d_close, const uint32_t* d_len
  * Philox key seed + b and steps exactly like mc_run in fp64, so its paths, percentiles and fan chart are
  * bit-identical to a single mc_run with that seed.  A history with fewer than `min_history` returns (100 in the
  * reference, app.py:594-595) or a NaN flag is skipped: h_results[b].n == 0.
+ *   d_fit       [n_series] from mc_calibrate_garch: history b steps with its own omega/alpha/beta (NULL: the
+ *               common ones of mc_batch_params); a history whose fit is not valid is skipped
  *   d_paths     [n_series, n_steps + 1, n_paths] fp64 (MC_FLAG_STORE_PATHS) or NULL
  *   d_terminal  [n_series, n_paths] fp64
  *   h_results   [n_series] (host); pct/pct_lo/pct_hi as in mc_run; sim_ms/total_ms/launches describe the batch
  *   h_fan       [n_series, n_steps + 1, n_path_pcts] fp64 (host) or NULL
  */
+/*
+ * GARCH(1,1) calibration (opt-in, it changes the results): per history, the (omega, alpha, beta)
+ * that maximise the Gaussian likelihood of its returns under the reference's own recursion
+ * var' = omega + alpha r^2 + beta var (app.py:632-633), in place of the constants of app.py:601-603.  Variance
+ * targeting (omega = mean(r^2) (1 - alpha - beta)), deterministic grid refinement over (alpha, alpha + beta):
+ * 16 x 16 candidates per level, `levels` levels (8 resolves both to ~1e-5).  Reads the pools and
+ * mc_series_inputs that mc_prepare_inputs wrote (fp64 pool), writes d_fit[n_series] on the device; asynchronous.
+ * `objective` = sum_t [log h_t + z_t^2 / h_t] on the standardised returns (-2 log-likelihood up to constants).
+ */
+typedef struct mc_garch_fit {
+    double omega, alpha, beta;   /* in the units of the raw log returns: pass as mc_params.omega/alpha/beta */
+    double objective;
+    uint64_t valid;              /* 0: history skipped (too short / NaN) */
+} mc_garch_fit;
+int mc_calibrate_garch(mc_handle* h, const double* d_pool, uint64_t pool_ld, const mc_series_inputs* d_inputs,
+                       uint32_t n_series, uint32_t min_history, uint32_t levels, mc_garch_fit* d_fit, void* stream);
+
 typedef struct mc_batch_params {
     uint32_t struct_size;        /* sizeof(mc_batch_params) */
     uint32_t version;            /* MC_ABI_VERSION */
@@ -256,8 +275,8 @@ typedef struct mc_batch_params {
     double tail_pct;             /* < 0: none */
 } mc_batch_params;
 int mc_run_batch(mc_handle* h, const mc_batch_params* p, const void* d_pool, uint64_t pool_ld,
-                 const mc_series_inputs* d_inputs, void* d_paths, void* d_terminal, mc_result* h_results,
-                 double* h_fan, void* stream);
+                 const mc_series_inputs* d_inputs, const mc_garch_fit* d_fit /* per-history omega/alpha/beta, or NULL */,
+                 void* d_paths, void* d_terminal, mc_result* h_results, double* h_fan, void* stream);
 
 #ifdef __cplusplus
 }

@@ -23,7 +23,7 @@ EXPORTS = (
     "mc_stage_begin", "mc_stage_words", "mc_stage_max_words", "mc_stage_next", "mc_fetch_result",
     "mc_stage_reads_paths", "mc_stage_resimulate",
     "mc_debug_shocks", "mc_debug_philox", "mc_percentiles", "mc_histogram", "mc_prepare_inputs",
-    "mc_run_batch",
+    "mc_run_batch", "mc_calibrate_garch",
 )
 
 
@@ -88,6 +88,13 @@ class McBatchParams(C.Structure):
     ]
 
 
+class McGarchFit(C.Structure):
+    """mc_garch_fit (include/mc_b200.h)."""
+    _fields_ = [("omega", C.c_double), ("alpha", C.c_double), ("beta", C.c_double), ("objective", C.c_double),
+                ("valid", C.c_uint64)]
+
+
+GARCH_FIT_DTYPE = [("omega", "<f8"), ("alpha", "<f8"), ("beta", "<f8"), ("objective", "<f8"), ("valid", "<u8")]
 INPUT_NAN = 1
 SERIES_INPUTS_DTYPE = [("s0", "<f8"), ("var0", "<f8"), ("pool_std", "<f8"), ("pool_len", "<u8"), ("flags", "<u8")]
 
@@ -133,7 +140,9 @@ def _declare(lib):
     lib.mc_prepare_inputs.restype = C.c_int
     lib.mc_prepare_inputs.argtypes = [vp, vp, vp, u32, u32, u64, u32, i32, vp, u64, vp, vp]
     lib.mc_run_batch.restype = C.c_int
-    lib.mc_run_batch.argtypes = [vp, C.POINTER(McBatchParams), vp, u64, vp, vp, vp, vp, vp, vp]
+    lib.mc_run_batch.argtypes = [vp, C.POINTER(McBatchParams), vp, u64, vp, vp, vp, vp, vp, vp, vp]
+    lib.mc_calibrate_garch.restype = C.c_int
+    lib.mc_calibrate_garch.argtypes = [vp, vp, u64, vp, u32, u32, u32, vp, vp]
 
 
 def load_library(path: str | None = None):

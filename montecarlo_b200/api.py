@@ -165,7 +165,7 @@ def garch_monte_carlo_from_close(close, n_sims: int, n_days: int, progress_callb
                                  dtype: str = "float64", return_paths="auto", omega: float = REF_OMEGA,
                                  alpha: float = REF_ALPHA, beta: float = REF_BETA, hist_bins: int = 0,
                                  hist_range=None, device: Optional[int] = None, fan_chart: Optional[bool] = None,
-                                 batched: Optional[bool] = None):
+                                 batched: Optional[bool] = None, calibrate: bool = False, calibrate_levels: int = 8):
     """The routine straight from close prices, without pandas: the device derives `log_ret`,
     `rvol_20`, `std_returns`, `current_var` and `current_price` (app.py:224, 233, 392-393, 592, 606, 609, 1213)
     for every price history in one launch, then runs the model of app.py:612-657 per history.
@@ -174,7 +174,9 @@ def garch_monte_carlo_from_close(close, n_sims: int, n_days: int, progress_callb
     valid in row b).  An entry is None where the reference returns None (fewer than 100 returns left,
     app.py:594-595).  Seeds: history b uses `seed + b`.  `batched` (default: 2-D fp64 input): all histories go
     through ONE simulation launch and one selection per result kind (`mc_run_batch`) instead of one run per
-    history; the results are bit-identical either way.  Raises ValueError for NaN / non-positive prices (the
+    history; the results are bit-identical either way.  `calibrate=True` (opt-in: it changes the
+    results) replaces the reference's hard-coded omega/alpha/beta (app.py:601-603) by each history's own
+    quasi-maximum-likelihood values (`mc_calibrate_garch`); every result then carries a 'garch' key.  Raises ValueError for NaN / non-positive prices (the
     reference would silently drop such rows)."""
     from . import _lib as L
     from .engine import get_engine
@@ -190,13 +192,20 @@ def garch_monte_carlo_from_close(close, n_sims: int, n_days: int, progress_callb
         for ok in live:
             if ok:
                 progress_callback("Running Monte Carlo simulation...")
+    fit = None
+    if calibrate:
+        if dtype != "float64":
+            pool64, _ = eng.prepare_inputs(close, lengths, first_row, "float64")
+        else:
+            pool64 = pool
+        fit = eng.calibrate_garch(pool64, info, calibrate_levels, MIN_HISTORY)
     if batched is None:       # the batched run is fp64, no histogram, fan chart from stored paths
         keeps_paths = _decide_paths(n_sims, n_days, dtype, return_paths)[0]
         batched = not single and dtype == "float64" and hist_bins == 0 and (keeps_paths or fan_chart is False)
     if batched:
         if dtype != "float64" or hist_bins:
             raise ValueError("the batched run is fp64 without histogram")
-        res = _run_batches(eng, pool, info, n_sims, n_days, base, omega, alpha, beta, return_paths, fan_chart)
+        res = _run_batches(eng, pool, info, n_sims, n_days, base, omega, alpha, beta, return_paths, fan_chart, fit)
         return res[0] if single else res
     results = []
     for b in range(len(info)):
@@ -204,18 +213,40 @@ def garch_monte_carlo_from_close(close, n_sims: int, n_days: int, progress_callb
             results.append(None)
             continue
         n = int(info["pool_len"][b])
+        o, a, be = (omega, alpha, beta) if fit is None else (float(fit[1][k][b]) for k in ("omega", "alpha", "beta"))
         results.append(_reference_model(pool[b, :n], float(info["var0"][b]), float(info["s0"][b]), n_sims, n_days,
                                         seed=(base + b) & 0xFFFFFFFFFFFFFFFF, dtype=dtype, return_paths=return_paths,
-                                        omega=omega, alpha=alpha, beta=beta, shock="bootstrap", injected_shocks=None,
+                                        omega=o, alpha=a, beta=be, shock="bootstrap", injected_shocks=None,
                                         hist_bins=hist_bins, hist_range=hist_range, device=device, group=None,
                                         fan_chart=fan_chart))
+        if fit is not None:
+            results[-1]["garch"] = _garch_entry(fit[1], b)
     return results[0] if single else results
 
 
 BATCH_PATHS_BYTES = 8 << 30       # histories are simulated together while their stored paths fit this
 
 
-def _run_batches(eng, pool, info, n_sims, n_days, base, omega, alpha, beta, return_paths, fan_chart):
+def _garch_entry(fit, b):
+    return {"omega": float(fit["omega"][b]), "alpha": float(fit["alpha"][b]), "beta": float(fit["beta"][b]),
+            "objective": float(fit["objective"][b])}
+
+
+def calibrate_garch(close, *, lengths=None, first_row: int = SMA_WARMUP_ROWS, levels: int = 8,
+                    device: Optional[int] = None):
+    """GARCH(1,1) parameters of each price history by Gaussian quasi-maximum likelihood under the reference's
+    recursion (app.py:632-633), in place of its constants (app.py:601-603).  SURVEY 8f N4.  -> list of
+    dict(omega, alpha, beta, objective) / None (fewer than 100 returns); one dict for a 1-D `close`."""
+    from .engine import get_engine
+    single = getattr(close, "ndim", None) == 1 or (hasattr(close, "dim") and close.dim() == 1)
+    eng = get_engine(device)
+    pool, info = eng.prepare_inputs(close, lengths, first_row, "float64")
+    _, fit = eng.calibrate_garch(pool, info, levels, MIN_HISTORY)
+    out = [_garch_entry(fit, b) if fit["valid"][b] else None for b in range(len(fit))]
+    return out[0] if single else out
+
+
+def _run_batches(eng, pool, info, n_sims, n_days, base, omega, alpha, beta, return_paths, fan_chart, fit=None):
     store, how = _decide_paths(n_sims, n_days, "float64", return_paths)
     want_fan = store if fan_chart is None else bool(fan_chart)
     if want_fan and not store:
@@ -227,8 +258,12 @@ def _run_batches(eng, pool, info, n_sims, n_days, base, omega, alpha, beta, retu
         sl = slice(b0, min(len(info), b0 + step))
         outs = eng.simulate_batch(pool[sl], info[sl], n_sims, n_days, (base + b0) & 0xFFFFFFFFFFFFFFFF,
                                   omega=omega, alpha=alpha, beta=beta, pcts=REF_TERMINAL_PCTS,
-                                  path_pcts=REF_PATH_PCTS, tail_pct=REF_TAIL_PCT, store_paths=store, fan_chart=want_fan)
-        results += [None if o is None else _result_dict(o, o.spec.s0, how) for o in outs]
+                                  path_pcts=REF_PATH_PCTS, tail_pct=REF_TAIL_PCT, store_paths=store, fan_chart=want_fan,
+                                  fit=None if fit is None else (fit[0][sl], fit[1][sl]))
+        for i, o in enumerate(outs):
+            results.append(None if o is None else _result_dict(o, o.spec.s0, how))
+            if o is not None and fit is not None:
+                results[-1]["garch"] = _garch_entry(fit[1], b0 + i)
     return results
 
 

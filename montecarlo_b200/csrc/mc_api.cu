@@ -698,9 +698,21 @@ int mc_prepare_inputs(mc_handle* h, const double* d_close, const uint32_t* d_len
     return MC_OK;
 }
 
+int mc_calibrate_garch(mc_handle* h, const double* d_pool, uint64_t pool_ld, const mc_series_inputs* d_inputs,
+                       uint32_t n_series, uint32_t min_history, uint32_t levels, mc_garch_fit* d_fit, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (n_series && (!d_pool || !d_inputs || !d_fit)) return fail(h, MC_ERR_INVALID, "mc_calibrate_garch: NULL buffer");
+    if (levels < 1 || levels > 16) return fail(h, MC_ERR_INVALID, "mc_calibrate_garch: levels must be 1..16");
+    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_CUDA(h, launch_calibrate_garch(d_pool, pool_ld, d_inputs, n_series, min_history, levels, d_fit,
+                                      static_cast<cudaStream_t>(stream)));
+    return MC_OK;
+}
+
 int mc_run_batch(mc_handle* h, const mc_batch_params* p, const void* d_pool, uint64_t pool_ld,
-                 const mc_series_inputs* d_inputs, void* d_paths, void* d_terminal, mc_result* h_results,
-                 double* h_fan, void* stream) {
+                 const mc_series_inputs* d_inputs, const mc_garch_fit* d_fit, void* d_paths, void* d_terminal,
+                 mc_result* h_results, double* h_fan, void* stream) {
     if (!h) return MC_ERR_INVALID;
     std::lock_guard<std::mutex> lock(h->mu);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -732,7 +744,7 @@ int mc_run_batch(mc_handle* h, const mc_batch_params* p, const void* d_pool, uin
     a.n_paths = p->n_paths; a.ld_terminal = p->n_paths; a.ld_paths = p->n_paths; a.pool_ld = pool_ld; a.seed = p->seed;
     a.n_steps = p->n_steps; a.n_series = p->n_series; a.min_history = p->min_history;
     a.omega = p->omega; a.alpha = p->alpha; a.beta = p->beta;
-    a.pool = static_cast<const double*>(d_pool); a.inputs = d_inputs;
+    a.pool = static_cast<const double*>(d_pool); a.inputs = d_inputs; a.fit = d_fit;
     a.paths = static_cast<double*>(d_paths); a.terminal = static_cast<double*>(d_terminal);
     MC_CUDA(h, launch_batch_simulation(a, store, h->dev.sm_count, s));
     ++launches;
@@ -747,7 +759,7 @@ int mc_run_batch(mc_handle* h, const mc_batch_params* p, const void* d_pool, uin
                               d_hi, &launches, s)))
             return rc;
     }
-    MC_CUDA(h, launch_batch_stats(a.terminal, p->n_paths, p->n_paths, p->n_series, d_inputs, p->min_history, d_pct, d_lo,
+    MC_CUDA(h, launch_batch_stats(a.terminal, p->n_paths, p->n_paths, p->n_series, d_inputs, d_fit, p->min_history, d_pct, d_lo,
                                   d_hi, (int)p->n_pcts, tail_idx, h->batch_res.p, s));
     ++launches;
     MC_CUDA(h, cudaMemcpyAsync(h_results, h->batch_res.p, B * sizeof(mc_result), cudaMemcpyDeviceToHost, s));

@@ -37,14 +37,15 @@ __device__ __forceinline__ RowAcc shuffle_down(const RowAcc& a, int d) {
 
 __global__ void __launch_bounds__(STATS_THREADS)
 batch_stats_kernel(const double* __restrict__ terminal, unsigned long long n, unsigned long long ld,
-                   const mc_series_inputs* __restrict__ inputs, uint32_t min_history, const double* __restrict__ pct,
+                   const mc_series_inputs* __restrict__ inputs, const mc_garch_fit* __restrict__ fit, uint32_t min_history,
+                   const double* __restrict__ pct,
                    const double* __restrict__ lo, const double* __restrict__ hi, int n_pcts, int tail_idx,
                    mc_result* __restrict__ results) {
     __shared__ RowAcc s_warp[STATS_THREADS / 32];
     const uint32_t b = blockIdx.x;
     mc_result* res = results + b;
     const mc_series_inputs in = inputs[b];
-    if (in.pool_len < min_history || in.flags != 0) {                  // skipped history: n = 0 marks it
+    if (in.pool_len < min_history || in.flags != 0 || (fit && fit[b].valid == 0)) {   // skipped history: n = 0 marks it
         if (threadIdx.x == 0) {
             res->n = 0; res->n_above = 0; res->mean = 0.0; res->std = 0.0; res->min = 0.0; res->max = 0.0;
             res->tail_count = 0; res->tail_sum = 0.0;
@@ -94,11 +95,11 @@ batch_stats_kernel(const double* __restrict__ terminal, unsigned long long n, un
 }
 
 cudaError_t launch_batch_stats(const double* d_terminal, unsigned long long n, unsigned long long ld,
-                               uint32_t n_series, const mc_series_inputs* d_inputs, uint32_t min_history,
-                               const double* d_pct, const double* d_lo, const double* d_hi, int n_pcts,
+                               uint32_t n_series, const mc_series_inputs* d_inputs, const mc_garch_fit* d_fit,
+                               uint32_t min_history, const double* d_pct, const double* d_lo, const double* d_hi, int n_pcts,
                                int tail_idx, mc_result* d_results, cudaStream_t stream) {
     if (n_series == 0) return cudaSuccess;
-    batch_stats_kernel<<<n_series, STATS_THREADS, 0, stream>>>(d_terminal, n, ld, d_inputs, min_history, d_pct, d_lo,
+    batch_stats_kernel<<<n_series, STATS_THREADS, 0, stream>>>(d_terminal, n, ld, d_inputs, d_fit, min_history, d_pct, d_lo,
                                                                d_hi, n_pcts, tail_idx, d_results);
     return cudaGetLastError();
 }

@@ -238,7 +238,13 @@ __global__ void __launch_bounds__(BATCH_BLOCK) batch_sim_kernel(const BatchSimAr
     double* s_pool = reinterpret_cast<double*>(smem_dyn);
     const uint32_t series = blockIdx.y;
     const mc_series_inputs in = b.inputs[series];
-    const bool live = in.pool_len >= b.min_history && in.flags == 0;
+    bool live = in.pool_len >= b.min_history && in.flags == 0;
+    double omega = b.omega, alpha = b.alpha, beta = b.beta;
+    if (b.fit) {                        // calibrated per history (mc_calibrate_garch)
+        const mc_garch_fit f = b.fit[series];
+        live = live && f.valid != 0;
+        omega = f.omega; alpha = f.alpha; beta = f.beta;
+    }
     double* terminal = b.terminal + (size_t)series * b.ld_terminal;
     double* paths = STORE ? b.paths + (size_t)series * (b.n_steps + 1ull) * b.ld_paths : nullptr;
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
@@ -257,7 +263,7 @@ __global__ void __launch_bounds__(BATCH_BLOCK) batch_sim_kernel(const BatchSimAr
     a.pool_len = (uint32_t)in.pool_len;
     a.pool_log2_copies = b.pool_in_smem ? 0 : -1;
     a.n_steps = b.n_steps;
-    a.omega = b.omega; a.alpha = b.alpha; a.beta = b.beta;
+    a.omega = omega; a.alpha = alpha; a.beta = beta;
     if (b.pool_in_smem) {
         for (uint32_t i = threadIdx.x; i < a.pool_len; i += blockDim.x) s_pool[i] = a.pool[i];
         __syncthreads();

@@ -47,6 +47,7 @@ struct BatchSimArgs {
     double omega, alpha, beta;
     const double* pool;                   // [n_series, pool_ld]
     const mc_series_inputs* inputs;       // [n_series] (device)
+    const mc_garch_fit* fit;              // [n_series] per-history omega/alpha/beta (device) or NULL
     double* paths;                        // [n_series, n_steps + 1, ld_paths] or NULL
     double* terminal;                     // [n_series, ld_terminal]
 };
@@ -55,8 +56,8 @@ cudaError_t launch_batch_simulation(const BatchSimArgs& args, bool store, int sm
 // per history: moments about s0, exceedance count, tail (count, sum) at the percentile `tail_idx`, and the
 // percentiles themselves, written as one mc_result per history (device memory)
 cudaError_t launch_batch_stats(const double* d_terminal, unsigned long long n, unsigned long long ld,
-                               uint32_t n_series, const mc_series_inputs* d_inputs, uint32_t min_history,
-                               const double* d_pct, const double* d_lo, const double* d_hi, int n_pcts,
+                               uint32_t n_series, const mc_series_inputs* d_inputs, const mc_garch_fit* d_fit,
+                               uint32_t min_history, const double* d_pct, const double* d_lo, const double* d_hi, int n_pcts,
                                int tail_idx, mc_result* d_results, cudaStream_t stream);
 
 }  // namespace mc

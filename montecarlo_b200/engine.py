@@ -352,9 +352,25 @@ class Engine:
             info = info_t.cpu().numpy().view(np.dtype(L.SERIES_INPUTS_DTYPE)).reshape(n_series)
         return pool, info
 
+    def calibrate_garch(self, pool: torch.Tensor, info: np.ndarray, levels: int = 8, min_history: int = 100):
+        """`mc_calibrate_garch`: per-history (omega, alpha, beta) by Gaussian quasi-maximum
+        likelihood under the reference's recursion (app.py:632-633).  Returns (fit_device [n_series, 5] int64
+        view of mc_garch_fit, fit_host structured array)."""
+        if pool.dtype != torch.float64:
+            raise ValueError("calibration reads the fp64 pool")
+        n_series = int(pool.shape[0])
+        with torch.cuda.device(self.device):
+            info_t = torch.from_numpy(info.view(np.int64).reshape(n_series, -1)).to(self.device)
+            fit_t = torch.empty((n_series, C.sizeof(L.McGarchFit) // 8), dtype=torch.int64, device=self.device)
+            self.check(self.lib.mc_calibrate_garch(self.handle, C.c_void_p(pool.data_ptr()), pool.stride(0),
+                                                   C.c_void_p(info_t.data_ptr()), n_series, int(min_history), int(levels),
+                                                   C.c_void_p(fit_t.data_ptr()), self.stream_ptr()))
+            fit = fit_t.cpu().numpy().view(np.dtype(L.GARCH_FIT_DTYPE)).reshape(n_series)
+        return fit_t, fit
+
     def simulate_batch(self, pool: torch.Tensor, info: np.ndarray, n_paths: int, n_steps: int, seed: int, *,
                        omega: float, alpha: float, beta: float, pcts, path_pcts, tail_pct, store_paths: bool,
-                       fan_chart: bool, min_history: int = 100):
+                       fan_chart: bool, min_history: int = 100, fit=None):
         """`mc_run_batch`: the reference's model (fp64) for every price history of `prepare_inputs` in one
         simulation launch.  Returns a list with one RunOutput per history (None where it was skipped)."""
         if pool.dtype != torch.float64:
@@ -379,7 +395,9 @@ class Engine:
             results = (L.McResult * n_series)()
             fan = np.zeros((n_series, n_steps + 1, len(path_pcts))) if fan_chart else None
             self.check(self.lib.mc_run_batch(self.handle, C.byref(p), C.c_void_p(pool.data_ptr()), pool.stride(0),
-                                             C.c_void_p(info_t.data_ptr()), _CudaStageBackend._ptr(paths),
+                                             C.c_void_p(info_t.data_ptr()),
+                                             C.c_void_p(fit[0].data_ptr()) if fit is not None else C.c_void_p(0),
+                                             _CudaStageBackend._ptr(paths),
                                              C.c_void_p(terminal.data_ptr()), C.cast(results, C.c_void_p),
                                              C.c_void_p(fan.ctypes.data) if fan is not None else C.c_void_p(0),
                                              self.stream_ptr()))
@@ -388,6 +406,8 @@ class Engine:
             if results[b].n == 0:
                 outs.append(None)
                 continue
+            if fit is not None:
+                omega, alpha, beta = (float(fit[1][k][b]) for k in ("omega", "alpha", "beta"))
             spec = SimSpec(n_paths=n_paths, n_steps=n_steps, s0=float(info["s0"][b]), var0=float(info["var0"][b]),
                            omega=omega, alpha=alpha, beta=beta, dtype="float64", seed=(int(seed) + b) & 0xFFFFFFFFFFFFFFFF,
                            store_paths=store_paths, fan_chart=fan_chart, pcts=tuple(pcts), path_pcts=tuple(path_pcts),
