@@ -57,6 +57,12 @@ struct PinnedBuf {
     }
     void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
 };
+struct SideBuf {
+    DevBuf<float> values;
+    DevBuf<unsigned int> counts;
+    DevBuf<uint32_t> brackets;
+    void release() { values.release(); counts.release(); brackets.release(); }
+};
 }  // namespace
 
 struct mc_handle {
@@ -82,6 +88,7 @@ struct mc_handle {
     DevBuf<double> edges;
     DevBuf<unsigned long long> hist_total;
     DevBuf<unsigned long long> stage;   // internal stage buffer (mc_run, mc_percentiles)
+    SideBuf side_t, side_f;             // side lists of the fp32 selection passes (terminal / fan-chart rows)
     DevBuf<double> batch_pct;           // mc_run_batch: [3][n_series][n_pcts]
     DevBuf<mc_result> batch_res;        // mc_run_batch: [n_series]
     PinnedBuf<unsigned char> h_stage;   // pinned staging for the D2H of results
@@ -147,6 +154,25 @@ size_t final_stage_words(const mc_params& p) { return 2 + (size_t)p.hist_bins; }
 
 unsigned int ranks_of(const mc_params& p) { return p.n_ranks ? p.n_ranks : 1u; }
 
+// Side lists for an fp32 problem (mc_select.cuh: SideLists); a failed allocation just leaves them off.
+void attach_side(mc_handle* h, SelectProblem& sp, SideBuf& buf) {
+    sp.side = SideLists{};
+    if (sp.dtype != MC_F32 || sp.n == 0 || sp.rows == 0 || getenv("MC_NO_SIDE_LISTS")) return;
+    const unsigned long long chunks = select_chunks_f32(sp, h->dev.sm_count);
+    unsigned int cap = side_list_cap(sp.n, chunks);
+    if (const char* e = getenv("MC_SIDE_CAP")) cap = (unsigned int)strtoul(e, nullptr, 10);     // tests: force overflows
+    if (cap == 0) return;
+    if (buf.values.reserve(side_list_floats(sp.rows, chunks, cap)) != cudaSuccess ||
+        buf.counts.reserve((size_t)sp.rows * chunks * SIDE_WARPS) != cudaSuccess ||
+        buf.brackets.reserve((size_t)sp.rows * SIDE_BRACKET_WORDS) != cudaSuccess) {
+        cudaGetLastError();
+        buf.release();
+        return;
+    }
+    sp.side.values = buf.values.p; sp.side.counts = buf.counts.p; sp.side.brackets = buf.brackets.p;
+    sp.side.cap = cap; sp.side.chunks = (unsigned int)chunks;
+}
+
 void setup_sampling(SelectProblem& sp, unsigned int n_ranks, bool contiguous) {
     sp.m_slot = sample_slot(sp.dtype, n_ranks);
     sp.m_local = sp.n < sp.m_slot ? (unsigned int)sp.n : sp.m_slot;
@@ -207,6 +233,7 @@ int select_rows(mc_handle* h, const void* d_x, int dtype, uint64_t rows, uint64_
         return fail(h, MC_ERR_INVALID, "percentiles must be ascending and within [0, 100]");
     sp.x = d_x; sp.dtype = dtype; sp.rows = rows; sp.n = n; sp.ld = ld;
     setup_sampling(sp, 1, iid_columns);                // arbitrary data: strided sample
+    attach_side(h, sp, h->side_f);
     MC_CUDA(h, h->states_f.reserve(rows));
     MC_CUDA(h, h->scratch_f.reserve(rows));
     sp.d_states = h->states_f.p;
@@ -289,7 +316,7 @@ int mc_destroy(mc_handle* h) {
     cudaSetDevice(h->device);
     h->partials.release(); h->lut.release(); h->res.release(); h->plans.release(); h->states_t.release(); h->states_f.release(); h->scratch_t.release(); h->scratch_f.release();
     h->pct_t.release(); h->fan.release(); h->tail_scratch.release(); h->edges.release(); h->hist_total.release();
-    h->batch_pct.release(); h->batch_res.release();
+    h->batch_pct.release(); h->batch_res.release(); h->side_t.release(); h->side_f.release();
     h->stage.release(); h->h_stage.release(); h->pending.release(); h->h_pending.release();
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->ev_pending) cudaEventDestroy(h->ev_pending);
@@ -336,6 +363,7 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
         h->prob_t.x = d_terminal; h->prob_t.dtype = p->dtype; h->prob_t.rows = 1; h->prob_t.n = p->n_paths;
         h->prob_t.ld = p->n_paths; h->prob_t.d_states = h->states_t.p; h->prob_t.d_scratch = h->scratch_t.p;
         setup_sampling(h->prob_t, R, true);            // paths are iid: the first values are a random sample
+        attach_side(h, h->prob_t, h->side_t);
         if ((rc = upload_plan(h, h->prob_t, 0, s))) return rc;
         if (p->tail_pct >= 0.0) {
             for (unsigned k = 0; k < p->n_pcts; ++k) if (p->pcts[k] == p->tail_pct) h->tail_idx = (int)k;
@@ -354,6 +382,7 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
         h->prob_f.ld = p->paths_ld ? p->paths_ld : p->n_paths; h->prob_f.d_states = h->states_f.p;
         h->prob_f.d_scratch = h->scratch_f.p;
         setup_sampling(h->prob_f, R, true);
+        attach_side(h, h->prob_f, h->side_f);
         if ((rc = upload_plan(h, h->prob_f, 1, s))) return rc;
     }
     if (p->hist_bins) {

@@ -448,7 +448,7 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass1_f32_kernel(const fl
                                                                         unsigned long long n, int vec,
                                                                         const RowSel* __restrict__ states,
                                                                         unsigned int* __restrict__ out, size_t row_slot,
-                                                                        size_t iv_slot, int n_iv_cap) {
+                                                                        size_t iv_slot, int n_iv_cap, SideLists side) {
     extern __shared__ unsigned int s_bins[];
     __shared__ uint32_t s_lo[MAX_IV];
     __shared__ int s_shift[MAX_IV];
@@ -464,6 +464,15 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass1_f32_kernel(const fl
     const int tid = threadIdx.x;
     if (tid < n_iv) { s_lo[tid] = (uint32_t)st.lo[tid]; s_shift[tid] = st.shift[tid]; }
     for (int i = tid; i < n_iv * SEL_BINS; i += FAST_THREADS) s_bins[i] = 0u;
+    // side list of this warp: the parked values, in the order they are drained
+    const size_t side_slot = (row * gridDim.x + blockIdx.x) * SIDE_WARPS + (tid >> 5);
+    float* side_w = side.values ? side.values + side_slot * side.cap : nullptr;
+    unsigned int side_n = 0;                 // warp-uniform
+    if (side.values && blockIdx.x == 0) {    // remember the brackets the lists cover
+        uint32_t* br = side.brackets + row * SIDE_BRACKET_WORDS;
+        if (tid == 0) br[0] = (uint32_t)n_iv;
+        if (tid < n_iv) { br[1 + tid] = (uint32_t)st.lo[tid]; br[1 + MAX_IV + tid] = (uint32_t)st.hi[tid]; }
+    }
     __syncthreads();
 
     unsigned int* out_row = out + row * row_slot;
@@ -494,8 +503,11 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass1_f32_kernel(const fl
                          : "+r"(q_top) : "f"(v), "f"(top), "n"(4 * FAST_THREADS) : "memory");
         },
         [&]() {
-            while (__any_sync(0xffffffffu, q_top != q_base)) {
-                if (q_top != q_base) {
+            for (;;) {
+                const bool has = q_top != q_base;
+                const unsigned int who = __ballot_sync(0xffffffffu, has);
+                if (!who) break;
+                if (has) {
                     q_top -= 4u * FAST_THREADS;
                     float v;
                     asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(q_top) : "memory");
@@ -504,9 +516,15 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass1_f32_kernel(const fl
                     for (int k = 0; k < NB; ++k) g += v >= lo_f[k] ? 1 : 0;
                     if (g >= 0)   // always: the value was parked because it lies in bracket g
                         atomicAdd(&s_bins[g * SEL_BINS + ((key_of(v) - s_lo[g]) >> s_shift[g])], 1u);
+                    if (side_w) {
+                        const unsigned int pos = side_n + __popc(who & ((1u << (tid & 31)) - 1u));
+                        if (pos < side.cap) side_w[pos] = v;
+                    }
                 }
+                side_n += __popc(who);
             }
         });
+    if (side_w && (tid & 31) == 0) side.counts[side_slot] = side_n;       // > cap: overflowed, not usable
 
     unsigned long long* out_ge = reinterpret_cast<unsigned long long*>(out_row);
 #pragma unroll
@@ -525,11 +543,12 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass2_f32_kernel(const fl
                                                                         unsigned long long n, int vec,
                                                                         const RowSel* __restrict__ states,
                                                                         unsigned int* __restrict__ out, size_t row_slot,
-                                                                        size_t iv_slot, int n_iv_cap) {
+                                                                        size_t iv_slot, int n_iv_cap, SideLists side) {
     extern __shared__ unsigned int s_bins[];
     __shared__ uint32_t s_lo[MAX_IV], s_hi[MAX_IV];
     __shared__ int s_shift[MAX_IV], s_mode[MAX_IV];
     __shared__ unsigned char s_map[MAP_BYTES];
+    __shared__ int s_use_side;
     const unsigned long long row = blockIdx.y;
     const RowSel& st = states[row];
     const int n_iv = st.n_iv;
@@ -549,15 +568,47 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass2_f32_kernel(const fl
         for (uint32_t b = (s_lo[tid] >> cs) - base; b <= (s_hi[tid] >> cs) - base; ++b) s_map[b] = 1;   // b <= 2048
     __syncthreads();
 
+    // the side lists of pass 1 hold every value of this chunk that lies in a pass-1 bracket: enough when each
+    // interval of the row is inside one of those brackets and none of this block's eight lists overflowed
+    const size_t side_slot = (row * gridDim.x + blockIdx.x) * SIDE_WARPS;
+    if (tid == 0) {
+        int ok = side.values != nullptr && side.chunks == gridDim.x;
+        if (ok) {
+            const uint32_t* br = side.brackets + row * SIDE_BRACKET_WORDS;
+            const int nb = (int)br[0];
+            for (int i = 0; i < n_iv && ok; ++i) {
+                int inside = 0;
+                for (int b = 0; b < nb; ++b) inside |= (br[1 + b] <= s_lo[i] && s_hi[i] <= br[1 + MAX_IV + b]) ? 1 : 0;
+                ok = inside;
+            }
+            for (int w = 0; w < SIDE_WARPS && ok; ++w) ok = side.counts[side_slot + w] <= side.cap;
+        }
+        s_use_side = ok;
+    }
+    __syncthreads();
+
     unsigned int* out_row = out + row * row_slot;
     FastRow c{s_lo, s_hi, s_shift, s_mode, s_bins, out_row + 2 * (size_t)n_iv_cap, iv_slot, n_iv};
-    unsigned long long beg, end;
-    fast_block_range(n, &beg, &end);
-    fast_stream(x + row * ld, beg, end, vec != 0, [&](float v) {
+    auto visit = [&](float v) {
         const uint32_t key = key_of(v);
         const uint32_t idx = min((key >> cs) - base, (uint32_t)(MAP_BYTES - 1));     // keys below k0 wrap: clamped too
         if (s_map[idx]) fast_member(c, key);
-    }, [] {});
+    };
+    if (s_use_side) {
+        const int warp = tid >> 5, lane = tid & 31;
+        const float* list = side.values + (side_slot + warp) * side.cap;
+        const unsigned int cnt = side.counts[side_slot + warp];
+        unsigned int i = lane;
+        for (; i + 96 < cnt; i += 128) {         // four loads in flight per lane
+            const float a0 = __ldcs(list + i), a1 = __ldcs(list + i + 32), a2 = __ldcs(list + i + 64), a3 = __ldcs(list + i + 96);
+            visit(a0); visit(a1); visit(a2); visit(a3);
+        }
+        for (; i < cnt; i += 32) visit(__ldcs(list + i));
+    } else {
+        unsigned long long beg, end;
+        fast_block_range(n, &beg, &end);
+        fast_stream(x + row * ld, beg, end, vec != 0, visit, [] {});
+    }
     __syncthreads();
     for (int i = tid; i < n_iv * SEL_BINS; i += FAST_THREADS) {
         const unsigned int v = s_bins[i];
@@ -574,18 +625,35 @@ static cudaError_t launch_fast(K k, const SelectProblem& sp, void* d_out, int n_
     }
     const float* x = static_cast<const float*>(sp.x);
     const int vec = (sp.ld % 4 == 0 && ((uintptr_t)x & 15u) == 0) ? 1 : 0;
+    SideLists side = sp.side;
+    if (side.values && side.chunks != grid.x) side.values = nullptr;         // laid out for another grid: off
     k<<<grid, FAST_THREADS, smem, stream>>>(x, sp.ld, sp.n, vec, sp.d_states, static_cast<unsigned int*>(d_out),
                                             row_slot_u32(sp.dtype, sp.plan.n_targets), iv_slot_u32(sp.dtype),
-                                            sp.plan.n_targets);
+                                            sp.plan.n_targets, side);
     return cudaGetLastError();
 }
 
-static cudaError_t launch_pass_f32(const SelectProblem& sp, bool first, void* d_out, int sm_count, cudaStream_t s) {
+unsigned long long select_chunks_f32(const SelectProblem& sp, int sm_count) {
     // one row: two blocks per SM stream it; many rows: ~8 resident blocks per SM in total, whole chunks of 4 KB
     unsigned long long chunks = sp.rows == 1 ? 2ull * sm_count : ((unsigned long long)sm_count * 8 + sp.rows - 1) / sp.rows;
     const unsigned long long max_chunks = (sp.n + 4095ull) / 4096ull;
     if (chunks > max_chunks) chunks = max_chunks;
     if (chunks < 1) chunks = 1;
+    return chunks;
+}
+
+unsigned int side_list_cap(unsigned long long n, unsigned long long chunks) {
+    // a quarter of the chunk, split over the block's warps (the brackets of 5..9 percentiles hold 9..13 % of a
+    // row when the pilot sample has 32768 values); at least one 128-byte line per list
+    unsigned long long per = (n + chunks - 1) / chunks;
+    per = (per + 1023ull) & ~1023ull;                       // fast_block_range's chunk length
+    unsigned long long cap = per / (4ull * SIDE_WARPS);
+    cap = (cap + 31ull) & ~31ull;
+    return (unsigned int)(cap < 32 ? 32 : cap);
+}
+
+static cudaError_t launch_pass_f32(const SelectProblem& sp, bool first, void* d_out, int sm_count, cudaStream_t s) {
+    const unsigned long long chunks = select_chunks_f32(sp, sm_count);
     dim3 grid((unsigned)chunks, (unsigned)sp.rows);
     const int np_ = sp.plan.n_pcts;
     if (!first) return launch_fast(select_pass2_f32_kernel, sp, d_out, sp.plan.n_targets, grid, s);

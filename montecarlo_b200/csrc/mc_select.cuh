@@ -5,6 +5,23 @@
 
 namespace mc {
 
+struct SelectProblem;
+constexpr int SIDE_WARPS = 8;             // warps of a pass block (FAST_THREADS / 32)
+struct SideLists {
+    float* values;            // [rows][chunks][SIDE_WARPS][cap]
+    unsigned int* counts;     // [rows][chunks][SIDE_WARPS]   (> cap: that list overflowed)
+    uint32_t* brackets;       // [rows][1 + 2 * MAX_IV]: n, lo keys, hi keys of the pass-1 brackets
+    unsigned int cap;         // floats per warp list
+    unsigned int chunks;      // the grid.x the lists were laid out for
+};
+// chunks (grid.x) of the fp32 pass kernels for this problem, and the side-list geometry that goes with it
+unsigned long long select_chunks_f32(const SelectProblem& sp, int sm_count);
+unsigned int side_list_cap(unsigned long long n, unsigned long long chunks);
+inline size_t side_list_floats(unsigned long long rows, unsigned long long chunks, unsigned int cap) {
+    return (size_t)rows * chunks * SIDE_WARPS * cap;
+}
+constexpr int SIDE_BRACKET_WORDS = 1 + 2 * MAX_IV;
+
 // One selection problem: `rows` independent rows of `n` local values each
 // (row r starts at x + r*ld).  Terminal percentiles: rows = 1.  Fan chart: rows = T+1.
 struct SelectProblem {
@@ -18,6 +35,11 @@ struct SelectProblem {
     SelectPlan* d_plan;       // device copy
     RowSel* d_states;         // [rows]
     ScanScratch* d_scratch;   // [rows]
+    // fp32 only (null: off).  Pass 1 keeps every value it finds inside a bracket -- a few percent of the row --
+    // in a side list per (row, chunk, warp); later passes read the side lists instead of streaming the rows
+    // again (the intervals they narrow lie inside the brackets; a block whose list overflowed, or whose row has
+    // an interval outside the brackets, streams its chunk of the row as before).
+    SideLists side;
 };
 
 // Build the plan for np.percentile(method='linear') over n_global values.
