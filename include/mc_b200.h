@@ -60,7 +60,12 @@ typedef enum mc_dtype { MC_F32 = 0, MC_F64 = 1 } mc_dtype;
 enum {
     MC_FLAG_STORE_PATHS = 1u,   /* write paths[(T+1), ld] time-major like app.py:612-613 */
     MC_FLAG_FAN_CHART = 2u,     /* per-step percentiles (app.py:643-645); needs STORE_PATHS */
-    MC_FLAG_NO_TERMINAL_SELECT = 4u  /* skip percentiles / tail (moments + histogram only) */
+    MC_FLAG_NO_TERMINAL_SELECT = 4u, /* skip percentiles / tail (moments + histogram only) */
+    MC_FLAG_PATHS_VOLATILE = 8u /* staged runs: d_paths is shared with other runs and may be overwritten between
+                                   stages (fan chart by regeneration).  From the second narrowing pass on, the
+                                   handle simulates the run again by itself, and only if the values it kept from
+                                   pass 1 do not cover what the pass needs; mc_stage_reads_paths then reports 1
+                                   only for the first pass. */
 };
 
 /*

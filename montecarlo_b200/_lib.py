@@ -16,7 +16,7 @@ MC_MAX_ASSETS = 32
 SHOCK_BOOTSTRAP, SHOCK_NORMAL, SHOCK_INJECTED = 0, 1, 2
 VAR_GARCH, VAR_CONST = 0, 1
 F32, F64 = 0, 1
-FLAG_STORE_PATHS, FLAG_FAN_CHART, FLAG_NO_TERMINAL_SELECT = 1, 2, 4
+FLAG_STORE_PATHS, FLAG_FAN_CHART, FLAG_NO_TERMINAL_SELECT, FLAG_PATHS_VOLATILE = 1, 2, 4, 8
 
 EXPORTS = (
     "mc_abi_version", "mc_create", "mc_destroy", "mc_last_error", "mc_run",

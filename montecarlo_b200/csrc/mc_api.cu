@@ -89,6 +89,9 @@ struct mc_handle {
     DevBuf<unsigned long long> hist_total;
     DevBuf<unsigned long long> stage;   // internal stage buffer (mc_run, mc_percentiles)
     SideBuf side_t, side_f;             // side lists of the fp32 selection passes (terminal / fan-chart rows)
+    DevBuf<unsigned int> side_blocks;   // [1] blocks of the next pass that cannot use their side lists
+    PinnedBuf<unsigned int> h_side_blocks;
+    unsigned resimulations = 0;         // MC_FLAG_PATHS_VOLATILE: times the handle had to simulate again
     DevBuf<double> batch_pct;           // mc_run_batch: [3][n_series][n_pcts]
     DevBuf<mc_result> batch_res;        // mc_run_batch: [n_series]
     PinnedBuf<unsigned char> h_stage;   // pinned staging for the D2H of results
@@ -298,6 +301,7 @@ int mc_create(int device_ordinal, mc_handle** out) {
               h->scratch_t.reserve(1) == cudaSuccess &&
               h->pct_t.reserve(3 * MC_MAX_PCTS) == cudaSuccess && h->tail_scratch.reserve(2 * 1024) == cudaSuccess &&
               h->pending.reserve(1) == cudaSuccess && h->h_pending.reserve(1) == cudaSuccess &&
+              h->side_blocks.reserve(1) == cudaSuccess && h->h_side_blocks.reserve(1) == cudaSuccess &&
               h->lut.reserve(4096) == cudaSuccess && launch_build_direction_table(h->lut.p, nullptr) == cudaSuccess &&
               cudaStreamSynchronize(nullptr) == cudaSuccess;
     for (int i = 0; i < 3 && ok; ++i) ok = cudaEventCreate(&h->ev[i]) == cudaSuccess;
@@ -317,6 +321,7 @@ int mc_destroy(mc_handle* h) {
     h->partials.release(); h->lut.release(); h->res.release(); h->plans.release(); h->states_t.release(); h->states_f.release(); h->scratch_t.release(); h->scratch_f.release();
     h->pct_t.release(); h->fan.release(); h->tail_scratch.release(); h->edges.release(); h->hist_total.release();
     h->batch_pct.release(); h->batch_res.release(); h->side_t.release(); h->side_f.release();
+    h->side_blocks.release(); h->h_side_blocks.release();
     h->stage.release(); h->h_stage.release(); h->pending.release(); h->h_pending.release();
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->ev_pending) cudaEventDestroy(h->ev_pending);
@@ -432,9 +437,39 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
 }
 
 // enqueue one narrowing pass of every selection problem into `out`
+static int resimulate_locked(mc_handle* h, cudaStream_t s) {
+    if (h->p.n_paths == 0) return MC_OK;
+    mc_portfolio pf{};
+    if (h->has_pf) {
+        pf.h_chol = h->pf_chol.data(); pf.h_sigma_step = h->pf_sigma.data(); pf.h_drift_step = h->pf_drift.data();
+        pf.h_s0 = h->pf_s0.data(); pf.h_weights = h->pf_w.data();
+    }
+    int grid = 0;
+    MC_CUDA(h, launch_simulation(h->p, h->has_pf ? &pf : nullptr, h->sim_buffers, h->dev, &grid, s));
+    h->launches += 1;
+    return MC_OK;
+}
+
+// MC_FLAG_PATHS_VOLATILE: the rows may have been overwritten since pass 1.  A later pass works from the side
+// lists pass 1 kept; only if some block of it cannot (overflowed list, interval outside the brackets) is the
+// run simulated again first.  Costs one small device->host read.
+static int restore_rows_if_needed(mc_handle* h, cudaStream_t s) {
+    if (!(h->p.flags & MC_FLAG_PATHS_VOLATILE) || !h->has_f || h->pass_idx == 0) return MC_OK;
+    MC_CUDA(h, cudaMemsetAsync(h->side_blocks.p, 0, sizeof(unsigned int), s));
+    MC_CUDA(h, launch_side_check(h->prob_f, h->dev.sm_count, h->side_blocks.p, s));
+    MC_CUDA(h, cudaMemcpyAsync(h->h_side_blocks.p, h->side_blocks.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
+    MC_CUDA(h, cudaStreamSynchronize(s));
+    h->launches += 1;
+    if (*h->h_side_blocks.p == 0) return MC_OK;
+    h->resimulations += 1;
+    return resimulate_locked(h, s);
+}
+
 static int enqueue_pass(mc_handle* h, unsigned long long* out, cudaStream_t s) {
     const PassLayout L = layout_pass(h);
     const bool first = h->pass_idx == 0;
+    int rc = restore_rows_if_needed(h, s);
+    if (rc) return rc;
     if (h->has_t) {
         MC_CUDA(h, launch_select_pass(h->prob_t, first, out + L.off_t, h->dev.sm_count, s));
         h->launches += h->prob_t.n ? 1 : 0;
@@ -599,6 +634,7 @@ int mc_stage_reads_paths(mc_handle* h) {
     if (!h->active) return fail(h, MC_ERR_STATE, "no staged run in flight");
     if (!h->has_f) return 0;
     if (h->phase == 0) return 1;                              // brackets, then the first pass
+    if (h->p.flags & MC_FLAG_PATHS_VOLATILE) return 0;        // later passes: the handle restores the rows itself
     if (h->phase == 1) return h->pass_idx < 2 ? 1 : 0;        // scan, then pass 2 -- or the closing stage
     if (h->pending_unchecked) {                               // final stage, unless rows are still undecided
         MC_CUDA(h, cudaSetDevice(h->device));
@@ -613,17 +649,7 @@ int mc_stage_resimulate(mc_handle* h, void* stream) {
     std::lock_guard<std::mutex> lock(h->mu);
     if (!h->active) return fail(h, MC_ERR_STATE, "no staged run in flight");
     MC_CUDA(h, cudaSetDevice(h->device));
-    if (h->p.n_paths == 0) return MC_OK;
-    mc_portfolio pf{};
-    if (h->has_pf) {
-        pf.h_chol = h->pf_chol.data(); pf.h_sigma_step = h->pf_sigma.data(); pf.h_drift_step = h->pf_drift.data();
-        pf.h_s0 = h->pf_s0.data(); pf.h_weights = h->pf_w.data();
-    }
-    int grid = 0;
-    MC_CUDA(h, launch_simulation(h->p, h->has_pf ? &pf : nullptr, h->sim_buffers, h->dev, &grid,
-                                 static_cast<cudaStream_t>(stream)));
-    h->launches += 1;
-    return MC_OK;
+    return resimulate_locked(h, static_cast<cudaStream_t>(stream));
 }
 
 int mc_fetch_result(mc_handle* h, mc_result* r, uint64_t* h_hist, double* h_fan, void* stream) {

@@ -652,6 +652,40 @@ unsigned int side_list_cap(unsigned long long n, unsigned long long chunks) {
     return (unsigned int)(cap < 32 ? 32 : cap);
 }
 
+// the decision select_pass2_f32_kernel takes per block, taken for all blocks ahead of the launch
+__global__ void side_check_kernel(const RowSel* __restrict__ states, unsigned long long rows, SideLists side,
+                                  unsigned int* __restrict__ blocks) {
+    const unsigned long long row = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= rows) return;
+    const RowSel& st = states[row];
+    if (st.n_iv == 0) return;
+    const uint32_t* br = side.brackets + row * SIDE_BRACKET_WORDS;
+    const int nb = (int)br[0];
+    bool ok = true;
+    for (int i = 0; i < st.n_iv && ok; ++i) {
+        bool inside = false;
+        for (int b = 0; b < nb; ++b) inside |= br[1 + b] <= (uint32_t)st.lo[i] && (uint32_t)st.hi[i] <= br[1 + MAX_IV + b];
+        ok = inside;
+    }
+    unsigned int bad = 0;
+    for (unsigned int c = 0; c < side.chunks; ++c) {
+        bool fits = ok;
+        for (int w = 0; w < SIDE_WARPS && fits; ++w) fits = side.counts[(row * side.chunks + c) * SIDE_WARPS + w] <= side.cap;
+        bad += fits ? 0u : 1u;
+    }
+    if (bad) atomicAdd(blocks, bad);
+}
+
+cudaError_t launch_side_check(const SelectProblem& sp, int sm_count, unsigned int* d_blocks, cudaStream_t stream) {
+    if (sp.plan.n_targets == 0 || sp.rows == 0 || sp.n == 0) return cudaSuccess;
+    if (sp.dtype != MC_F32 || !sp.side.values || sp.side.chunks != select_chunks_f32(sp, sm_count)) {
+        const unsigned int all = 1u;        // no lists: every block streams its rows
+        return cudaMemcpyAsync(d_blocks, &all, sizeof(all), cudaMemcpyHostToDevice, stream);
+    }
+    side_check_kernel<<<(unsigned)((sp.rows + 127) / 128), 128, 0, stream>>>(sp.d_states, sp.rows, sp.side, d_blocks);
+    return cudaGetLastError();
+}
+
 static cudaError_t launch_pass_f32(const SelectProblem& sp, bool first, void* d_out, int sm_count, cudaStream_t s) {
     const unsigned long long chunks = select_chunks_f32(sp, sm_count);
     dim3 grid((unsigned)chunks, (unsigned)sp.rows);

@@ -73,6 +73,9 @@ cudaError_t launch_select_brackets(const SelectProblem& sp, const unsigned long 
 // collected candidates into d_out (layout row_slot_u32; zeroed by the callee)
 cudaError_t launch_select_pass(const SelectProblem& sp, bool first_pass, void* d_out, int sm_count,
                                cudaStream_t stream);
+// adds to *d_blocks the number of (row, chunk) blocks of the next fp32 pass that cannot work from their side
+// lists (they would stream the rows); adds rows * chunks when the problem has no side lists at all
+cudaError_t launch_side_check(const SelectProblem& sp, int sm_count, unsigned int* d_blocks, cudaStream_t stream);
 // merge the pass output of all ranks and shrink every target's interval; adds the number of
 // rows that still have undecided targets to *d_pending
 cudaError_t launch_select_scan(const SelectProblem& sp, const void* d_gathered_pass, unsigned int n_ranks,

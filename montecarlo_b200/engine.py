@@ -243,7 +243,8 @@ class Engine:
             for c in range(n_chunks):
                 lo = min(c * chunk, n_local)
                 cnt = min(chunk, n_local - lo)
-                params = make_params(spec, path_offset=offset + lo, n_local=cnt, paths_ld=buf.shape[1], n_ranks=vworld)
+                params = make_params(spec, path_offset=offset + lo, n_local=cnt, paths_ld=buf.shape[1], n_ranks=vworld,
+                                     paths_volatile=True)
                 backs.append(_CudaStageBackend(engines[c], params, pf, pool_t, None, buf, terminal[lo:lo + cnt], 1))
             launches = 0
             for b in backs:                      # simulate + moments + pilot sample, chunk by chunk

@@ -122,7 +122,7 @@ def shard_range(n_global: int, rank: int, world: int) -> Tuple[int, int]:
 
 
 def make_params(spec: SimSpec, path_offset: int = 0, n_local: Optional[int] = None,
-                paths_ld: int = 0, n_ranks: int = 1) -> L.McParams:
+                paths_ld: int = 0, n_ranks: int = 1, paths_volatile: bool = False) -> L.McParams:
     spec.validate()
     p = L.McParams()
     p.struct_size = C.sizeof(L.McParams)
@@ -144,6 +144,8 @@ def make_params(spec: SimSpec, path_offset: int = 0, n_local: Optional[int] = No
         flags |= L.FLAG_FAN_CHART
     if not spec.pcts:
         flags |= L.FLAG_NO_TERMINAL_SELECT
+    if paths_volatile:
+        flags |= L.FLAG_PATHS_VOLATILE
     p.flags = flags
     p.seed = spec.seed & 0xFFFFFFFFFFFFFFFF
     p.s0 = spec.s0
