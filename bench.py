@@ -328,6 +328,35 @@ def _roofline_for(workload, r, n_sm, clocks, peaks, peaks_kind):
             "fp32_lane_tflops": ach * lane_ops * 1e-12, "lane_ops_per_path_step": lane_ops}
 
 
+def callers_leg():
+    """The callers either side of the path, at the reference's own sizes: the dashboard's default call
+    through the drop-in, and 100 tickers from raw close prices in one batched call.  Wall clock, median of 7."""
+    import numpy as np
+    import pandas as pd
+    import torch
+    from montecarlo_b200 import garch_monte_carlo, garch_monte_carlo_from_close
+
+    def med(f, reps=7):
+        f()
+        ts = []
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            out = f()
+            ts.append((time.perf_counter() - t0) * 1e3)
+        return statistics.median(ts), out
+    rs = np.random.RandomState(0)
+    df = pd.DataFrame({"log_ret": rs.normal(0.0, 0.02, 1250), "rvol_20": 0.02 * math.sqrt(252)})
+    t_call, res = med(lambda: garch_monte_carlo(df, 1000, 20, 100.0, seed=1))
+    close = 50.0 * np.exp(np.cumsum(rs.normal(3e-4, 0.017, (100, 1260)), axis=1))
+    t_batch, many = med(lambda: garch_monte_carlo_from_close(close, 1000, 20, seed=1, return_paths="device"))
+    return {"drop_in_1000x20": {"ms_per_call": t_call, "device_ms": res["timing"]["total_ms"],
+                                "launches": res["timing"]["launches"], "note": "app.py:1240 with the sliders' defaults"},
+            "from_close_100_tickers_1000x20": {"ms_per_call": t_batch, "device_ms": many[0]["timing"]["total_ms"],
+                                               "launches": many[0]["timing"]["launches"],
+                                               "note": "mc_prepare_inputs + mc_run_batch, all tickers in one simulation launch"}}
+
+
 # --------------------------------------------------------------------------- CPU arms
 CPU_KIND = {"c2": "gbm", "c4": "gbm", "c5": "gbm", "c3": "gbm", "ref": "garch", "c4fan": "gbm"}
 
@@ -433,6 +462,10 @@ def main():
             except Exception as exc:      # an extra must never lose the headline line
                 extras[wl] = {"error": repr(exc)[:200]}
             torch.cuda.empty_cache()
+        try:
+            extras["callers"] = callers_leg()
+        except Exception as exc:
+            extras["callers"] = {"error": repr(exc)[:200]}
         line["extras"] = extras
     if rank == 0:
         print(json.dumps(line), flush=True)
