@@ -599,9 +599,12 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass2_f32_kernel(const fl
         const float* list = side.values + (side_slot + warp) * side.cap;
         const unsigned int cnt = side.counts[side_slot + warp];
         unsigned int i = lane;
-        for (; i + 96 < cnt; i += 128) {         // four loads in flight per lane
-            const float a0 = __ldcs(list + i), a1 = __ldcs(list + i + 32), a2 = __ldcs(list + i + 64), a3 = __ldcs(list + i + 96);
-            visit(a0); visit(a1); visit(a2); visit(a3);
+        for (; i + 224 < cnt; i += 256) {        // eight loads in flight per lane
+            float a[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) a[u] = __ldcs(list + i + 32 * u);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) visit(a[u]);
         }
         for (; i < cnt; i += 32) visit(__ldcs(list + i));
     } else {
