@@ -190,8 +190,12 @@ __device__ __forceinline__ float boot_g4(const u32x4& w) {                      
     const uint32_t b = __byte_perm(__byte_perm(w.x, w.y, 0x0040), w.z, 0x7410);   // [w0.b0, w1.b0, w2.b0, -]
     return __uint_as_float((b & 0x007FFFFFu) | 0x4B000000u);
 }
+// bits(2^23 + floor(field * H / 2^23) + 1) from g = 2^23 + field, scale = H 2^-23, bias = 2^23 - H + 1:
+// the FMA is exact inside and ROUNDS DOWN at ulp 1 (2^23 <= result < 2^24), i.e. it takes the floor.  (Round to
+// nearest with bias ... + 1/2 is wrong on the ties field * H = k 2^23: half of them land one index low, and
+// field = 0 lands on index -1.)
 __device__ __forceinline__ uint32_t boot_index_bits(float g, float scale, float bias) {
-    return __float_as_uint(fmaf(g, scale, bias));
+    return __float_as_uint(__fmaf_rd(g, scale, bias));
 }
 
 }  // namespace mc

@@ -623,7 +623,7 @@ static Sim32Args make_args32(const mc_params& p, const SimBuffers& b) {
     a.pool_len = p.pool_len;
     a.table_lc = 0;
     a.idx_scale = (float)p.pool_len * 1.1920928955078125e-07f;     // H 2^-23: exact
-    a.idx_bias = 8388608.0f - (float)p.pool_len + 0.5f;            // exact: below 2^23 the ulp is <= 1/2
+    a.idx_bias = 8388608.0f - (float)p.pool_len + 1.0f;            // exact (an integer below 2^24)
     a.rk = expand_key((uint32_t)p.seed, (uint32_t)(p.seed >> 32));
     a.lut = b.d_lut;
     a.pool = static_cast<const float*>(b.d_pool);

@@ -20,7 +20,7 @@ struct Sim32Args {
     unsigned long long n_paths, path_offset, ld_paths;
     uint32_t n_steps, pool_len;
     int table_lc;                  // BOOTSTRAP: log2(copies) of the shared table
-    float idx_scale, idx_bias;     // BOOTSTRAP: H 2^-23 and 2^23 - H + 1/2 (mc_rng.cuh: boot_index_bits)
+    float idx_scale, idx_bias;     // BOOTSTRAP: H 2^-23 and 2^23 - H + 1 (mc_rng.cuh: boot_index_bits)
     RoundKeys rk;
     const float2* lut;             // NORMAL: [DIR_COUNT] (cos, sin), built once per handle
     const float* pool;             // BOOTSTRAP: [pool_len]

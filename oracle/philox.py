@@ -145,12 +145,16 @@ def _boot_fields(w):
 
 
 def _boot_index32(field, pool_len: int):
-    """floor(field*H/2^23) exactly as the device's single FFMA rounds it."""
+    """floor(field*H/2^23).  The device takes it with ONE fp32 FMA that rounds down:
+    rd((2^23 + field) * (H 2^-23) + (2^23 - H + 1)) = 2^23 + floor(field*H/2^23) + 1 -- the product and the sum are
+    exact inside the FMA and the result lies in [2^23, 2^24), where the fp32 grid is the integers.  Restated here
+    with that same single rounding (exact in fp64, then floor), and checked against the integer floor in
+    tests/test_oracle_golden.py."""
     g = 8388608.0 + field.astype(np.float64)                       # exact
     scale = float(np.float32(pool_len) * np.float32(2.0 ** -23))     # exact in fp32
-    bias = float(np.float32(8388608.0 - pool_len + 0.5))             # exact in fp32
-    t = np.float32(g * scale + bias)                                 # exact in fp64, ONE rounding to fp32
-    return (t.view(np.uint32).astype(np.int64) - 0x4B000000) - 1
+    bias = float(np.float32(8388608.0 - pool_len + 1.0))             # exact in fp32
+    t = np.floor(g * scale + bias)                                   # exact in fp64; rounding down to the fp32 grid
+    return (t.astype(np.float32).view(np.uint32).astype(np.int64) - 0x4B000000) - 1
 
 
 def bootstrap_indices(seed: int, path_offset: int, n_paths: int, n_steps: int, pool_len: int,

@@ -96,6 +96,22 @@ def test_device_bootstrap_run_matches_port(engine, dtype, n, t):
     assert out2.pct == out.pct and out2.paths is None and out2.fan is None
 
 
+@pytest.mark.parametrize("store", [False, True])
+def test_fp32_bootstrap_values_do_not_depend_on_the_size_of_the_run(engine, store):
+    """Regression: with round-to-nearest in the single-FMA floor, a 23-bit field of 0 (one draw in 8.4 million)
+    became index -1 and the kernel read whatever lay in front of its shared-memory table -- a handful of paths
+    per million then depended on the launch shape (found by the 4-GPU NCCL run against one GPU)."""
+    pool = port.bootstrap_pool(np.random.RandomState(5).standard_t(4, 1250) * 0.014)
+    outs = {}
+    for n in (2_000_003, 500_001, 500_000, 20_000):
+        spec = SimSpec(n_paths=n, n_steps=60, s0=100.0, var0=1.6e-4, dtype="float32", seed=12, store_paths=store)
+        outs[n] = engine.simulate(spec, pool=pool).terminal
+    base = outs[2_000_003]
+    assert bool(torch.isfinite(base).all()) and float(base.min()) > 0
+    for n, v in outs.items():
+        assert torch.equal(v, base[:n]), n
+
+
 @pytest.mark.parametrize("dtype", ["float32", "float64"])
 def test_gbm_injected_and_device_normals(engine, dtype):
     n, t, s0, mu, sigma, dt, seed = 4099, 37, 100.0, 0.05, 0.2, 1 / 252, 99

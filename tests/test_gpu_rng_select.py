@@ -38,8 +38,11 @@ def test_device_normals_match_bit_model(engine, dtype, tol):
 
 
 @pytest.mark.parametrize("dtype", ["float32", "float64"])
-def test_device_bootstrap_draws_match_bit_model(engine, dtype):
-    n, t, seed, H = 2000, 9, 77, 1250
+@pytest.mark.parametrize("n,t,H", [(2000, 9, 1250), (60_000, 25, 1024), (20_000, 10, 65536), (30_000, 20, 100)])
+def test_device_bootstrap_draws_match_bit_model(engine, dtype, n, t, H):
+    """Pool lengths with a power of two in them put many 23-bit fields exactly on an index boundary
+    (field * H = k 2^23: one draw in 8192 for H = 1024): the fp32 single-FMA floor must take those right."""
+    seed = 77
     pool = np.random.RandomState(1).normal(size=H)
     spec = SimSpec(n_paths=n, n_steps=t, s0=100.0, dtype=dtype, seed=seed, var0=4e-4)
     z = engine.debug_shocks(spec, pool=pool).cpu().numpy()
