@@ -112,6 +112,34 @@ def test_fp32_bootstrap_values_do_not_depend_on_the_size_of_the_run(engine, stor
         assert torch.equal(v, base[:n]), n
 
 
+@pytest.mark.parametrize("mode", ["gbm32", "gbm32_store", "gbm64", "garch64", "portfolio32"])
+def test_values_do_not_depend_on_the_size_of_the_run(engine, mode):
+    """A path's value is a function of (seed, global path id) only: runs of different sizes -- hence different
+    grids, block sizes and shared-memory layouts -- agree on their common paths bit for bit."""
+    from montecarlo_b200 import PortfolioSpec
+    pool = port.bootstrap_pool(np.random.RandomState(5).standard_t(4, 1250) * 0.014)
+    sizes = (1_500_003, 300_001, 300_000, 9_000) if mode != "portfolio32" else (400_003, 100_001, 9_000)
+    outs = {}
+    for n in sizes:
+        if mode.startswith("gbm"):
+            spec = SimSpec.gbm(n, 48, 100.0, 0.05, 0.2, 1 / 252, dtype="float32" if "32" in mode else "float64", seed=3,
+                               store_paths=mode.endswith("store"))
+            p = None
+        elif mode == "garch64":
+            spec, p = SimSpec(n_paths=n, n_steps=48, s0=100.0, var0=1.6e-4, dtype="float64", seed=3), pool
+        else:
+            d = 16
+            pf = PortfolioSpec(s0=[100.0] * d, mu=[0.05] * d, sigma=[0.15 + 0.01 * i for i in range(d)], weights=[1.0 / d] * d,
+                               corr=0.3 * np.ones((d, d)) + 0.7 * np.eye(d))
+            spec, p = SimSpec(n_paths=n, n_steps=12, s0=100.0, shock="normal", var_model="const", dtype="float32", seed=3,
+                              portfolio=pf), None
+        outs[n] = engine.simulate(spec, pool=p).terminal
+    base = outs[sizes[0]]
+    assert bool(torch.isfinite(base).all())
+    for n, v in outs.items():
+        assert torch.equal(v, base[:n]), n
+
+
 @pytest.mark.parametrize("dtype", ["float32", "float64"])
 def test_gbm_injected_and_device_normals(engine, dtype):
     n, t, s0, mu, sigma, dt, seed = 4099, 37, 100.0, 0.05, 0.2, 1 / 252, 99
