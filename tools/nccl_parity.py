@@ -24,6 +24,16 @@ cases = {
     "garch 2,000,000 x 40 fp32, fan chart by regeneration": (SimSpec(n_paths=2_000_000, n_steps=40, s0=100.0, var0=1.6e-4, dtype="float32",
                                                                     seed=14, store_paths=True, fan_chart=True, fan_chunk_paths=100_000), pool),
 }
+from montecarlo_b200 import PortfolioSpec
+d = 16
+pf = PortfolioSpec(s0=[100.0] * d, mu=[0.05] * d, sigma=[0.15 + 0.01 * i for i in range(d)], weights=[1.0 / d] * d,
+                   corr=0.3 * np.ones((d, d)) + 0.7 * np.eye(d))
+cases["gbm 2,000,001 x 100 fp32, stored paths + fan chart"] = (
+    SimSpec.gbm(2_000_001, 100, 100.0, 0.05, 0.2, 1 / 252, dtype="float32", seed=15, store_paths=True, fan_chart=True), None)
+cases["16-asset portfolio 1,000,003 x 252 fp32"] = (
+    SimSpec(n_paths=1_000_003, n_steps=252, s0=100.0, shock="normal", var_model="const", dtype="float32", seed=16, portfolio=pf), None)
+cases["garch 10,000,019 x 252 fp32 (the reference's model at config-2 size)"] = (
+    SimSpec(n_paths=10_000_019, n_steps=252, s0=100.0, var0=1.6e-4, dtype="float32", seed=17, hist_bins=512), pool)
 report = {}
 for name, (spec, p) in cases.items():
     shard = eng.simulate(spec, pool=p, group=dist.group.WORLD)
