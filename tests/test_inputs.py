@@ -152,3 +152,24 @@ def test_batched_run_many_histories_without_paths():
     assert one["percentiles"] == res[17]["percentiles"]
     assert np.array_equal(one["final_prices"].cpu().numpy(), res[17]["final_prices"].cpu().numpy())
     assert res[0]["timing"]["launches"] < 30                  # for all 64 histories together
+
+
+@pytest.mark.gpu
+def test_long_histories_take_the_global_memory_paths():
+    """Pools beyond 40 KB are gathered from global memory by the batched kernel and re-read by the calibration
+    instead of being staged in shared memory: same results as one run per history / as the restatement."""
+    from oracle import garch_fit
+    from montecarlo_b200 import calibrate_garch, garch_monte_carlo_from_close
+    lengths = np.array([9000, 6500, 700], dtype=np.uint32)
+    close = np.full((3, 9000), 5.0)
+    for b, n in enumerate(lengths):
+        close[b, :n] = 30.0 * np.exp(np.cumsum(garch_fit.simulate_garch(int(n), 4e-6, 0.07, 0.9, seed=70 + b)))
+    loop = garch_monte_carlo_from_close(close, 600, 15, lengths=lengths, seed=2, batched=False)
+    batch = garch_monte_carlo_from_close(close, 600, 15, lengths=lengths, seed=2, batched=True)
+    for a, b in zip(loop, batch):
+        assert np.array_equal(a["paths"], b["paths"]) and a["percentiles"] == b["percentiles"]
+    fits = calibrate_garch(close, lengths=lengths)
+    for b, n in enumerate(lengths):
+        exp = garch_fit.calibrate(port.history_inputs(close[b, :n])["returns"])
+        assert abs(fits[b]["objective"] - exp["objective"]) <= 1e-9 * abs(exp["objective"])
+        assert abs(fits[b]["alpha"] - exp["alpha"]) <= 2e-4 and abs(fits[b]["beta"] - exp["beta"]) <= 2e-4
