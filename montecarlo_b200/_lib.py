@@ -69,6 +69,12 @@ class McResult(C.Structure):
     ]
 
 
+RESULT_DTYPE = [("n", "<u8"), ("n_above", "<u8"), ("mean", "<f8"), ("std", "<f8"), ("min", "<f8"), ("max", "<f8"),
+                ("pct", "<f8", (MC_MAX_PCTS,)), ("pct_lo", "<f8", (MC_MAX_PCTS,)), ("pct_hi", "<f8", (MC_MAX_PCTS,)),
+                ("tail_count", "<u8"), ("tail_sum", "<f8"), ("hist_lo", "<f8"), ("hist_hi", "<f8"),
+                ("sim_ms", "<f4"), ("total_ms", "<f4"), ("launches", "<u4"), ("reserved", "<u4")]
+
+
 class McSeriesInputs(C.Structure):
     """mc_series_inputs (include/mc_b200.h): what app.py:592/606/609/1213 derive from one price history."""
     _fields_ = [("s0", C.c_double), ("var0", C.c_double), ("pool_std", C.c_double),

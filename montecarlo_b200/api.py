@@ -246,6 +246,46 @@ def calibrate_garch(close, *, lengths=None, first_row: int = SMA_WARMUP_ROWS, le
     return out[0] if single else out
 
 
+def _batch_dicts(res, fan_all, terminal, paths, info, how, fit):
+    """Result dicts (app.py:647-657) for every history of one mc_run_batch, built from the arrays in one go."""
+    s0 = info["s0"]
+    with np.errstate(all="ignore"):
+        expected_return = (res["mean"] / s0 - 1) * 100            # app.py:652
+        expected_vol = res["std"] / s0 * 100                      # app.py:653
+        prob_profit = res["n_above"] / np.maximum(res["n"], 1) * 100
+        tail_k = REF_TERMINAL_PCTS.index(REF_TAIL_PCT)
+        var_tail = (s0 - res["pct"][:, tail_k]) / s0 * 100        # app.py:655
+        cvar_tail = (s0 - res["tail_sum"] / np.maximum(res["tail_count"], 1)) / s0 * 100   # app.py:656
+    names = [f"p{p:g}" for p in REF_TERMINAL_PCTS]
+    fan_names = [f"p{p:g}" for p in REF_PATH_PCTS]
+    fan_t = np.ascontiguousarray(fan_all.transpose(0, 2, 1)) if fan_all is not None else None
+    if how == "numpy":
+        host_paths = paths.to("cpu").numpy() if paths is not None else None
+        host_final = terminal.to("cpu").numpy() if paths is None else None
+    out = []
+    for b in range(len(res)):
+        if res["n"][b] == 0:
+            out.append(None)
+            continue
+        d = {}
+        if how == "numpy":
+            d["paths"] = host_paths[b] if host_paths is not None else None
+            d["final_prices"] = host_paths[b, -1, :] if host_paths is not None else host_final[b]   # a view, app.py:636
+        else:
+            d["paths"] = paths[b] if paths is not None else None
+            d["final_prices"] = terminal[b]
+        d["percentiles"] = dict(zip(names, res["pct"][b, :len(names)]))
+        d["path_percentiles"] = dict(zip(fan_names, fan_t[b])) if fan_t is not None else None
+        d["expected_return"], d["expected_vol"], d["prob_profit"] = expected_return[b], expected_vol[b], prob_profit[b]
+        d[f"var_{100 - REF_TAIL_PCT:g}"], d[f"cvar_{100 - REF_TAIL_PCT:g}"] = var_tail[b], cvar_tail[b]
+        d["timing"] = {"sim_ms": float(res["sim_ms"][b]), "total_ms": float(res["total_ms"][b]),
+                       "launches": int(res["launches"][b])}
+        if fit is not None:
+            d["garch"] = _garch_entry(fit, b)
+        out.append(d)
+    return out
+
+
 def _run_batches(eng, pool, info, n_sims, n_days, base, omega, alpha, beta, return_paths, fan_chart, fit=None):
     store, how = _decide_paths(n_sims, n_days, "float64", return_paths)
     want_fan = store if fan_chart is None else bool(fan_chart)
@@ -256,14 +296,11 @@ def _run_batches(eng, pool, info, n_sims, n_days, base, omega, alpha, beta, retu
     results = []
     for b0 in range(0, len(info), step):
         sl = slice(b0, min(len(info), b0 + step))
-        outs = eng.simulate_batch(pool[sl], info[sl], n_sims, n_days, (base + b0) & 0xFFFFFFFFFFFFFFFF,
-                                  omega=omega, alpha=alpha, beta=beta, pcts=REF_TERMINAL_PCTS,
-                                  path_pcts=REF_PATH_PCTS, tail_pct=REF_TAIL_PCT, store_paths=store, fan_chart=want_fan,
-                                  fit=None if fit is None else (fit[0][sl], fit[1][sl]))
-        for i, o in enumerate(outs):
-            results.append(None if o is None else _result_dict(o, o.spec.s0, how))
-            if o is not None and fit is not None:
-                results[-1]["garch"] = _garch_entry(fit[1], b0 + i)
+        res, fan_all, terminal, paths = eng.simulate_batch(
+            pool[sl], info[sl], n_sims, n_days, (base + b0) & 0xFFFFFFFFFFFFFFFF, omega=omega, alpha=alpha, beta=beta,
+            pcts=REF_TERMINAL_PCTS, path_pcts=REF_PATH_PCTS, tail_pct=REF_TAIL_PCT, store_paths=store,
+            fan_chart=want_fan, fit=None if fit is None else (fit[0][sl], fit[1][sl]), raw=True)
+        results += _batch_dicts(res, fan_all, terminal, paths, info[sl], how, None if fit is None else fit[1][sl])
     return results
 
 

@@ -371,7 +371,7 @@ class Engine:
 
     def simulate_batch(self, pool: torch.Tensor, info: np.ndarray, n_paths: int, n_steps: int, seed: int, *,
                        omega: float, alpha: float, beta: float, pcts, path_pcts, tail_pct, store_paths: bool,
-                       fan_chart: bool, min_history: int = 100, fit=None):
+                       fan_chart: bool, min_history: int = 100, fit=None, raw: bool = False):
         """`mc_run_batch`: the reference's model (fp64) for every price history of `prepare_inputs` in one
         simulation launch.  Returns a list with one RunOutput per history (None where it was skipped)."""
         if pool.dtype != torch.float64:
@@ -402,6 +402,8 @@ class Engine:
                                              C.c_void_p(terminal.data_ptr()), C.cast(results, C.c_void_p),
                                              C.c_void_p(fan.ctypes.data) if fan is not None else C.c_void_p(0),
                                              self.stream_ptr()))
+        if raw:      # (mc_result records as a structured array, fan [n_series, T+1, n_path_pcts], terminal, paths)
+            return np.frombuffer(results, dtype=np.dtype(L.RESULT_DTYPE)).copy(), fan, terminal, paths
         outs = []
         for b in range(n_series):
             if results[b].n == 0:
