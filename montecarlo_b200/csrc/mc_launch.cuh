@@ -14,20 +14,30 @@ namespace mc {
 struct LaunchCache {
     std::mutex mu;
     std::map<std::tuple<int, const void*>, size_t> smem_limit;                 // (device, kernel) -> bytes enabled
+    std::map<std::tuple<int, const void*>, size_t> static_smem;                // (device, kernel) -> static bytes
     std::map<std::tuple<int, const void*, int, size_t>, int> blocks_per_sm;   // (device, kernel, block, smem)
     static LaunchCache& get() { static LaunchCache c; return c; }
 };
 
-// make `smem` bytes of dynamic shared memory launchable for `func` on the current device
+// make `smem` bytes of dynamic shared memory launchable for `func` on the current device: the opt-in is needed
+// as soon as dynamic + STATIC shared memory exceed 48 KB (the static size is asked of the runtime once)
 template <typename K>
-inline cudaError_t ensure_dynamic_smem(K func, size_t smem, size_t static_smem = 0) {
-    if (smem + static_smem <= 48 * 1024) return cudaSuccess;
+inline cudaError_t ensure_dynamic_smem(K func, size_t smem, size_t /*static_hint*/ = 0) {
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     LaunchCache& c = LaunchCache::get();
     std::lock_guard<std::mutex> lock(c.mu);
-    size_t& have = c.smem_limit[std::make_tuple(dev, reinterpret_cast<const void*>(func))];
+    const auto key = std::make_tuple(dev, reinterpret_cast<const void*>(func));
+    auto st = c.static_smem.find(key);
+    if (st == c.static_smem.end()) {
+        cudaFuncAttributes attr{};
+        e = cudaFuncGetAttributes(&attr, func);
+        if (e != cudaSuccess) return e;
+        st = c.static_smem.emplace(key, attr.sharedSizeBytes).first;
+    }
+    if (smem + st->second <= 48 * 1024) return cudaSuccess;
+    size_t& have = c.smem_limit[key];
     if (have >= smem) return cudaSuccess;
     e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess) have = smem;

@@ -622,10 +622,8 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass2_f32_kernel(const fl
 template <typename K>
 static cudaError_t launch_fast(K k, const SelectProblem& sp, void* d_out, int n_iv_smem, dim3 grid, cudaStream_t stream) {
     const size_t smem = (size_t)n_iv_smem * SEL_BINS * sizeof(unsigned int);
-    if (smem > 20 * 1024) {      // the kernels also hold up to ~21 KB of static shared memory (queue / map)
-        cudaError_t e = ensure_dynamic_smem(k, smem, 28 * 1024);
-        if (e != cudaSuccess) return e;
-    }
+    cudaError_t e = ensure_dynamic_smem(k, smem);      // the kernels also hold ~21 KB of static shared memory
+    if (e != cudaSuccess) return e;
     const float* x = static_cast<const float*>(sp.x);
     const int vec = (sp.ld % 4 == 0 && ((uintptr_t)x & 15u) == 0) ? 1 : 0;
     SideLists side = sp.side;
@@ -703,10 +701,8 @@ template <typename Real, int NIV>
 static cudaError_t launch_pass_t(const SelectProblem& sp, void* d_out, int n_iv_smem, dim3 grid, cudaStream_t stream) {
     auto k = select_pass_kernel<Real, NIV>;
     const size_t smem = (size_t)n_iv_smem * SEL_BINS * sizeof(unsigned int);
-    if (smem > 48 * 1024) {
-        cudaError_t e = ensure_dynamic_smem(k, smem);
-        if (e != cudaSuccess) return e;
-    }
+    cudaError_t e = ensure_dynamic_smem(k, smem);
+    if (e != cudaSuccess) return e;
     k<<<grid, 256, smem, stream>>>(static_cast<const Real*>(sp.x), sp.ld, sp.n, sp.d_states,
                                    static_cast<unsigned int*>(d_out), row_slot_u32(sp.dtype, sp.plan.n_targets),
                                    iv_slot_u32(sp.dtype), sp.plan.n_targets);
