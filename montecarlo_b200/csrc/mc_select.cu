@@ -1037,15 +1037,20 @@ __global__ void __launch_bounds__(256) tail_hist_kernel(const Real* __restrict__
                                                         unsigned int bins, const double* __restrict__ edges,
                                                         const float* __restrict__ edges_f,
                                                         double* __restrict__ scratch,
-                                                        unsigned long long* __restrict__ counts) {
+                                                        unsigned long long* __restrict__ counts, int staged) {
+    // staged: edges and per-block counts live in shared memory; else (more bins than fit) the edges are read
+    // through L1 and every value adds to the global counts directly
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ double s_sum[8];
     __shared__ unsigned long long s_cnt[8];
-    Real* s_edge = reinterpret_cast<Real*>(smem_raw);                               // [bins + 1]
-    unsigned int* s_counts = reinterpret_cast<unsigned int*>(s_edge + (bins ? bins + 2 : 0));   // [bins]
+    Real* s_edge_buf = reinterpret_cast<Real*>(smem_raw);                           // [bins + 1]
+    unsigned int* s_counts = reinterpret_cast<unsigned int*>(s_edge_buf + (bins ? bins + 2 : 0));   // [bins]
     const Real* esrc = EdgeSrc<Real>::get(edges, edges_f);
-    for (unsigned int i = threadIdx.x; i < bins; i += blockDim.x) s_counts[i] = 0u;
-    for (unsigned int i = threadIdx.x; bins && i <= bins; i += blockDim.x) s_edge[i] = esrc[i];
+    if (staged) {
+        for (unsigned int i = threadIdx.x; i < bins; i += blockDim.x) s_counts[i] = 0u;
+        for (unsigned int i = threadIdx.x; bins && i <= bins; i += blockDim.x) s_edge_buf[i] = esrc[i];
+    }
+    const Real* s_edge = staged ? s_edge_buf : esrc;
     __syncthreads();
     // v <= thr (a double) for a float v  <=>  v <= floor_f32(thr)
     Real thr = (Real)(-INFINITY);
@@ -1067,7 +1072,8 @@ __global__ void __launch_bounds__(256) tail_hist_kernel(const Real* __restrict__
             idx = idx < 0 ? 0 : (idx > last ? last : idx);
             while (idx > 0 && v < s_edge[idx]) --idx;
             while (idx < last && v >= s_edge[idx + 1]) ++idx;
-            atomicAdd(&s_counts[idx], 1u);
+            if (staged) atomicAdd(&s_counts[idx], 1u);
+            else atomicAdd(&counts[idx], 1ull);
         }
     };
     unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1091,7 +1097,7 @@ __global__ void __launch_bounds__(256) tail_hist_kernel(const Real* __restrict__
         scratch[2 * blockIdx.x] = ts;
         scratch[2 * blockIdx.x + 1] = __longlong_as_double((long long)tc);
     }
-    for (unsigned int i = threadIdx.x; i < bins; i += blockDim.x) {
+    for (unsigned int i = threadIdx.x; staged && i < bins; i += blockDim.x) {
         const unsigned int c = s_counts[i];
         if (c) atomicAdd(&counts[i], (unsigned long long)c);
     }
@@ -1130,17 +1136,19 @@ cudaError_t launch_tail_hist(const void* x, int dtype, unsigned long long n, boo
     if (blocks > 1024) blocks = 1024;
     if (blocks > (unsigned long long)sm_count * 6) blocks = (unsigned long long)sm_count * 6;
     const size_t esz = dtype == MC_F64 ? 8 : 4;
-    const size_t smem = bins ? ((size_t)bins + 2) * esz + (size_t)bins * 4 : 0;
+    size_t smem = bins ? ((size_t)bins + 2) * esz + (size_t)bins * 4 : 0;
+    const int staged = smem <= 96 * 1024 ? 1 : 0;           // 8192 fp64 / 12288 fp32 bins; two blocks per SM
+    if (!staged) smem = 0;
     if (dtype == MC_F64) {
         auto k = tail_hist_kernel<double>;
         if ((e = ensure_dynamic_smem(k, smem)) != cudaSuccess) return e;
         k<<<(unsigned)blocks, 256, smem, stream>>>(static_cast<const double*>(x), n, d_res, want_tail ? 1 : 0, bins,
-                                                   d_edges, d_edges_f, d_scratch, d_words + 2);
+                                                   d_edges, d_edges_f, d_scratch, d_words + 2, staged);
     } else {
         auto k = tail_hist_kernel<float>;
         if ((e = ensure_dynamic_smem(k, smem)) != cudaSuccess) return e;
         k<<<(unsigned)blocks, 256, smem, stream>>>(static_cast<const float*>(x), n, d_res, want_tail ? 1 : 0, bins,
-                                                   d_edges, d_edges_f, d_scratch, d_words + 2);
+                                                   d_edges, d_edges_f, d_scratch, d_words + 2, staged);
     }
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     if (want_tail) {
