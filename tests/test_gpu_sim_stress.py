@@ -71,3 +71,33 @@ def test_random_job(engine, seed):
             assert np.array_equal(np.stack([out.fan[f"p{p:g}"] for p in spec.path_pcts]), ref)
     else:
         assert out.paths is None
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_fan_chart_by_regeneration(engine, seed):
+    """Random chunkings of a stored-paths job (every chunk a virtual rank of the stage protocol, simulated again
+    only when a pass needs its rows): the same exact results as the job kept whole."""
+    rs = np.random.RandomState(7000 + seed)
+    n = int(rs.choice([1000, 4099, 50_001, 120_000]))
+    t = int(rs.choice([1, 3, 20, 61]))
+    dtype = str(rs.choice(["float32", "float64"]))
+    chunk = int(rs.choice([max(4096, n // 7), max(4096, n // 3), 4096]))
+    pcts = tuple(sorted(set(np.round(rs.uniform(0, 100, int(rs.randint(1, 10))), 0).tolist())))
+    kw = dict(dtype=dtype, seed=int(rs.randint(1, 1 << 30)), store_paths=True, fan_chart=True, pcts=pcts,
+              tail_pct=float(pcts[0]), hist_bins=int(rs.choice([0, 64])), hist_range=(50.0, 200.0))
+    pool = None
+    if rs.uniform() < 0.5:
+        mk = lambda **e: SimSpec.gbm(n, t, 100.0, 0.05, 0.25, 1 / 252, **kw, **e)
+    else:
+        pool = port.bootstrap_pool(rs.standard_t(4, int(rs.choice([128, 1250]))) * 0.014)
+        mk = lambda **e: SimSpec(n_paths=n, n_steps=t, s0=100.0, var0=2e-4, **kw, **e)
+    whole = engine.simulate(mk(), pool=pool)
+    parts = engine.simulate(mk(fan_chunk_paths=chunk), pool=pool)
+    assert torch.equal(whole.terminal, parts.terminal)
+    assert whole.pct == parts.pct and whole.n_above == parts.n_above and whole.tail_count == parts.tail_count
+    for k in whole.fan:
+        assert np.array_equal(whole.fan[k], parts.fan[k]), k
+    if whole.hist is not None:
+        assert np.array_equal(whole.hist, parts.hist)
+    assert abs(whole.mean - parts.mean) <= 1e-12 * abs(whole.mean)
+    assert abs(whole.tail_sum - parts.tail_sum) <= 1e-12 * abs(whole.tail_sum)
