@@ -403,13 +403,26 @@ __device__ __forceinline__ void fast_stream(const float* __restrict__ xr, unsign
         const unsigned long long n4 = (end - beg) >> 2;
         const unsigned long long n4_even = n4 - n4 % (4ull * FAST_THREADS);     // whole batches: no lane idles
         unsigned long long i = tid;
-        for (; i < n4_even; i += 4ull * FAST_THREADS) {
-            float4 q[4];
+        // the loads of the next batch are issued before this batch is worked on: a warp always has 64 bytes per
+        // lane in flight (without this the pass stalls on its own loads at 50 % occupancy, ncu: long scoreboard)
+        float4 q[4];
+        if (i < n4_even) {
 #pragma unroll
             for (int u = 0; u < 4; ++u) q[u] = __ldcs(x4 + i + (unsigned long long)u * FAST_THREADS);
+        }
+        while (i < n4_even) {
+            const unsigned long long nxt = i + 4ull * FAST_THREADS;
+            float4 qn[4];
+            if (nxt < n4_even) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) qn[u] = __ldcs(x4 + nxt + (unsigned long long)u * FAST_THREADS);
+            }
 #pragma unroll
             for (int u = 0; u < 4; ++u) { f(q[u].x); f(q[u].y); f(q[u].z); f(q[u].w); }
             batch_done();
+#pragma unroll
+            for (int u = 0; u < 4; ++u) q[u] = qn[u];
+            i = nxt;
         }
         for (; i < n4; i += FAST_THREADS) { const float4 q = __ldcs(x4 + i); f(q.x); f(q.y); f(q.z); f(q.w); }
         for (unsigned long long k = beg + (n4 << 2) + tid; k < end; k += FAST_THREADS) f(xr[k]);
@@ -530,6 +543,183 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass1_f32_kernel(const fl
 #pragma unroll
     for (int g = 0; g < NB; ++g) {
         const unsigned int total = __reduce_add_sync(0xffffffffu, (unsigned int)cnt[g]);
+        if ((tid & 31) == 0 && g < n_iv && total) atomicAdd(&out_ge[g], (unsigned long long)total);
+    }
+    __syncthreads();
+    for (int i = tid; i < n_iv * SEL_BINS; i += FAST_THREADS) {
+        const unsigned int v = s_bins[i];
+        if (v) atomicAdd(&out_iv[(size_t)(i >> SEL_BIN_BITS) * iv_slot + 2 + (i & (SEL_BINS - 1))], v);
+    }
+}
+
+// Pass 1 for <= 5 brackets (the fan chart, app.py:643-645) with the classification of a value taken from a
+// table instead of a compare chain.  The brackets of a row are sorted and disjoint, so a value lies in one
+// of n_iv + 1 GAPS between them or inside a bracket.  q(v) = rn(2047 sat(v qs + qb)) is monotone in v (two
+// correctly rounded FMAs and a clamp), so with q evaluated at the bracket bounds by the very same
+// instructions, every table bin that lies strictly between q(hi[j-1]) and q(lo[j]) holds values of gap j
+// only -- whatever the rounding did.  Those bins carry a one-hot 5-bit field (a thread sees <= 16 values
+// between two flushes); all other bins carry 0 and their values (in a bracket, or in one of the <= 2 n_iv
+// bins that straddle a bound) take the exact path through the queue.  Per value: 2 FFMA, LEA, LDS, IADD and the
+// predicated park -- against 3 instructions PER BRACKET before.
+constexpr int LUT_BINS = 2048;
+constexpr float LUT_TOP_F = (float)(LUT_BINS - 1);
+constexpr uint32_t LUT_MAGIC_BITS = 0x4B000000u;        // bits of 2^23: rn(t + 2^23) has the integer t in its mantissa
+
+__device__ __forceinline__ uint32_t lut_bits(float v, float qs, float qb) {
+    float t, u;
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(t) : "f"(v), "f"(qs), "f"(qb));          // NaN -> 0
+    asm("fma.rn.f32 %0, %1, %2, %3;" : "=f"(u) : "f"(t), "f"(LUT_TOP_F), "f"(8388608.0f));
+    return __float_as_uint(u);                                                             // LUT_MAGIC_BITS + bin
+}
+
+__global__ void __launch_bounds__(FAST_THREADS) select_pass1_lut_f32_kernel(const float* __restrict__ x, unsigned long long ld,
+                                                                            unsigned long long n, int vec,
+                                                                            const RowSel* __restrict__ states,
+                                                                            unsigned int* __restrict__ out, size_t row_slot,
+                                                                            size_t iv_slot, int n_iv_cap, SideLists side) {
+    constexpr int NB = 5;
+    extern __shared__ unsigned int s_bins[];
+    __shared__ uint32_t s_lo[MAX_IV];
+    __shared__ int s_shift[MAX_IV];
+    __shared__ uint32_t s_lut[LUT_BINS];
+    __shared__ float s_queue[QUEUE_DEPTH * FAST_THREADS];
+    __shared__ float s_ring[SIDE_WARPS][64];
+    const unsigned long long row = blockIdx.y;
+    const RowSel& st = states[row];
+    const int n_iv = st.n_iv;
+    if (n_iv == 0) return;
+    const int tid = threadIdx.x;
+    if (tid < n_iv) { s_lo[tid] = (uint32_t)st.lo[tid]; s_shift[tid] = st.shift[tid]; }
+    for (int i = tid; i < n_iv * SEL_BINS; i += FAST_THREADS) s_bins[i] = 0u;
+    const size_t side_slot = (row * gridDim.x + blockIdx.x) * SIDE_WARPS + (tid >> 5);
+    float* side_w = side.values ? side.values + side_slot * side.cap : nullptr;
+    unsigned int side_n = 0;                 // warp-uniform
+    if (side.values && blockIdx.x == 0) {    // remember the brackets the lists cover
+        uint32_t* br = side.brackets + row * SIDE_BRACKET_WORDS;
+        if (tid == 0) br[0] = (uint32_t)n_iv;
+        if (tid < n_iv) { br[1 + tid] = (uint32_t)st.lo[tid]; br[1 + MAX_IV + tid] = (uint32_t)st.hi[tid]; }
+    }
+
+    float lo_f[NB], hi_f[NB], cnt[NB];      // cnt: parked values at or above lo (per thread < 2^24: exact in fp32)
+    float fmin_ = INFINITY, fmax_ = -INFINITY;
+#pragma unroll
+    for (int g = 0; g < NB; ++g) {
+        const bool used = g < n_iv;
+        const uint32_t kl = used ? (uint32_t)st.lo[g] : 0u, kh = used ? (uint32_t)st.hi[g] : 0u;
+        lo_f[g] = used ? value_of(kl < KEY32_NEG_INF ? KEY32_NEG_INF : kl) : __int_as_float(0x7FC00000);   // NaN: never >=
+        hi_f[g] = value_of(kh > KEY32_POS_INF ? KEY32_POS_INF : (kh < KEY32_NEG_INF ? KEY32_NEG_INF : kh));
+        cnt[g] = 0.0f;
+        if (used && fabsf(lo_f[g]) < INFINITY) { fmin_ = fminf(fmin_, lo_f[g]); fmax_ = fmaxf(fmax_, lo_f[g]); }
+        if (used && fabsf(hi_f[g]) < INFINITY) { fmin_ = fminf(fmin_, hi_f[g]); fmax_ = fmaxf(fmax_, hi_f[g]); }
+    }
+    // the table spans the finite bracket bounds plus 1/64 on either side
+    float qs = 0.0f, qb = 0.0f;
+    {
+        const float w = fmax_ - fmin_, m = w * (1.0f / 64.0f);
+        const float s = 1.0f / (w + 2.0f * m), b = -(fmin_ - m) * s;
+        if (w > 0.0f && s > 0.0f && s < INFINITY && fabsf(b) < INFINITY) { qs = s; qb = b; }      // else: every bin parks
+    }
+    {
+        uint32_t qlo[NB], qhi[NB];
+#pragma unroll
+        for (int g = 0; g < NB; ++g) {
+            qlo[g] = lut_bits(lo_f[g], qs, qb) - LUT_MAGIC_BITS;
+            qhi[g] = lut_bits(hi_f[g], qs, qb) - LUT_MAGIC_BITS;
+        }
+        for (uint32_t k = tid; k < (uint32_t)LUT_BINS; k += FAST_THREADS) {
+            int gap = 0;
+            bool straddles = qs == 0.0f;
+#pragma unroll
+            for (int g = 0; g < NB; ++g) {
+                if (g < n_iv) {
+                    gap += qhi[g] < k ? 1 : 0;
+                    straddles |= qlo[g] <= k && k <= qhi[g];
+                }
+            }
+            s_lut[k] = straddles ? 0u : 1u << (5 * gap);
+        }
+    }
+    __syncthreads();
+
+    unsigned int* out_row = out + row * row_slot;
+    unsigned int* out_iv = out_row + 2 * (size_t)n_iv_cap;
+    uint32_t lut_base;                       // table address minus the shifted magic, opaque to the compiler: the
+    asm volatile("mov.u32 %0, %1;"           // address of a value's word is then ONE LEA
+                 : "=r"(lut_base) : "r"((uint32_t)__cvta_generic_to_shared(s_lut) - (LUT_MAGIC_BITS << 2)));
+    uint32_t acc = 0u;                       // six 5-bit gap counters of the current batch
+    unsigned int gapc[NB + 1];
+#pragma unroll
+    for (int j = 0; j <= NB; ++j) gapc[j] = 0u;
+    const uint32_t q_base = (uint32_t)__cvta_generic_to_shared(s_queue) + 4u * tid;
+    uint32_t q_top = q_base;                 // byte address of this thread's next free queue slot
+    volatile float* ring = s_ring[tid >> 5];
+    unsigned int n_ring = 0u;                // warp-uniform
+    const unsigned int lane = tid & 31, lane_lt = (1u << lane) - 1u;
+    // exact treatment of one parked value per lane: counts at or above each lower bound, and -- inside a bracket --
+    // the bracket's histogram and the warp's side list
+    auto exact = [&](float v, bool live) {
+        int g = -1;
+        float top = -INFINITY;
+#pragma unroll
+        for (int k = 0; k < NB; ++k) {
+            const bool ge = live && v >= lo_f[k];
+            cnt[k] += ge ? 1.0f : 0.0f;
+            g += ge ? 1 : 0;
+            top = ge ? hi_f[k] : top;
+        }
+        const bool inb = g >= 0 && v <= top;
+        if (inb) atomicAdd(&s_bins[g * SEL_BINS + ((key_of(v) - s_lo[g]) >> s_shift[g])], 1u);
+        const unsigned int who = __ballot_sync(0xffffffffu, inb);
+        if (side_w && inb) {
+            const unsigned int pos = side_n + __popc(who & lane_lt);
+            if (pos < side.cap) side_w[pos] = v;
+        }
+        side_n += __popc(who);
+    };
+    unsigned long long beg, end;
+    fast_block_range(n, &beg, &end);
+    fast_stream(x + row * ld, beg, end, vec != 0,
+        [&](float v) {
+            uint32_t w;
+            asm("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"((lut_bits(v, qs, qb) << 2) + lut_base));
+            acc += w;
+            asm volatile("{\n\t.reg .pred q;\n\tsetp.eq.u32 q, %2, 0;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, %3;\n\t}"
+                         : "+r"(q_top) : "f"(v), "r"(w), "n"(4 * FAST_THREADS) : "memory");
+        },
+        [&]() {
+#pragma unroll
+            for (int j = 0; j <= NB; ++j) gapc[j] += (acc >> (5 * j)) & 31u;
+            acc = 0u;
+            // the lanes hold 0..16 parked values each (1.5 on average): pack them into the warp's ring and
+            // treat them 32 at a time, every lane busy
+            for (;;) {
+                const bool has = q_top != q_base;
+                const unsigned int who = __ballot_sync(0xffffffffu, has);
+                if (!who) break;
+                if (has) {
+                    q_top -= 4u * FAST_THREADS;
+                    float v;
+                    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(q_top) : "memory");
+                    ring[n_ring + __popc(who & lane_lt)] = v;
+                }
+                n_ring += __popc(who);
+                __syncwarp();
+                if (n_ring >= 32u) {
+                    n_ring -= 32u;
+                    exact(ring[n_ring + lane], true);
+                    __syncwarp();
+                }
+            }
+        });
+    if (n_ring) exact(lane < n_ring ? ring[lane] : 0.0f, lane < n_ring);
+    if (side_w && (tid & 31) == 0) side.counts[side_slot] = side_n;       // > cap: overflowed, not usable
+
+    unsigned long long* out_ge = reinterpret_cast<unsigned long long*>(out_row);
+    unsigned int above = 0u;                 // values of this thread in the gaps above bracket g
+#pragma unroll
+    for (int g = NB - 1; g >= 0; --g) {
+        above += gapc[g + 1];
+        const unsigned int total = __reduce_add_sync(0xffffffffu, (unsigned int)cnt[g] + above);
         if ((tid & 31) == 0 && g < n_iv && total) atomicAdd(&out_ge[g], (unsigned long long)total);
     }
     __syncthreads();
@@ -692,7 +882,9 @@ static cudaError_t launch_pass_f32(const SelectProblem& sp, bool first, void* d_
     dim3 grid((unsigned)chunks, (unsigned)sp.rows);
     const int np_ = sp.plan.n_pcts;
     if (!first) return launch_fast(select_pass2_f32_kernel, sp, d_out, sp.plan.n_targets, grid, s);
-    if (np_ <= 5) return launch_fast(select_pass1_f32_kernel<5>, sp, d_out, np_, grid, s);
+    if (np_ <= 5)
+        return getenv("MC_PASS1_CHAIN") ? launch_fast(select_pass1_f32_kernel<5>, sp, d_out, np_, grid, s)
+                                        : launch_fast(select_pass1_lut_f32_kernel, sp, d_out, np_, grid, s);
     if (np_ <= 9) return launch_fast(select_pass1_f32_kernel<9>, sp, d_out, np_, grid, s);
     return launch_fast(select_pass1_f32_kernel<16>, sp, d_out, np_, grid, s);
 }
