@@ -394,7 +394,7 @@ __device__ __forceinline__ void fast_member(const FastRow& c, uint32_t key) {
 
 // stream one block's share [beg, end) of a row through f(value), calling batch_done() after every 16
 // values of a thread (warp-converged); 16-byte loads when the row allows it
-template <typename F, typename G>
+template <bool PREFETCH, typename F, typename G>
 __device__ __forceinline__ void fast_stream(const float* __restrict__ xr, unsigned long long beg, unsigned long long end,
                                             bool vec, F f, G batch_done) {
     const int tid = threadIdx.x;
@@ -406,22 +406,27 @@ __device__ __forceinline__ void fast_stream(const float* __restrict__ xr, unsign
         // the loads of the next batch are issued before this batch is worked on: a warp always has 64 bytes per
         // lane in flight (without this the pass stalls on its own loads at 50 % occupancy, ncu: long scoreboard)
         float4 q[4];
-        if (i < n4_even) {
+        if (PREFETCH && i < n4_even) {
 #pragma unroll
             for (int u = 0; u < 4; ++u) q[u] = __ldcs(x4 + i + (unsigned long long)u * FAST_THREADS);
         }
         while (i < n4_even) {
             const unsigned long long nxt = i + 4ull * FAST_THREADS;
             float4 qn[4];
-            if (nxt < n4_even) {
+            if (!PREFETCH) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) q[u] = __ldcs(x4 + i + (unsigned long long)u * FAST_THREADS);
+            } else if (nxt < n4_even) {
 #pragma unroll
                 for (int u = 0; u < 4; ++u) qn[u] = __ldcs(x4 + nxt + (unsigned long long)u * FAST_THREADS);
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u) { f(q[u].x); f(q[u].y); f(q[u].z); f(q[u].w); }
             batch_done();
+            if (PREFETCH) {
 #pragma unroll
-            for (int u = 0; u < 4; ++u) q[u] = qn[u];
+                for (int u = 0; u < 4; ++u) q[u] = qn[u];
+            }
             i = nxt;
         }
         for (; i < n4; i += FAST_THREADS) { const float4 q = __ldcs(x4 + i); f(q.x); f(q.y); f(q.z); f(q.w); }
@@ -503,7 +508,7 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass1_f32_kernel(const fl
     uint32_t q_top = q_base;                 // byte address of this thread's next free queue slot
     unsigned long long beg, end;
     fast_block_range(n, &beg, &end);
-    fast_stream(x + row * ld, beg, end, vec != 0,
+    fast_stream<false>(x + row * ld, beg, end, vec != 0,
         [&](float v) {
             float top = -INFINITY;           // upper bound of the last bracket whose lower bound v reached
 #pragma unroll
@@ -572,15 +577,14 @@ __device__ __forceinline__ uint32_t lut_bits(float v, float qs, float qb) {
     return __float_as_uint(u);                                                             // LUT_MAGIC_BITS + bin
 }
 
-__global__ void __launch_bounds__(FAST_THREADS) select_pass1_lut_f32_kernel(const float* __restrict__ x, unsigned long long ld,
+__global__ void __launch_bounds__(FAST_THREADS, 3) select_pass1_lut_f32_kernel(const float* __restrict__ x, unsigned long long ld,
                                                                             unsigned long long n, int vec,
                                                                             const RowSel* __restrict__ states,
                                                                             unsigned int* __restrict__ out, size_t row_slot,
                                                                             size_t iv_slot, int n_iv_cap, SideLists side) {
     constexpr int NB = 5;
     extern __shared__ unsigned int s_bins[];
-    __shared__ uint32_t s_lo[MAX_IV];
-    __shared__ int s_shift[MAX_IV];
+    __shared__ uint4 s_br[NB];               // per bracket: lower key, shift, upper bound (float bits), address of its bins
     __shared__ uint32_t s_lut[LUT_BINS];
     __shared__ float s_queue[QUEUE_DEPTH * FAST_THREADS];
     __shared__ float s_ring[SIDE_WARPS][64];
@@ -589,7 +593,13 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass1_lut_f32_kernel(cons
     const int n_iv = st.n_iv;
     if (n_iv == 0) return;
     const int tid = threadIdx.x;
-    if (tid < n_iv) { s_lo[tid] = (uint32_t)st.lo[tid]; s_shift[tid] = st.shift[tid]; }
+    if (tid < NB) {
+        const uint32_t kh = tid < n_iv ? (uint32_t)st.hi[tid] : 0u;
+        const float hf = value_of(kh > KEY32_POS_INF ? KEY32_POS_INF : (kh < KEY32_NEG_INF ? KEY32_NEG_INF : kh));
+        s_br[tid] = make_uint4(tid < n_iv ? (uint32_t)st.lo[tid] : 0u, tid < n_iv ? (uint32_t)st.shift[tid] : 0u,
+                               __float_as_uint(hf),
+                               (uint32_t)__cvta_generic_to_shared(s_bins) + (uint32_t)tid * SEL_BINS * 4u);
+    }
     for (int i = tid; i < n_iv * SEL_BINS; i += FAST_THREADS) s_bins[i] = 0u;
     const size_t side_slot = (row * gridDim.x + blockIdx.x) * SIDE_WARPS + (tid >> 5);
     float* side_w = side.values ? side.values + side_slot * side.cap : nullptr;
@@ -652,23 +662,33 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass1_lut_f32_kernel(cons
     for (int j = 0; j <= NB; ++j) gapc[j] = 0u;
     const uint32_t q_base = (uint32_t)__cvta_generic_to_shared(s_queue) + 4u * tid;
     uint32_t q_top = q_base;                 // byte address of this thread's next free queue slot
-    volatile float* ring = s_ring[tid >> 5];
-    unsigned int n_ring = 0u;                // warp-uniform
+    if (side_w) asm volatile("mov.u64 %0, %0;" : "+l"(side_w));      // keep the pointer in registers (it was rebuilt per store)
+    float* ring = s_ring[tid >> 5];
+    const uint32_t ring_addr = (uint32_t)__cvta_generic_to_shared(ring);
+    uint32_t ring_top = ring_addr;           // fill level of the ring, as an address (warp-uniform)
     const unsigned int lane = tid & 31, lane_lt = (1u << lane) - 1u;
-    // exact treatment of one parked value per lane: counts at or above each lower bound, and -- inside a bracket --
-    // the bracket's histogram and the warp's side list
-    auto exact = [&](float v, bool live) {
-        int g = -1;
-        float top = -INFINITY;
+    // exact treatment of one parked value per lane (NaN: idle lane): counts at or above each lower bound, and --
+    // inside a bracket -- the bracket's histogram and the warp's side list
+    uint32_t br_addr;
+    asm volatile("mov.u32 %0, %1;" : "=r"(br_addr) : "r"((uint32_t)__cvta_generic_to_shared(s_br)));
+    auto exact = [&](float v) {
+        float gf = 0.0f;
 #pragma unroll
         for (int k = 0; k < NB; ++k) {
-            const bool ge = live && v >= lo_f[k];
-            cnt[k] += ge ? 1.0f : 0.0f;
-            g += ge ? 1 : 0;
-            top = ge ? hi_f[k] : top;
+            float ge;
+            asm("set.ge.f32.f32 %0, %1, %2;" : "=f"(ge) : "f"(v), "f"(lo_f[k]));     // 1.0f / 0.0f
+            cnt[k] += ge;
+            gf += ge;
         }
-        const bool inb = g >= 0 && v <= top;
-        if (inb) atomicAdd(&s_bins[g * SEL_BINS + ((key_of(v) - s_lo[g]) >> s_shift[g])], 1u);
+        const int g = __float2int_rn(gf) - 1;
+        uint4 br;
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(br.x), "=r"(br.y), "=r"(br.z), "=r"(br.w)
+                     : "r"(br_addr + 16u * (uint32_t)(g < 0 ? 0 : g)) : "memory");
+        const bool inb = g >= 0 && v <= __uint_as_float(br.z);
+        if (inb) {
+            const uint32_t a = br.w + (((key_of(v) - br.x) >> br.y) << 2);
+            asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(a) : "memory");
+        }
         const unsigned int who = __ballot_sync(0xffffffffu, inb);
         if (side_w && inb) {
             const unsigned int pos = side_n + __popc(who & lane_lt);
@@ -678,7 +698,7 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass1_lut_f32_kernel(cons
     };
     unsigned long long beg, end;
     fast_block_range(n, &beg, &end);
-    fast_stream(x + row * ld, beg, end, vec != 0,
+    fast_stream<true>(x + row * ld, beg, end, vec != 0,
         [&](float v) {
             uint32_t w;
             asm("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"((lut_bits(v, qs, qb) << 2) + lut_base));
@@ -690,28 +710,39 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass1_lut_f32_kernel(cons
 #pragma unroll
             for (int j = 0; j <= NB; ++j) gapc[j] += (acc >> (5 * j)) & 31u;
             acc = 0u;
-            // the lanes hold 0..16 parked values each (1.5 on average): pack them into the warp's ring and
-            // treat them 32 at a time, every lane busy
-            for (;;) {
-                const bool has = q_top != q_base;
-                const unsigned int who = __ballot_sync(0xffffffffu, has);
-                if (!who) break;
-                if (has) {
-                    q_top -= 4u * FAST_THREADS;
-                    float v;
-                    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(q_top) : "memory");
-                    ring[n_ring + __popc(who & lane_lt)] = v;
-                }
-                n_ring += __popc(who);
-                __syncwarp();
-                if (n_ring >= 32u) {
-                    n_ring -= 32u;
-                    exact(ring[n_ring + lane], true);
+            // the lanes hold 0..16 parked values each (1.5 on average).  They are packed into the warp's ring --
+            // a lane's values go behind those of the lanes below it -- and treated 32 at a time, every lane busy
+            {
+                // one value per lane and turn; shared-memory addresses are kept as 32-bit registers and the
+                // predicated part is spelled out (the C++ form of this loop compiled to 40 instructions a turn)
+                for (;;) {
+                    const unsigned int who = __ballot_sync(0xffffffffu, q_top != q_base);
+                    if (!who) break;
+                    asm volatile("{\n\t.reg .pred p;\n\t.reg .b32 t;\n\t.reg .f32 v;\n\t"
+                                 "setp.ne.u32 p, %0, %2;\n\t"
+                                 "@p sub.u32 %0, %0, %3;\n\t"
+                                 "@p ld.shared.f32 v, [%0];\n\t"
+                                 "and.b32 t, %4, %5;\n\t"
+                                 "popc.b32 t, t;\n\t"
+                                 "shl.b32 t, t, 2;\n\t"
+                                 "add.u32 t, t, %1;\n\t"
+                                 "@p st.shared.f32 [t], v;\n\t}"
+                                 : "+r"(q_top) : "r"(ring_top), "r"(q_base), "n"(4 * FAST_THREADS), "r"(who), "r"(lane_lt)
+                                 : "memory");
+                    ring_top += 4u * __popc(who);
                     __syncwarp();
+                    if (ring_top >= ring_addr + 128u) {
+                        ring_top -= 128u;
+                        float v;
+                        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(ring_top + 4u * lane) : "memory");
+                        exact(v);
+                        __syncwarp();
+                    }
                 }
             }
         });
-    if (n_ring) exact(lane < n_ring ? ring[lane] : 0.0f, lane < n_ring);
+    const unsigned int n_ring = (ring_top - ring_addr) >> 2;
+    if (n_ring) exact(lane < n_ring ? ring[lane] : __int_as_float(0x7FC00000));
     if (side_w && (tid & 31) == 0) side.counts[side_slot] = side_n;       // > cap: overflowed, not usable
 
     unsigned long long* out_ge = reinterpret_cast<unsigned long long*>(out_row);
@@ -800,7 +831,7 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass2_f32_kernel(const fl
     } else {
         unsigned long long beg, end;
         fast_block_range(n, &beg, &end);
-        fast_stream(x + row * ld, beg, end, vec != 0, visit, [] {});
+        fast_stream<false>(x + row * ld, beg, end, vec != 0, visit, [] {});
     }
     __syncthreads();
     for (int i = tid; i < n_iv * SEL_BINS; i += FAST_THREADS) {
@@ -882,9 +913,7 @@ static cudaError_t launch_pass_f32(const SelectProblem& sp, bool first, void* d_
     dim3 grid((unsigned)chunks, (unsigned)sp.rows);
     const int np_ = sp.plan.n_pcts;
     if (!first) return launch_fast(select_pass2_f32_kernel, sp, d_out, sp.plan.n_targets, grid, s);
-    if (np_ <= 5)
-        return getenv("MC_PASS1_CHAIN") ? launch_fast(select_pass1_f32_kernel<5>, sp, d_out, np_, grid, s)
-                                        : launch_fast(select_pass1_lut_f32_kernel, sp, d_out, np_, grid, s);
+    if (np_ <= 5) return launch_fast(select_pass1_lut_f32_kernel, sp, d_out, np_, grid, s);
     if (np_ <= 9) return launch_fast(select_pass1_f32_kernel<9>, sp, d_out, np_, grid, s);
     return launch_fast(select_pass1_f32_kernel<16>, sp, d_out, np_, grid, s);
 }
