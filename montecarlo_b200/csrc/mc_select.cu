@@ -421,7 +421,10 @@ __device__ __forceinline__ void fast_stream(const float* __restrict__ xr, unsign
                 for (int u = 0; u < 4; ++u) qn[u] = __ldcs(x4 + nxt + (unsigned long long)u * FAST_THREADS);
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) { f(q[u].x); f(q[u].y); f(q[u].z); f(q[u].w); }
+            for (int u = 0; u < 4; ++u) {
+                if constexpr (PREFETCH) f(q[u]);       // the functor of the prefetching form also takes four values at once
+                else { f(q[u].x); f(q[u].y); f(q[u].z); f(q[u].w); }
+            }
             batch_done();
             if (PREFETCH) {
 #pragma unroll
@@ -699,12 +702,28 @@ __global__ void __launch_bounds__(FAST_THREADS, 3) select_pass1_lut_f32_kernel(c
     unsigned long long beg, end;
     fast_block_range(n, &beg, &end);
     fast_stream<true>(x + row * ld, beg, end, vec != 0,
-        [&](float v) {
-            uint32_t w;
-            asm("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"((lut_bits(v, qs, qb) << 2) + lut_base));
-            acc += w;
-            asm volatile("{\n\t.reg .pred q;\n\tsetp.eq.u32 q, %2, 0;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, %3;\n\t}"
-                         : "+r"(q_top) : "f"(v), "r"(w), "n"(4 * FAST_THREADS) : "memory");
+        [&](auto v) {
+            if constexpr (sizeof(v) == sizeof(float4)) {       // four values: one register for the queue top throughout
+                uint32_t w0, w1, w2, w3;
+                asm("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"((lut_bits(v.x, qs, qb) << 2) + lut_base));
+                asm("ld.shared.u32 %0, [%1];" : "=r"(w1) : "r"((lut_bits(v.y, qs, qb) << 2) + lut_base));
+                asm("ld.shared.u32 %0, [%1];" : "=r"(w2) : "r"((lut_bits(v.z, qs, qb) << 2) + lut_base));
+                asm("ld.shared.u32 %0, [%1];" : "=r"(w3) : "r"((lut_bits(v.w, qs, qb) << 2) + lut_base));
+                acc += (w0 + w1) + (w2 + w3);
+                asm volatile("{\n\t.reg .pred q;\n\t"
+                             "setp.eq.u32 q, %5, 0;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, %9;\n\t"
+                             "setp.eq.u32 q, %6, 0;\n\t@q st.shared.f32 [%0], %2;\n\t@q add.u32 %0, %0, %9;\n\t"
+                             "setp.eq.u32 q, %7, 0;\n\t@q st.shared.f32 [%0], %3;\n\t@q add.u32 %0, %0, %9;\n\t"
+                             "setp.eq.u32 q, %8, 0;\n\t@q st.shared.f32 [%0], %4;\n\t@q add.u32 %0, %0, %9;\n\t}"
+                             : "+r"(q_top) : "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(w0), "r"(w1), "r"(w2), "r"(w3),
+                               "n"(4 * FAST_THREADS) : "memory");
+            } else {
+                uint32_t w;
+                asm("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"((lut_bits(v, qs, qb) << 2) + lut_base));
+                acc += w;
+                asm volatile("{\n\t.reg .pred q;\n\tsetp.eq.u32 q, %2, 0;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, %3;\n\t}"
+                             : "+r"(q_top) : "f"(v), "r"(w), "n"(4 * FAST_THREADS) : "memory");
+            }
         },
         [&]() {
 #pragma unroll
