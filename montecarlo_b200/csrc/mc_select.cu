@@ -368,8 +368,10 @@ __global__ void __launch_bounds__(256) select_pass_kernel(const Real* __restrict
 //   pass 2  `below` is known and the intervals are 1/1024 of a bracket wide: a byte map over <= 2048
 //           coarse key bins (one LDS.U8) rejects ~98 % of the values; the rest take the exact path.
 constexpr int FAST_THREADS = 256;
-constexpr int MAP_BINS_LOG2 = 11;
-constexpr int MAP_BYTES = (1 << MAP_BINS_LOG2) + 64;
+constexpr int MAP_BITS_LOG2 = 14;                 // pass 2: a bit per hashed key bin
+constexpr int MAP_BITS = 1 << MAP_BITS_LOG2;
+constexpr int MAP_WORDS = MAP_BITS / 32;
+constexpr uint32_t MAP_FILL_MAX = 2048;           // an interval wider than this many bins switches the filter off
 
 struct FastRow {
     const uint32_t* s_lo; const uint32_t* s_hi; const int* s_shift; const int* s_mode;
@@ -787,7 +789,7 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass2_f32_kernel(const fl
     extern __shared__ unsigned int s_bins[];
     __shared__ uint32_t s_lo[MAX_IV], s_hi[MAX_IV];
     __shared__ int s_shift[MAX_IV], s_mode[MAX_IV];
-    __shared__ unsigned char s_map[MAP_BYTES];
+    __shared__ uint32_t s_map[MAP_WORDS];
     __shared__ int s_use_side;
     const unsigned long long row = blockIdx.y;
     const RowSel& st = states[row];
@@ -799,13 +801,26 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass2_f32_kernel(const fl
         s_shift[tid] = st.shift[tid]; s_mode[tid] = st.mode[tid];
     }
     for (int i = tid; i < n_iv * SEL_BINS; i += FAST_THREADS) s_bins[i] = 0u;
-    for (int i = tid; i < MAP_BYTES; i += FAST_THREADS) s_map[i] = 0;
+    for (int i = tid; i < MAP_WORDS; i += FAST_THREADS) s_map[i] = 0u;
     __syncthreads();
-    const uint32_t k0 = s_lo[0], k1 = s_hi[n_iv - 1];
-    const int cs = max(0, bit_length((unsigned long long)(k1 - k0)) - MAP_BINS_LOG2);
-    const uint32_t base = k0 >> cs;
-    if (tid < n_iv)
-        for (uint32_t b = (s_lo[tid] >> cs) - base; b <= (s_hi[tid] >> cs) - base; ++b) s_map[b] = 1;   // b <= 2048
+    // prefilter: bit (key >> cs) mod 2^14 is set for every key inside an interval.  cs makes the narrowest interval
+    // about four bins wide, so a handful of the 16384 bits are set and a value outside the intervals gets past
+    // with probability ~1e-3 (the exact test behind it diverges the warp: with the former 2048 bins over the
+    // whole span of the intervals ~4 % of the parked values got past and most warps took the slow path)
+    int min_bl = 32;
+    for (int i = 0; i < n_iv; ++i) min_bl = min(min_bl, bit_length((unsigned long long)(s_hi[i] - s_lo[i])));
+    const int cs = max(0, min_bl - 2);
+    if (tid < n_iv) {
+        const uint32_t b0 = s_lo[tid] >> cs, nb = (s_hi[tid] >> cs) - b0 + 1u;
+        if (nb > MAP_FILL_MAX) {
+            for (int i = 0; i < MAP_WORDS; ++i) atomicOr(&s_map[i], 0xFFFFFFFFu);
+        } else {
+            for (uint32_t b = 0; b < nb; ++b) {
+                const uint32_t idx = (b0 + b) & (uint32_t)(MAP_BITS - 1);
+                atomicOr(&s_map[idx >> 5], 1u << (idx & 31u));
+            }
+        }
+    }
     __syncthreads();
 
     // the side lists of pass 1 hold every value of this chunk that lies in a pass-1 bracket: enough when each
@@ -831,8 +846,8 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass2_f32_kernel(const fl
     FastRow c{s_lo, s_hi, s_shift, s_mode, s_bins, out_row + 2 * (size_t)n_iv_cap, iv_slot, n_iv};
     auto visit = [&](float v) {
         const uint32_t key = key_of(v);
-        const uint32_t idx = min((key >> cs) - base, (uint32_t)(MAP_BYTES - 1));     // keys below k0 wrap: clamped too
-        if (s_map[idx]) fast_member(c, key);
+        const uint32_t idx = (key >> cs) & (uint32_t)(MAP_BITS - 1);
+        if ((s_map[idx >> 5] >> (idx & 31u)) & 1u) fast_member(c, key);
     };
     if (s_use_side) {
         const int warp = tid >> 5, lane = tid & 31;
