@@ -300,7 +300,7 @@ def _roofline_for(workload, r, n_sm, clocks, peaks, peaks_kind):
         bytes_ = 3 * 4.0 * n * (t + 1)
         ach = bytes_ / (r["ms_per_step"] * 1e-3) / 1e9
         peak = float(peaks["hbm_gbs"])
-        return {"bound": "hbm", "kernel": "whole job: 2 x sim32_kernel<STORE,V=4> + select_pass1_f32 per 8 GB chunk, pass 2 from side lists",
+        return {"bound": "hbm", "kernel": "whole job: 2 x sim32_kernel<STORE,V=4> + select_pass1_lut_f32 per 8 GB chunk, pass 2 from side lists",
                 "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
                 "peak_source": f"{peaks_kind} copy bandwidth", "algorithmic_bytes_per_job": bytes_}
     if workload == "c5":

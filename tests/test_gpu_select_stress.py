@@ -51,3 +51,30 @@ def test_random_selection_problems(engine, dtype, seed):
             ref = np.percentile(xt.cpu().numpy().astype(np.float64), pcts, axis=1).T
         same = (got == ref) | (np.isnan(got) & np.isnan(ref))
         assert same.all(), (family, rows, n, pcts, got[~same][:3], ref[~same][:3])
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_table_pass_edge_cases(engine, seed):
+    """<= 5 percentiles in fp32 take the table-driven pass 1 (select_pass1_lut_f32_kernel): rows long enough for many
+    batches per thread, unaligned rows (scalar loads), lengths that are no multiple of 4, constant rows (no usable
+    table scale: every value takes the exact path), rows whose outer brackets are infinite, heavy ties at a bracket
+    bound, and a row that is one huge outlier away from constant."""
+    rs = np.random.RandomState(7000 + seed)
+    n = int(rs.choice([262_147, 1_000_003, 2_097_152 + 5]))
+    rows = []
+    rows.append(100 * np.exp(0.02 * rs.standard_normal(n)))                       # narrow lognormal (early fan-chart rows)
+    rows.append(np.full(n, 100.0))                                                 # constant (row 0 of the paths)
+    x = rs.normal(size=n); x[rs.uniform(size=n) < 0.08] = np.inf; x[rs.uniform(size=n) < 0.08] = -np.inf
+    rows.append(x)                                                                 # p5 / p95 are infinite
+    rows.append(np.round(rs.normal(size=n), 1))                                    # ~60 distinct values: ties everywhere
+    x = np.full(n, 3.25); x[rs.randint(n)] = 1e30; x[rs.randint(n)] = -1e30
+    rows.append(x)
+    rows.append(rs.standard_t(2.0, n) * 1e-3)                                      # heavy tails around zero, both signs
+    full = torch.tensor(np.stack(rows), dtype=torch.float32, device=engine.device)
+    for view in (full, full[:, 1:], full[:, 3:n - 2]):                             # aligned / unaligned starts and ends
+        for pcts in ([5, 25, 50, 75, 95], [50.0], [0.0, 100.0], [1, 99], [33.3, 66.6, 99.99]):
+            got = engine.percentiles(view, pcts)
+            with np.errstate(all="ignore"):
+                ref = np.percentile(view.cpu().numpy().astype(np.float64), pcts, axis=1).T
+            same = (got == ref) | (np.isnan(got) & np.isnan(ref))
+            assert same.all(), (seed, n, tuple(view.shape), pcts, np.argwhere(~same)[:4].tolist(), got[~same][:3], ref[~same][:3])
