@@ -63,6 +63,19 @@ struct SideBuf {
     DevBuf<uint32_t> brackets;
     void release() { values.release(); counts.release(); brackets.release(); }
 };
+
+// Small results go to the host by stores into pinned (device-mapped) memory instead of copy-engine transfers: a
+// cudaMemcpyAsync between two kernels costs the stream ~15 us (kernel -> copy engine -> kernel), a one-block
+// kernel ~4 us (torch.profiler timeline of a config-2 job).
+__global__ void words_to_host_kernel(unsigned long long* __restrict__ dst, const unsigned long long* __restrict__ a,
+                                     size_t na, const unsigned long long* __restrict__ b, size_t nb,
+                                     const unsigned long long* __restrict__ c, size_t nc) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < na + nb + nc; i += stride)
+        dst[i] = i < na ? a[i] : (i < na + nb ? b[i - na] : c[i - na - nb]);
+}
+__global__ void u32_to_host_kernel(unsigned int* dst, const unsigned int* src) { *dst = *src; }
+constexpr size_t HOST_STORE_MAX_BYTES = 512 * 1024;     // beyond this the copy engine wins
 }  // namespace
 
 struct mc_handle {
@@ -556,7 +569,8 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
     }
     // gathered = output of narrowing pass `pass_idx`
     const PassLayout L = layout_pass(h);
-    MC_CUDA(h, cudaMemsetAsync(h->pending.p, 0, sizeof(unsigned int), s));
+    // the counter is read only behind the second and later scans; the first one may add to whatever is there
+    if (h->pass_idx >= 2) MC_CUDA(h, cudaMemsetAsync(h->pending.p, 0, sizeof(unsigned int), s));
     if (h->has_t) {
         MC_CUDA(h, launch_select_scan(h->prob_t, g + L.off_t, n_ranks, stride, h->pending.p, s));
         h->launches += 1;
@@ -567,7 +581,8 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
     }
     if (h->pass_idx < 2) return enqueue_pass(h, out, s);
     // the second pass normally decides everything: go on to the closing stage and look at the counter later
-    MC_CUDA(h, cudaMemcpyAsync(h->h_pending.p, h->pending.p, sizeof(unsigned int), cudaMemcpyDeviceToHost, s));
+    u32_to_host_kernel<<<1, 1, 0, s>>>(h->h_pending.p, h->pending.p);
+    MC_CUDA(h, cudaGetLastError());
     MC_CUDA(h, cudaEventRecord(h->ev_pending, s));
     h->pending_unchecked = true;
     return enqueue_closing(h, out, s);
@@ -582,11 +597,32 @@ static int fetch_locked(mc_handle* h, mc_result* r, uint64_t* h_hist, double* h_
     const size_t bytes = sizeof(DeviceResult) + (size_t)p.hist_bins * 8 + fan_n * 8;
     MC_CUDA(h, h->h_stage.reserve(bytes));
     unsigned char* hp = h->h_stage.p;
-    MC_CUDA(h, cudaMemcpyAsync(hp, h->res.p, sizeof(DeviceResult), cudaMemcpyDeviceToHost, s));
-    if (p.hist_bins && h_hist)
-        MC_CUDA(h, cudaMemcpyAsync(hp + sizeof(DeviceResult), h->hist_total.p, (size_t)p.hist_bins * 8, cudaMemcpyDeviceToHost, s));
-    if (fan_n && h_fan)
-        MC_CUDA(h, cudaMemcpyAsync(hp + sizeof(DeviceResult) + (size_t)p.hist_bins * 8, h->fan.p, fan_n * 8, cudaMemcpyDeviceToHost, s));
+    static_assert(sizeof(DeviceResult) % 8 == 0, "DeviceResult is copied in 8-byte words");
+    const bool want_hist = p.hist_bins && h_hist, want_fan = fan_n && h_fan;
+    if (bytes <= HOST_STORE_MAX_BYTES) {
+        const size_t na = sizeof(DeviceResult) / 8, nb = want_hist ? (size_t)p.hist_bins : 0, nc = want_fan ? fan_n : 0;
+        // the layout below keeps the histogram's slot even when it is not wanted
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(hp);
+        const unsigned int blocks = (unsigned int)((na + nb + nc + 255) / 256 < 64 ? (na + nb + nc + 255) / 256 : 64);
+        if (want_hist || !want_fan) {
+            words_to_host_kernel<<<blocks, 256, 0, s>>>(dst, reinterpret_cast<const unsigned long long*>(h->res.p), na,
+                                                        reinterpret_cast<const unsigned long long*>(h->hist_total.p), nb,
+                                                        reinterpret_cast<const unsigned long long*>(h->fan.p), nc);
+        } else {      // fan chart without histogram: two pieces around the unused histogram slot
+            words_to_host_kernel<<<blocks, 256, 0, s>>>(dst, reinterpret_cast<const unsigned long long*>(h->res.p), na,
+                                                        nullptr, 0, nullptr, 0);
+            words_to_host_kernel<<<blocks, 256, 0, s>>>(dst + na + (size_t)p.hist_bins,
+                                                        reinterpret_cast<const unsigned long long*>(h->fan.p), nc, nullptr, 0,
+                                                        nullptr, 0);
+        }
+        MC_CUDA(h, cudaGetLastError());
+    } else {
+        MC_CUDA(h, cudaMemcpyAsync(hp, h->res.p, sizeof(DeviceResult), cudaMemcpyDeviceToHost, s));
+        if (want_hist)
+            MC_CUDA(h, cudaMemcpyAsync(hp + sizeof(DeviceResult), h->hist_total.p, (size_t)p.hist_bins * 8, cudaMemcpyDeviceToHost, s));
+        if (want_fan)
+            MC_CUDA(h, cudaMemcpyAsync(hp + sizeof(DeviceResult) + (size_t)p.hist_bins * 8, h->fan.p, fan_n * 8, cudaMemcpyDeviceToHost, s));
+    }
     MC_CUDA(h, cudaStreamSynchronize(s));
     DeviceResult d;
     memcpy(&d, hp, sizeof(d));
