@@ -582,15 +582,59 @@ __device__ __forceinline__ uint32_t lut_bits(float v, float qs, float qb) {
     return __float_as_uint(u);                                                             // LUT_MAGIC_BITS + bin
 }
 
-__global__ void __launch_bounds__(FAST_THREADS, 3) select_pass1_lut_f32_kernel(const float* __restrict__ x, unsigned long long ld,
+template <int NB> struct LutWord { using type = uint32_t; };
+template <> struct LutWord<9> { using type = uint64_t; };
+template <typename W> __device__ __forceinline__ W lut_word(uint32_t addr);
+template <> __device__ __forceinline__ uint32_t lut_word<uint32_t>(uint32_t addr) {
+    uint32_t w;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(addr));
+    return w;
+}
+template <> __device__ __forceinline__ uint64_t lut_word<uint64_t>(uint32_t addr) {
+    uint64_t w;
+    asm("ld.shared.u64 %0, [%1];" : "=l"(w) : "r"(addr));
+    return w;
+}
+// park a value in the thread's queue column when its table word is 0 ("look closer"): predicated, no branch
+__device__ __forceinline__ void park1(uint32_t& q_top, float v, uint32_t w) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.eq.u32 q, %2, 0;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, %3;\n\t}"
+                 : "+r"(q_top) : "f"(v), "r"(w), "n"(4 * FAST_THREADS) : "memory");
+}
+__device__ __forceinline__ void park1(uint32_t& q_top, float v, uint64_t w) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.eq.u64 q, %2, 0;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, %3;\n\t}"
+                 : "+r"(q_top) : "f"(v), "l"(w), "n"(4 * FAST_THREADS) : "memory");
+}
+__device__ __forceinline__ void park4(uint32_t& q_top, float4 v, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
+    asm volatile("{\n\t.reg .pred q;\n\t"
+                 "setp.eq.u32 q, %5, 0;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, %9;\n\t"
+                 "setp.eq.u32 q, %6, 0;\n\t@q st.shared.f32 [%0], %2;\n\t@q add.u32 %0, %0, %9;\n\t"
+                 "setp.eq.u32 q, %7, 0;\n\t@q st.shared.f32 [%0], %3;\n\t@q add.u32 %0, %0, %9;\n\t"
+                 "setp.eq.u32 q, %8, 0;\n\t@q st.shared.f32 [%0], %4;\n\t@q add.u32 %0, %0, %9;\n\t}"
+                 : "+r"(q_top) : "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(w0), "r"(w1), "r"(w2), "r"(w3),
+                   "n"(4 * FAST_THREADS) : "memory");
+}
+__device__ __forceinline__ void park4(uint32_t& q_top, float4 v, uint64_t w0, uint64_t w1, uint64_t w2, uint64_t w3) {
+    asm volatile("{\n\t.reg .pred q;\n\t"
+                 "setp.eq.u64 q, %5, 0;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, %9;\n\t"
+                 "setp.eq.u64 q, %6, 0;\n\t@q st.shared.f32 [%0], %2;\n\t@q add.u32 %0, %0, %9;\n\t"
+                 "setp.eq.u64 q, %7, 0;\n\t@q st.shared.f32 [%0], %3;\n\t@q add.u32 %0, %0, %9;\n\t"
+                 "setp.eq.u64 q, %8, 0;\n\t@q st.shared.f32 [%0], %4;\n\t@q add.u32 %0, %0, %9;\n\t}"
+                 : "+r"(q_top) : "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "l"(w0), "l"(w1), "l"(w2), "l"(w3),
+                   "n"(4 * FAST_THREADS) : "memory");
+}
+
+template <int NB>
+__global__ void __launch_bounds__(FAST_THREADS, NB <= 5 ? 3 : 2) select_pass1_lut_f32_kernel(const float* __restrict__ x, unsigned long long ld,
                                                                             unsigned long long n, int vec,
                                                                             const RowSel* __restrict__ states,
                                                                             unsigned int* __restrict__ out, size_t row_slot,
                                                                             size_t iv_slot, int n_iv_cap, SideLists side) {
-    constexpr int NB = 5;
+    static_assert(NB == 5 || NB == 9, "gap counters: six 5-bit fields in 32 bits, or ten 6-bit fields in 64");
+    using Word = typename LutWord<NB>::type;
+    constexpr int FIELD = NB <= 5 ? 5 : 6, WSHIFT = NB <= 5 ? 2 : 3;
     extern __shared__ unsigned int s_bins[];
     __shared__ uint4 s_br[NB];               // per bracket: lower key, shift, upper bound (float bits), address of its bins
-    __shared__ uint32_t s_lut[LUT_BINS];
+    __shared__ Word s_lut[LUT_BINS];
     __shared__ float s_queue[QUEUE_DEPTH * FAST_THREADS];
     __shared__ float s_ring[SIDE_WARPS][64];
     const unsigned long long row = blockIdx.y;
@@ -651,7 +695,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 3) select_pass1_lut_f32_kernel(c
                     straddles |= qlo[g] <= k && k <= qhi[g];
                 }
             }
-            s_lut[k] = straddles ? 0u : 1u << (5 * gap);
+            s_lut[k] = straddles ? Word(0) : Word(1) << (FIELD * gap);
         }
     }
     __syncthreads();
@@ -660,8 +704,8 @@ __global__ void __launch_bounds__(FAST_THREADS, 3) select_pass1_lut_f32_kernel(c
     unsigned int* out_iv = out_row + 2 * (size_t)n_iv_cap;
     uint32_t lut_base;                       // table address minus the shifted magic, opaque to the compiler: the
     asm volatile("mov.u32 %0, %1;"           // address of a value's word is then ONE LEA
-                 : "=r"(lut_base) : "r"((uint32_t)__cvta_generic_to_shared(s_lut) - (LUT_MAGIC_BITS << 2)));
-    uint32_t acc = 0u;                       // six 5-bit gap counters of the current batch
+                 : "=r"(lut_base) : "r"((uint32_t)__cvta_generic_to_shared(s_lut) - (LUT_MAGIC_BITS << WSHIFT)));
+    Word acc = 0;                            // the gap counters of the current batch: NB + 1 fields of FIELD bits
     unsigned int gapc[NB + 1];
 #pragma unroll
     for (int j = 0; j <= NB; ++j) gapc[j] = 0u;
@@ -706,31 +750,22 @@ __global__ void __launch_bounds__(FAST_THREADS, 3) select_pass1_lut_f32_kernel(c
     fast_stream<true>(x + row * ld, beg, end, vec != 0,
         [&](auto v) {
             if constexpr (sizeof(v) == sizeof(float4)) {       // four values: one register for the queue top throughout
-                uint32_t w0, w1, w2, w3;
-                asm("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"((lut_bits(v.x, qs, qb) << 2) + lut_base));
-                asm("ld.shared.u32 %0, [%1];" : "=r"(w1) : "r"((lut_bits(v.y, qs, qb) << 2) + lut_base));
-                asm("ld.shared.u32 %0, [%1];" : "=r"(w2) : "r"((lut_bits(v.z, qs, qb) << 2) + lut_base));
-                asm("ld.shared.u32 %0, [%1];" : "=r"(w3) : "r"((lut_bits(v.w, qs, qb) << 2) + lut_base));
+                const Word w0 = lut_word<Word>((lut_bits(v.x, qs, qb) << WSHIFT) + lut_base);
+                const Word w1 = lut_word<Word>((lut_bits(v.y, qs, qb) << WSHIFT) + lut_base);
+                const Word w2 = lut_word<Word>((lut_bits(v.z, qs, qb) << WSHIFT) + lut_base);
+                const Word w3 = lut_word<Word>((lut_bits(v.w, qs, qb) << WSHIFT) + lut_base);
                 acc += (w0 + w1) + (w2 + w3);
-                asm volatile("{\n\t.reg .pred q;\n\t"
-                             "setp.eq.u32 q, %5, 0;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, %9;\n\t"
-                             "setp.eq.u32 q, %6, 0;\n\t@q st.shared.f32 [%0], %2;\n\t@q add.u32 %0, %0, %9;\n\t"
-                             "setp.eq.u32 q, %7, 0;\n\t@q st.shared.f32 [%0], %3;\n\t@q add.u32 %0, %0, %9;\n\t"
-                             "setp.eq.u32 q, %8, 0;\n\t@q st.shared.f32 [%0], %4;\n\t@q add.u32 %0, %0, %9;\n\t}"
-                             : "+r"(q_top) : "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(w0), "r"(w1), "r"(w2), "r"(w3),
-                               "n"(4 * FAST_THREADS) : "memory");
+                park4(q_top, v, w0, w1, w2, w3);
             } else {
-                uint32_t w;
-                asm("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"((lut_bits(v, qs, qb) << 2) + lut_base));
+                const Word w = lut_word<Word>((lut_bits(v, qs, qb) << WSHIFT) + lut_base);
                 acc += w;
-                asm volatile("{\n\t.reg .pred q;\n\tsetp.eq.u32 q, %2, 0;\n\t@q st.shared.f32 [%0], %1;\n\t@q add.u32 %0, %0, %3;\n\t}"
-                             : "+r"(q_top) : "f"(v), "r"(w), "n"(4 * FAST_THREADS) : "memory");
+                park1(q_top, v, w);
             }
         },
         [&]() {
 #pragma unroll
-            for (int j = 0; j <= NB; ++j) gapc[j] += (acc >> (5 * j)) & 31u;
-            acc = 0u;
+            for (int j = 0; j <= NB; ++j) gapc[j] += (unsigned int)(acc >> (FIELD * j)) & ((1u << FIELD) - 1u);
+            acc = 0;
             // the lanes hold 0..16 parked values each (1.5 on average).  They are packed into the warp's ring --
             // a lane's values go behind those of the lanes below it -- and treated 32 at a time, every lane busy
             {
@@ -947,8 +982,8 @@ static cudaError_t launch_pass_f32(const SelectProblem& sp, bool first, void* d_
     dim3 grid((unsigned)chunks, (unsigned)sp.rows);
     const int np_ = sp.plan.n_pcts;
     if (!first) return launch_fast(select_pass2_f32_kernel, sp, d_out, sp.plan.n_targets, grid, s);
-    if (np_ <= 5) return launch_fast(select_pass1_lut_f32_kernel, sp, d_out, np_, grid, s);
-    if (np_ <= 9) return launch_fast(select_pass1_f32_kernel<9>, sp, d_out, np_, grid, s);
+    if (np_ <= 5) return launch_fast(select_pass1_lut_f32_kernel<5>, sp, d_out, np_, grid, s);
+    if (np_ <= 9) return launch_fast(select_pass1_lut_f32_kernel<9>, sp, d_out, np_, grid, s);
     return launch_fast(select_pass1_f32_kernel<16>, sp, d_out, np_, grid, s);
 }
 
