@@ -329,7 +329,10 @@ struct PortArgs {
     Real v0;                          // portfolio value at t=0
     double center;
     BlockPartial* partials;
-    Real chol[D * (D + 1) / 2];       // packed lower triangle, row-major, kernel units
+    // Cholesky factor (times sigma_i per step), kernel units.  fp64: packed lower triangle, row-major,
+    // chol[r (r + 1) / 2 + c].  fp32: ROW PAIRS for the packed FFMA2 of sm_100 -- pair p = rows (2p, 2p + 1),
+    // columns 0 .. 2p + 1, entry (p, c) = (L[2p][c], L[2p+1][c]) at chol[2 (p (p + 1) + c)] (L[2p][2p+1] = 0)
+    Real chol[D * (D + 2) / 2];
     Real drift[D];                    // per step, kernel units
     Real s0w[D];                      // w_i * S0_i
 };
@@ -388,12 +391,31 @@ __global__ void __launch_bounds__(SIM_BLOCK) portfolio_kernel(const __grid_const
                 }
                 call += a.calls_per_step;
             }
+            if constexpr (sizeof(Real) == 4) {
+                // y = L z, two rows per instruction: fma.rn.f32x2 (FFMA2) takes the pair of L from a uniform
+                // register and z[c] as a broadcast operand; 72 of them replace 136 FFMA at D = 16, each row's
+                // sum in the same order as before (the extra term of an even row is fma(0, z, x) = x)
 #pragma unroll
-            for (int r = 0; r < D; ++r) {
-                Real s = x[r];
+                for (int pr = 0; pr < D / 2; ++pr) {
+                    unsigned long long acc;
+                    asm("mov.b64 %0, {%1, %2};" : "=l"(acc) : "f"(x[2 * pr]), "f"(x[2 * pr + 1]));
 #pragma unroll
-                for (int c = 0; c <= r; ++c) s = fma_units(a.chol[r * (r + 1) / 2 + c], z[c], s);
-                x[r] = s;
+                    for (int c = 0; c <= 2 * pr + 1; ++c) {
+                        unsigned long long l2, z2;
+                        asm("mov.b64 %0, {%1, %2};" : "=l"(l2) : "f"(a.chol[2 * (pr * (pr + 1) + c)]), "f"(a.chol[2 * (pr * (pr + 1) + c) + 1]));
+                        asm("mov.b64 %0, {%1, %1};" : "=l"(z2) : "f"(z[c]));
+                        asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(l2), "l"(z2));
+                    }
+                    asm("mov.b64 {%0, %1}, %2;" : "=f"(x[2 * pr]), "=f"(x[2 * pr + 1]) : "l"(acc));
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < D; ++r) {
+                    Real s = x[r];
+#pragma unroll
+                    for (int c = 0; c <= r; ++c) s = fma_units(a.chol[r * (r + 1) / 2 + c], z[c], s);
+                    x[r] = s;
+                }
             }
             if (STORE)
                 a.paths[(unsigned long long)(t + 1) * a.ld_paths + i] = portfolio_value<Real, D>(a, x, (Real)(t + 1));
@@ -717,8 +739,11 @@ static cudaError_t launch_portfolio_impl(const mc_params& p, const mc_portfolio&
     a.terminal = static_cast<Real*>(b.d_terminal);
     double v0 = 0.0;
     for (int i = 0; i < d; ++i) {
-        for (int c = 0; c <= i; ++c)
-            a.chol[i * (i + 1) / 2 + c] = (Real)(pf.h_chol[i * d + c] * pf.h_sigma_step[i] * u);
+        for (int c = 0; c <= i; ++c) {
+            const Real l = (Real)(pf.h_chol[i * d + c] * pf.h_sigma_step[i] * u);
+            if (sizeof(Real) == 4) a.chol[2 * ((i / 2) * (i / 2 + 1) + c) + (i & 1)] = l;      // row pairs (see PortArgs)
+            else a.chol[i * (i + 1) / 2 + c] = l;
+        }
         a.drift[i] = (Real)(pf.h_drift_step[i] * u);
         a.s0w[i] = (Real)(pf.h_s0[i] * pf.h_weights[i]);
         v0 += pf.h_s0[i] * pf.h_weights[i];
