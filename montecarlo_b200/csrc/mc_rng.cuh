@@ -132,27 +132,34 @@ __device__ __forceinline__ void direction_of(uint32_t w, uint32_t lut_base, floa
     asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(c), "=f"(s) : "r"(lut_base + ((w << 3) & 0x7FF8u)));
 }
 
+// (cos, sin) as one 64-bit register pair, for the packed fp32 instructions of sm_100 (FMUL2 / FFMA2)
+__device__ __forceinline__ unsigned long long direction_pair_of(uint32_t w, uint32_t lut_base) {
+    unsigned long long cs;
+    asm volatile("ld.shared.b64 %0, [%1];" : "=l"(cs) : "r"(lut_base + ((w << 3) & 0x7FF8u)));
+    return cs;
+}
+
 __device__ __forceinline__ void normals8(const u32x4& w, uint32_t lut_base, float (&z)[8]) {
     const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const float r = BM_RADIUS_SCALE_F * rho20(ww[k]);
-        float c, s;
-        direction_of(ww[k], lut_base, c, s);
-        z[2 * k] = r * c;
-        z[2 * k + 1] = r * s;
+        unsigned long long rr, zz;
+        asm("mov.b64 %0, {%1, %1};" : "=l"(rr) : "f"(r));
+        asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(zz) : "l"(rr), "l"(direction_pair_of(ww[k], lut_base)));   // (r cos, r sin)
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(z[2 * k]), "=f"(z[2 * k + 1]) : "l"(zz));
     }
 }
-// acc + (sum of the eight normals) / sqrt(2 ln 2): one FFMA per normal, constant applied by the caller
-__device__ __forceinline__ float normals8_sum(const u32x4& w, uint32_t lut_base, float acc) {
+// acc + (the eight normals) / sqrt(2 ln 2), cosine terms in the low half and sine terms in the high half of a
+// packed pair: one FFMA2 per Box-Muller pair; the caller adds the halves and applies the constant
+__device__ __forceinline__ unsigned long long normals8_sum(const u32x4& w, uint32_t lut_base, unsigned long long acc) {
     const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const float r = rho20(ww[k]);
-        float c, s;
-        direction_of(ww[k], lut_base, c, s);
-        acc = fmaf(r, c, acc);
-        acc = fmaf(r, s, acc);
+        unsigned long long rr;
+        asm("mov.b64 %0, {%1, %1};" : "=l"(rr) : "f"(r));
+        asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(rr), "l"(direction_pair_of(ww[k], lut_base)));
     }
     return acc;
 }

@@ -157,10 +157,12 @@ __global__ void __launch_bounds__(SHOCK == MC_SHOCK_NORMAL ? 512 : 1024) sim32_k
             // constant sigma, nothing stored: y_T = sigma sqrt(2 ln 2) * sum(rho * dir); one FFMA per normal
             const unsigned long long gid = a.path_offset + i0;
             const uint32_t c0 = (uint32_t)gid, c1 = (uint32_t)(gid >> 32);
-            float s = 0.0f;
+            unsigned long long s2 = 0ull;       // (sum of the cosine terms, sum of the sine terms)
 #pragma unroll 2
-            for (uint32_t j = 0; j < n_full; ++j) s = normals8_sum(philox4x32_10(c0, c1, j, 0u, a.rk), table_base, s);
-            y[0] = a.sig * BM_RADIUS_SCALE_F * s;
+            for (uint32_t j = 0; j < n_full; ++j) s2 = normals8_sum(philox4x32_10(c0, c1, j, 0u, a.rk), table_base, s2);
+            float s_cos, s_sin;
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(s_cos), "=f"(s_sin) : "l"(s2));
+            y[0] = a.sig * BM_RADIUS_SCALE_F * (s_cos + s_sin);
             t = n_full * K;
         } else {
 #pragma unroll 1
