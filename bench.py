@@ -51,12 +51,12 @@ STEPS_PER_SM_CLK = {"c2": 8.0, "c4": 8.0, "ref": 7.5, "c3": 0.33}
 # The kernels as built: what the binding pipe allows at the MEASURED issue rates of
 # sm_100a (tools/microbench*.cu: IMAD.WIDE 31.6 lanes/clk/SM, MUFU 15.9).  Philox-4x32-10 costs 20
 # IMAD.WIDE per call; a call feeds 8 normals (fp32), 5 bootstrap indices, or half a 16-asset step.
-OWN_BOUND_PER_SM_CLK = {"c2": 31.6 * 8 / 20, "c4": 31.6 * 8 / 20, "ref": 31.6 * 5 / 20, "c3": 128.0 / 310}
+OWN_BOUND_PER_SM_CLK = {"c2": 31.6 * 8 / 20, "c4": 31.6 * 8 / 20, "ref": 31.6 * 5 / 20, "c3": 128.0 / 300}
 OWN_BOUND_PIPE = {"c2": "IMAD.WIDE (Philox): 2.5 per normal at 31.6 lanes/clk/SM",
                   "c4": "IMAD.WIDE (Philox): 2.5 per normal at 31.6 lanes/clk/SM",
                   "ref": "IMAD.WIDE (Philox): 4 per bootstrap index at 31.6 lanes/clk/SM",
-                  "c3": "issue: ~310 instructions per 16-asset step (2 Philox calls, 8 Box-Muller pairs, "
-                        "152 FFMA) at 128 lane-instr/clk/SM"}
+                  "c3": "issue: ~300 instructions per 16-asset step (2 Philox calls, 8 Box-Muller pairs, "
+                        "72 FFMA2 + 16 FFMA; ncu v5: 302) at 128 lane-instr/clk/SM"}
 
 
 class ClockSampler:
