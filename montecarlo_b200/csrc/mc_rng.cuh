@@ -154,9 +154,20 @@ __device__ __forceinline__ void normals8(const u32x4& w, uint32_t lut_base, floa
 // packed pair: one FFMA2 per Box-Muller pair; the caller adds the halves and applies the constant
 __device__ __forceinline__ unsigned long long normals8_sum(const u32x4& w, uint32_t lut_base, unsigned long long acc) {
     const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+    // the four radius uniforms (radius_uniform20) by two packed FMAs
+    float v[4];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        unsigned long long b2, m2, k2, u2;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(b2) : "r"(__funnelshift_r(ww[2 * h], 0x3F8u, 12)), "r"(__funnelshift_r(ww[2 * h + 1], 0x3F8u, 12)));
+        asm("mov.b64 %0, {%1, %1};" : "=l"(m2) : "f"(-8.0f));
+        asm("mov.b64 %0, {%1, %1};" : "=l"(k2) : "f"(9.0f));
+        asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(u2) : "l"(b2), "l"(m2), "l"(k2));
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(v[2 * h]), "=f"(v[2 * h + 1]) : "l"(u2));
+    }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const float r = rho20(ww[k]);
+        const float r = fast_sqrt(-fast_lg2(v[k]));
         unsigned long long rr;
         asm("mov.b64 %0, {%1, %1};" : "=l"(rr) : "f"(r));
         asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(rr), "l"(direction_pair_of(ww[k], lut_base)));
@@ -203,6 +214,15 @@ __device__ __forceinline__ float boot_g4(const u32x4& w) {                      
 // field = 0 lands on index -1.)
 __device__ __forceinline__ uint32_t boot_index_bits(float g, float scale, float bias) {
     return __float_as_uint(__fmaf_rd(g, scale, bias));
+}
+// two at once: FFMA2.RM (sm_100 packed fp32), each half the same round-down FMA
+__device__ __forceinline__ void boot_index_bits2(float g0, float g1, float scale, float bias, uint32_t& t0, uint32_t& t1) {
+    unsigned long long g2, s2, b2, r2;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(g2) : "f"(g0), "f"(g1));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(s2) : "f"(scale));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(b2) : "f"(bias));
+    asm("fma.rm.f32x2 %0, %1, %2, %3;" : "=l"(r2) : "l"(g2), "l"(s2), "l"(b2));
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(t0), "=r"(t1) : "l"(r2));
 }
 
 }  // namespace mc

@@ -69,10 +69,14 @@ __device__ __forceinline__ void advance(const Sim32Args& a, const u32x4& w, uint
         }
     } else {
         const float gf[5] = {boot_g(w.x), boot_g(w.y), boot_g(w.z), boot_g(w.w), boot_g4(w)};
+        uint32_t tbs[5];                           // bits(2^23 + idx + 1): four of the five floors by two packed FMAs
+        boot_index_bits2(gf[0], gf[1], a.idx_scale, a.idx_bias, tbs[0], tbs[1]);
+        boot_index_bits2(gf[2], gf[3], a.idx_scale, a.idx_bias, tbs[2], tbs[3]);
+        tbs[4] = boot_index_bits(gf[4], a.idx_scale, a.idx_bias);
 #pragma unroll
         for (int k = 0; k < 5; ++k) {
             if (TAIL && k >= limit) break;
-            const uint32_t tb = boot_index_bits(gf[k], a.idx_scale, a.idx_bias);  // bits(2^23 + idx + 1)
+            const uint32_t tb = tbs[k];
             float z, g;
             if (TAB == TAB_SMEM8) {          // eight copies: the shift is an immediate and folds into one LEA
                 asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(z), "=f"(g) : "r"((tb << 6) + table_base));
