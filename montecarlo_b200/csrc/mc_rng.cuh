@@ -139,11 +139,25 @@ __device__ __forceinline__ unsigned long long direction_pair_of(uint32_t w, uint
     return cs;
 }
 
+// SCALED: eight N(0,1) draws.  !SCALED: the draws divided by sqrt(2 ln 2) -- for callers that fold the constant
+// into what multiplies the draws (the portfolio kernel's Cholesky factor)
+template <bool SCALED = true>
 __device__ __forceinline__ void normals8(const u32x4& w, uint32_t lut_base, float (&z)[8]) {
     const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+    float v[4];                     // the four radius uniforms (radius_uniform20) by two packed FMAs
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        unsigned long long b2, m2, k2, u2;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(b2) : "r"(__funnelshift_r(ww[2 * h], 0x3F8u, 12)), "r"(__funnelshift_r(ww[2 * h + 1], 0x3F8u, 12)));
+        asm("mov.b64 %0, {%1, %1};" : "=l"(m2) : "f"(-8.0f));
+        asm("mov.b64 %0, {%1, %1};" : "=l"(k2) : "f"(9.0f));
+        asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(u2) : "l"(b2), "l"(m2), "l"(k2));
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(v[2 * h]), "=f"(v[2 * h + 1]) : "l"(u2));
+    }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const float r = BM_RADIUS_SCALE_F * rho20(ww[k]);
+        const float rho = fast_sqrt(-fast_lg2(v[k]));
+        const float r = SCALED ? BM_RADIUS_SCALE_F * rho : rho;
         unsigned long long rr, zz;
         asm("mov.b64 %0, {%1, %1};" : "=l"(rr) : "f"(r));
         asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(zz) : "l"(rr), "l"(direction_pair_of(ww[k], lut_base)));   // (r cos, r sin)
@@ -183,7 +197,9 @@ __device__ __forceinline__ void normals4(const u32x4& w, double (&z)[8]) {
 }
 
 template <typename Real> struct NormalsPerCall { static constexpr int value = sizeof(Real) == 4 ? 8 : 4; };
-__device__ __forceinline__ void draw_normals(const u32x4& w, uint32_t lut_base, float (&z)[8]) { normals8(w, lut_base, z); }
+template <bool SCALED = true>
+__device__ __forceinline__ void draw_normals(const u32x4& w, uint32_t lut_base, float (&z)[8]) { normals8<SCALED>(w, lut_base, z); }
+template <bool SCALED = true>
 __device__ __forceinline__ void draw_normals(const u32x4& w, uint32_t, double (&z)[8]) { normals4(w, z); }
 
 // ---- bootstrap indices (the reference's np.random.choice(std_returns, size=n_sims), app.py:620) ----

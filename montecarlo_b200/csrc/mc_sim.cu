@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(SIM_BLOCK) portfolio_kernel(const __grid_const
                     Real zq[8] = {Real(0), Real(0), Real(0), Real(0), Real(0), Real(0), Real(0), Real(0)};
                     if (q < (int)a.calls_per_step) {
                         const u32x4 w = philox4x32_10(c0, c1, call + q, 0u, a.rk);
-                        draw_normals(w, lut_base, zq);
+                        draw_normals<false>(w, lut_base, zq);      // fp32: sqrt(2 ln 2) is folded into a.chol
                     }
 #pragma unroll
                     for (int k = 0; k < NPC; ++k)
@@ -740,7 +740,9 @@ static cudaError_t launch_portfolio_impl(const mc_params& p, const mc_portfolio&
     double v0 = 0.0;
     for (int i = 0; i < d; ++i) {
         for (int c = 0; c <= i; ++c) {
-            const Real l = (Real)(pf.h_chol[i * d + c] * pf.h_sigma_step[i] * u);
+            // fp32 device normals come without their constant sqrt(2 ln 2) (normals8<false>): it goes in here
+            const double zs = (sizeof(Real) == 4 && !INJECTED) ? (double)BM_RADIUS_SCALE_F : 1.0;
+            const Real l = (Real)(pf.h_chol[i * d + c] * pf.h_sigma_step[i] * u * zs);
             if (sizeof(Real) == 4) a.chol[2 * ((i / 2) * (i / 2 + 1) + c) + (i & 1)] = l;      // row pairs (see PortArgs)
             else a.chol[i * (i + 1) / 2 + c] = l;
         }
