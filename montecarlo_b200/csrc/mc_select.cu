@@ -674,7 +674,11 @@ __global__ void __launch_bounds__(FAST_THREADS, NB <= 5 ? 3 : 2) select_pass1_lu
     // the table spans the finite bracket bounds plus 1/64 on either side
     float qs = 0.0f, qb = 0.0f;
     {
-        const float w = fmax_ - fmin_, m = w * (1.0f / 64.0f);
+        float w = fmax_ - fmin_;
+        // one finite bound only (a bracket that reaches to an infinity: percentile 0 or 100; a constant row): any
+        // scale around it does -- the infinite bounds quantise to the first / last bin by saturation
+        if (!(w > 0.0f) && fabsf(fmin_) < INFINITY) w = fmaxf(fabsf(fmin_) * 0.015625f, 1e-30f);
+        const float m = w * (1.0f / 64.0f);
         const float s = 1.0f / (w + 2.0f * m), b = -(fmin_ - m) * s;
         if (w > 0.0f && s > 0.0f && s < INFINITY && fabsf(b) < INFINITY) { qs = s; qb = b; }      // else: every bin parks
     }
