@@ -582,6 +582,20 @@ __device__ __forceinline__ uint32_t lut_bits(float v, float qs, float qb) {
     return __float_as_uint(u);                                                             // LUT_MAGIC_BITS + bin
 }
 
+// two values: the clamp FMAs stay scalar (no .sat on the packed form), the second FMA is one FFMA2 -- each half the
+// same correctly rounded FMA as in lut_bits, so the bins are the ones the table was built for
+__device__ __forceinline__ void lut_bits2(float v0, float v1, float qs, float qb, uint32_t& b0, uint32_t& b1) {
+    float t0, t1;
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(t0) : "f"(v0), "f"(qs), "f"(qb));
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(t1) : "f"(v1), "f"(qs), "f"(qb));
+    unsigned long long t2, m2, k2, u2;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(t2) : "f"(t0), "f"(t1));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(m2) : "f"(LUT_TOP_F));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(k2) : "f"(8388608.0f));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(u2) : "l"(t2), "l"(m2), "l"(k2));
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(b0), "=r"(b1) : "l"(u2));
+}
+
 template <int NB> struct LutWord { using type = uint32_t; };
 template <> struct LutWord<9> { using type = uint64_t; };
 template <typename W> __device__ __forceinline__ W lut_word(uint32_t addr);
@@ -754,10 +768,13 @@ __global__ void __launch_bounds__(FAST_THREADS, NB <= 5 ? 3 : 2) select_pass1_lu
     fast_stream<true>(x + row * ld, beg, end, vec != 0,
         [&](auto v) {
             if constexpr (sizeof(v) == sizeof(float4)) {       // four values: one register for the queue top throughout
-                const Word w0 = lut_word<Word>((lut_bits(v.x, qs, qb) << WSHIFT) + lut_base);
-                const Word w1 = lut_word<Word>((lut_bits(v.y, qs, qb) << WSHIFT) + lut_base);
-                const Word w2 = lut_word<Word>((lut_bits(v.z, qs, qb) << WSHIFT) + lut_base);
-                const Word w3 = lut_word<Word>((lut_bits(v.w, qs, qb) << WSHIFT) + lut_base);
+                uint32_t b0, b1, b2, b3;
+                lut_bits2(v.x, v.y, qs, qb, b0, b1);
+                lut_bits2(v.z, v.w, qs, qb, b2, b3);
+                const Word w0 = lut_word<Word>((b0 << WSHIFT) + lut_base);
+                const Word w1 = lut_word<Word>((b1 << WSHIFT) + lut_base);
+                const Word w2 = lut_word<Word>((b2 << WSHIFT) + lut_base);
+                const Word w3 = lut_word<Word>((b3 << WSHIFT) + lut_base);
                 acc += (w0 + w1) + (w2 + w3);
                 park4(q_top, v, w0, w1, w2, w3);
             } else {
