@@ -174,6 +174,32 @@ def test_full_size_c2_properties():
         assert abs(res[k] - exp[k]) < 1e-9 * max(1.0, abs(exp[k])), k
 
 
+def test_full_size_c4_share_properties():
+    """BASELINE config 4: one GPU's share of 100M x 2520 (12.5M paths, fp32 GBM, ten years of daily steps):
+    exact percentiles / histogram / tail on the returned terminals, closed-form lognormal answers within 4 SE."""
+    n, t, s0, mu, sigma, dt = 12_500_000, 2520, 100.0, 0.05, 0.2, 1 / 252
+    res = simulate_gbm(n, t, s0, mu, sigma, dt=dt, seed=0x123456789ABCDEF0, hist_bins=2048)
+    term = res["final_prices"].cpu().numpy().astype(np.float64)
+    assert term.shape == (n,)
+    for p, v in zip(port.REF_TERMINAL_PCTS, np.percentile(term, port.REF_TERMINAL_PCTS)):
+        assert res["percentiles"][f"p{p}"] == v
+    h = res["histogram"]
+    assert np.array_equal(h["counts"], np.histogram(term, bins=2048, range=h["range"])[0])
+    cf = port.gbm_closed_form(s0, mu, sigma, t * dt, q=np.array(port.REF_TERMINAL_PCTS) / 100)
+    assert abs(term.mean() - cf["mean"]) < 4 * cf["std"] / math.sqrt(n)
+    # std of a lognormal with sigma sqrt(T) = 0.63: the fourth moment is large; SE from the sample itself
+    m2 = (term - term.mean()) ** 2
+    assert abs(term.std() ** 2 - cf["std"] ** 2) < 4 * m2.std() / math.sqrt(n)
+    from scipy.stats import norm
+    for p, qv in zip(port.REF_TERMINAL_PCTS, cf["quantiles"]):
+        q = p / 100
+        dens = norm.pdf(norm.ppf(q)) / (qv * sigma * math.sqrt(t * dt))
+        assert abs(res["percentiles"][f"p{p}"] - qv) < 4 * math.sqrt(q * (1 - q) / n) / dens, p
+    exp = port.terminal_statistics(term, s0)
+    for k in ("expected_return", "expected_vol", "prob_profit", "var_95", "cvar_95"):
+        assert abs(res[k] - exp[k]) < 1e-9 * max(1.0, abs(exp[k])), k
+
+
 def test_full_size_c3_portfolio_properties():
     """BASELINE config 3: 16 correlated assets, 1M x 252: portfolio mean and VaR/CVaR consistency."""
     d, n, t, dt = 16, 1_000_000, 252, 1 / 252

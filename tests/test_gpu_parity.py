@@ -189,3 +189,67 @@ def test_portfolio_matches_port(engine, dtype, d):
         _check_reductions(out, v, v0, spec)
         paths = out.paths.cpu().numpy().astype(np.float64)
         assert np.allclose(paths[0], v0, rtol=1e-6) and np.array_equal(paths[-1], v)
+
+
+# ---------------------------------------------------------------- BASELINE config 4's horizon: T = 2520 in fp32
+# SURVEY 7 names "fp32 over 2,520 steps" a hard part: the log-price is a sum of 2,520 rounded terms.  These tests
+# replay the device's own draws (oracle/philox.py bit model) through the fp64 port of the reference's loop
+# (app.py:618-633) for >= 50k paths and hold the fp32 kernels to BASELINE's per-path tolerance.
+T_LONG, N_LONG, CHUNK_LONG = 2520, 50_007, 10_000
+
+
+def _chunks(n, step):
+    return [(lo, min(step, n - lo)) for lo in range(0, n, step)]
+
+
+def test_fp32_fused_gbm_terminals_at_2520_steps_match_fp64_bit_model(engine):
+    """sim32_kernel<NORMAL, CONST, nostore> (configs 2 and 4: y_T = sigma sum z, one FFMA2 per Box-Muller pair)."""
+    s0, mu, sigma, dt, seed = 100.0, 0.05, 0.2, 1 / 252, 0xC4C4
+    spec = SimSpec.gbm(N_LONG, T_LONG, s0, mu, sigma, dt, dtype="float32", seed=seed)
+    out = engine.simulate(spec)
+    term = out.terminal.cpu().numpy().astype(np.float64)
+    worst = 0.0
+    for lo, cnt in _chunks(N_LONG, CHUNK_LONG):
+        z = philox.normal_shocks(seed, lo, cnt, T_LONG, dtype=np.float32)
+        ref = port.gbm_paths(z, s0, mu, sigma, dt)[-1]
+        worst = max(worst, float(np.abs(term[lo:lo + cnt] / ref - 1).max()))
+    assert worst < RTOL["float32"], worst
+    _check_reductions(out, term, s0, spec)
+
+
+def test_fp32_bootstrap_garch_terminals_at_2520_steps_match_fp64_bit_model(engine):
+    """sim32_kernel<BOOTSTRAP, GARCH, nostore>: the reference's own model (app.py:618-633) over ten years."""
+    s0, seed = 100.0, 0xC4C5
+    pool = port.bootstrap_pool(np.random.RandomState(3).standard_t(4, 1250) * 0.014)
+    var0 = port.initial_variance(0.02 * np.sqrt(252))
+    spec = SimSpec(n_paths=N_LONG, n_steps=T_LONG, s0=s0, var0=var0, dtype="float32", seed=seed)
+    out = engine.simulate(spec, pool=pool)
+    term = out.terminal.cpu().numpy().astype(np.float64)
+    pool_dev = pool.astype(np.float32).astype(np.float64)
+    worst = 0.0
+    for lo, cnt in _chunks(N_LONG, CHUNK_LONG):
+        idx = philox.bootstrap_indices(seed, lo, cnt, T_LONG, len(pool), dtype=np.dtype("float32"))
+        ref = port.step_paths(pool_dev[idx], s0, var0)[-1]
+        worst = max(worst, float(np.abs(term[lo:lo + cnt] / ref - 1).max()))
+    assert worst < RTOL["float32"], worst
+    _check_reductions(out, term, s0, spec)
+
+
+@pytest.mark.parametrize("model", ["gbm", "garch"])
+def test_fp32_injected_shocks_at_2520_steps(engine, model):
+    """north_star check (a) at config 4's horizon: the identical pre-generated shock matrix through the fp32
+    kernel and through the fp64 port, per-path terminals within 1e-5 relative."""
+    n, s0 = 20_003, 100.0
+    rs = np.random.RandomState(2520)
+    z32 = rs.standard_normal((T_LONG, n)).astype(np.float32)
+    z = z32.astype(np.float64)
+    if model == "gbm":
+        spec = SimSpec.gbm(n, T_LONG, s0, 0.05, 0.2, 1 / 252, dtype="float32", shock="injected")
+        ref = port.gbm_paths(z, s0, 0.05, 0.2, 1 / 252)[-1]
+    else:
+        var0 = port.initial_variance(0.02 * np.sqrt(252))
+        spec = SimSpec(n_paths=n, n_steps=T_LONG, s0=s0, shock="injected", var_model="garch", var0=var0, dtype="float32")
+        ref = port.step_paths(z, s0, var0)[-1]
+    out = engine.simulate(spec, shocks=z32)
+    term = out.terminal.cpu().numpy().astype(np.float64)
+    assert float(np.abs(term / ref - 1).max()) < RTOL["float32"]
