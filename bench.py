@@ -156,7 +156,7 @@ def make_spec(workload, world):
     else:
         returns, rvol = synthetic_history()
         pool = bootstrap_pool(returns)
-        spec = SimSpec(n_paths=n, n_steps=t, s0=S0, var0=rvol ** 2 / 252, seed=SEED, hist_bins=2048)
+        spec = SimSpec(n_paths=n, n_steps=t, s0=S0, var0=rvol ** 2 / 252, seed=SEED, hist_bins=2048, hist_range=hist_range(t))
     return spec, pool
 
 
@@ -182,7 +182,7 @@ def api_call(workload, world, group):
     returns, rvol = synthetic_history()
     df = pd.DataFrame({"log_ret": returns, "rvol_20": rvol})
     return mc.garch_monte_carlo(df, n, t, S0, seed=SEED, dtype="float32", return_paths=False, fan_chart=False,
-                                hist_bins=2048, group=group)
+                                hist_bins=2048, hist_range=hist_range(t), group=group)
 
 
 def io_bytes(workload, spec, pool):

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define MC_ABI_VERSION 2u
+#define MC_ABI_VERSION 3u
 #define MC_MAX_PCTS 16u       /* terminal percentiles per call (reference uses 9, app.py:639) */
 #define MC_MAX_PATH_PCTS 8u   /* fan-chart percentiles (reference uses 5, app.py:644) */
 #define MC_MAX_ASSETS 32u
@@ -61,11 +61,15 @@ enum {
     MC_FLAG_STORE_PATHS = 1u,   /* write paths[(T+1), ld] time-major like app.py:612-613 */
     MC_FLAG_FAN_CHART = 2u,     /* per-step percentiles (app.py:643-645); needs STORE_PATHS */
     MC_FLAG_NO_TERMINAL_SELECT = 4u, /* skip percentiles / tail (moments + histogram only) */
-    MC_FLAG_PATHS_VOLATILE = 8u /* staged runs: d_paths is shared with other runs and may be overwritten between
+    MC_FLAG_PATHS_VOLATILE = 8u, /* staged runs: d_paths is shared with other runs and may be overwritten between
                                    stages (fan chart by regeneration).  From the second narrowing pass on, the
                                    handle simulates the run again by itself, and only if the values it kept from
                                    pass 1 do not cover what the pass needs; mc_stage_reads_paths then reports 1
                                    only for the first pass. */
+    MC_FLAG_TERMINAL_GIVEN = 16u /* d_terminal already holds this rank's final prices (app.py:636): no simulation, only
+                                   the reductions of app.py:638-640 and 652-656.  What mc_run itself falls back to when
+                                   the fused closing reports mc_result.status = 1; the same call serves a caller who
+                                   produced the terminal values elsewhere. */
 };
 
 /*
@@ -127,7 +131,9 @@ typedef struct mc_result {
     float sim_ms;               /* device time of the simulation kernel(s), CUDA events */
     float total_ms;             /* device time of the whole call */
     uint32_t launches;          /* kernels launched by this call */
-    uint32_t reserved;
+    uint32_t status;            /* 0: complete.  1 (mc_run_sharded only; mc_run handles it itself): the key window of the
+                                   fused closing missed or a candidate list overflowed -- identically on every rank --
+                                   and the reductions must be redone with mc_stage_* and MC_FLAG_TERMINAL_GIVEN */
 } mc_result;
 
 typedef struct mc_handle mc_handle;
@@ -176,6 +182,32 @@ int mc_fetch_result(mc_handle* h, mc_result* h_result, uint64_t* h_hist, double*
                     void* stream);
 
 /*
+ * Path-sharded runs WITHOUT host round trips (runs without a fan chart).  The reductions of
+ * app.py:636-656 need two exchanges between the ranks -- each rank's 32 KB key histogram of its terminal values, then
+ * the values of the few histogram bins that hold the wanted order statistics plus moments / tail sums / fixed-bin
+ * counts -- and the kernels carry them out themselves: every rank owns an exchange buffer, maps its peers' buffers
+ * (CUDA IPC over NVLink), stores its contribution straight into every peer's buffer while it is being produced and
+ * raises a flag there; the consuming kernel spins on its own copy of the flags.  No NCCL launch, no stage call.
+ *
+ *   mc_peer_export(h, n_ranks, ipc_handle[64], &local_ptr, &bytes)   allocate the buffer, name it
+ *   (the host all-gathers the 64-byte handles: torch.distributed, MPI, files ...)
+ *   mc_peer_attach(h, rank, n_ranks, all_handles, NULL)              map the peers (same process: pass the
+ *                                                                    peers' local_ptr values instead of handles)
+ *   mc_run_sharded(h, params, ...)        enqueue this rank's share; every rank calls it, in the same order
+ *   mc_fetch_result(h, &result, hist, NULL, stream)                   synchronises; identical result on every rank
+ *
+ * mc_run_sharded needs params->n_ranks == n_ranks of the attachment and a request the fused closing accepts (no
+ * fan chart, an explicit histogram range, <= 16384 bins); otherwise MC_ERR_INVALID and the staged protocol above
+ * applies.  A peer that does not arrive within 20 s fails the run (MC_ERR_STATE from mc_fetch_result).
+ */
+int mc_peer_export(mc_handle* h, uint32_t n_ranks, void* out_ipc_handle /* 64 bytes, may be NULL */,
+                   void** out_local_ptr, uint64_t* out_bytes);
+int mc_peer_attach(mc_handle* h, uint32_t rank, uint32_t n_ranks, const void* ipc_handles /* n_ranks x 64 B or NULL */,
+                   void* const* local_ptrs /* n_ranks device pointers (same process) or NULL */);
+int mc_run_sharded(mc_handle* h, const mc_params* p, const mc_portfolio* pf,
+                   const void* d_pool, const void* d_shocks, void* d_paths, void* d_terminal, void* stream);
+
+/*
  * Fan chart without keeping the paths (app.py:643-645 at any n_sims).  A path range that
  * does not fit in HBM is cut into chunks that take turns in ONE [n_steps+1, chunk] buffer; each chunk runs
  * as a virtual rank of the staged protocol (one handle per chunk, n_ranks = ranks x chunks).  Paths are
@@ -202,6 +234,13 @@ int mc_debug_philox(mc_handle* h, const uint32_t* d_ctr, uint32_t n, uint32_t ke
 /* np.percentile(x[r, :], pcts, method='linear') for r in rows of a [rows, ld] matrix */
 int mc_percentiles(mc_handle* h, const void* d_x, int32_t dtype, uint64_t rows, uint64_t n,
                    uint64_t ld, const double* pcts, uint32_t n_pcts, double* h_out, void* stream);
+/* Test knobs, per handle: capacity of the fp32 selection's side lists (< 0: automatic) and whether they are used;
+ * process-wide: waves of blocks per launch of the non-persistent simulation kernels (>= 1, 0: default 24) and threads
+ * per block of the fused GBM kernel (128 / 256 / 512, 0: default).  Invalid values select the default. */
+int mc_debug_set_tuning(mc_handle* h, int side_cap, int no_side_lists, int waves, int nblock);
+/* counters: 0 fused runs, 1 fused runs that had to be redone by the staged selection, 2 status of the last fused
+ * run, 3 re-simulations of MC_FLAG_PATHS_VOLATILE runs */
+int64_t mc_debug_counter(mc_handle* h, int which);
 /* np.histogram(x, bins, range=(lo, hi)) on float64-cast values */
 int mc_histogram(mc_handle* h, const void* d_x, int32_t dtype, uint64_t n, uint32_t bins,
                  double lo, double hi, uint64_t* h_counts, void* stream);

@@ -8,7 +8,7 @@ import threading
 
 from .build import LIB_PATH
 
-MC_ABI_VERSION = 2
+MC_ABI_VERSION = 3
 MC_MAX_PCTS = 16
 MC_MAX_PATH_PCTS = 8
 MC_MAX_ASSETS = 32
@@ -16,7 +16,7 @@ MC_MAX_ASSETS = 32
 SHOCK_BOOTSTRAP, SHOCK_NORMAL, SHOCK_INJECTED = 0, 1, 2
 VAR_GARCH, VAR_CONST = 0, 1
 F32, F64 = 0, 1
-FLAG_STORE_PATHS, FLAG_FAN_CHART, FLAG_NO_TERMINAL_SELECT, FLAG_PATHS_VOLATILE = 1, 2, 4, 8
+FLAG_STORE_PATHS, FLAG_FAN_CHART, FLAG_NO_TERMINAL_SELECT, FLAG_PATHS_VOLATILE, FLAG_TERMINAL_GIVEN = 1, 2, 4, 8, 16
 
 EXPORTS = (
     "mc_abi_version", "mc_create", "mc_destroy", "mc_last_error", "mc_run",
@@ -24,6 +24,7 @@ EXPORTS = (
     "mc_stage_reads_paths", "mc_stage_resimulate",
     "mc_debug_shocks", "mc_debug_philox", "mc_percentiles", "mc_histogram", "mc_prepare_inputs",
     "mc_run_batch", "mc_calibrate_garch",
+    "mc_peer_export", "mc_peer_attach", "mc_run_sharded", "mc_debug_set_tuning", "mc_debug_counter",
 )
 
 
@@ -65,14 +66,14 @@ class McResult(C.Structure):
         ("tail_count", C.c_uint64), ("tail_sum", C.c_double),
         ("hist_lo", C.c_double), ("hist_hi", C.c_double),
         ("sim_ms", C.c_float), ("total_ms", C.c_float),
-        ("launches", C.c_uint32), ("reserved", C.c_uint32),
+        ("launches", C.c_uint32), ("status", C.c_uint32),
     ]
 
 
 RESULT_DTYPE = [("n", "<u8"), ("n_above", "<u8"), ("mean", "<f8"), ("std", "<f8"), ("min", "<f8"), ("max", "<f8"),
                 ("pct", "<f8", (MC_MAX_PCTS,)), ("pct_lo", "<f8", (MC_MAX_PCTS,)), ("pct_hi", "<f8", (MC_MAX_PCTS,)),
                 ("tail_count", "<u8"), ("tail_sum", "<f8"), ("hist_lo", "<f8"), ("hist_hi", "<f8"),
-                ("sim_ms", "<f4"), ("total_ms", "<f4"), ("launches", "<u4"), ("reserved", "<u4")]
+                ("sim_ms", "<f4"), ("total_ms", "<f4"), ("launches", "<u4"), ("status", "<u4")]
 
 
 class McSeriesInputs(C.Structure):
@@ -149,6 +150,16 @@ def _declare(lib):
     lib.mc_run_batch.argtypes = [vp, C.POINTER(McBatchParams), vp, u64, vp, vp, vp, vp, vp, vp, vp]
     lib.mc_calibrate_garch.restype = C.c_int
     lib.mc_calibrate_garch.argtypes = [vp, vp, u64, vp, u32, u32, u32, vp, vp]
+    lib.mc_peer_export.restype = C.c_int
+    lib.mc_peer_export.argtypes = [vp, u32, vp, C.POINTER(vp), C.POINTER(u64)]
+    lib.mc_peer_attach.restype = C.c_int
+    lib.mc_peer_attach.argtypes = [vp, u32, u32, vp, vp]
+    lib.mc_run_sharded.restype = C.c_int
+    lib.mc_run_sharded.argtypes = [vp, PP, PF, vp, vp, vp, vp, vp]
+    lib.mc_debug_set_tuning.restype = C.c_int
+    lib.mc_debug_set_tuning.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]
+    lib.mc_debug_counter.restype = C.c_int64
+    lib.mc_debug_counter.argtypes = [vp, C.c_int]
 
 
 def load_library(path: str | None = None):

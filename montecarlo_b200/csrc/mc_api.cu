@@ -10,6 +10,7 @@
 // still have undecided order statistics (identical on every rank) and keeps going if needed.
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -17,6 +18,7 @@
 #include <string>
 #include <vector>
 
+#include "mc_fused.cuh"
 #include "mc_inputs.cuh"
 #include "mc_select.cuh"
 #include "mc_sim.cuh"
@@ -127,6 +129,27 @@ struct mc_handle {
     SimBuffers sim_buffers{};
     bool has_pf = false;
     std::vector<double> pf_chol, pf_sigma, pf_drift, pf_s0, pf_w;
+
+    // ---- fused closing (mc_fused.cuh): runs without a fan chart ----
+    DevBuf<unsigned char> xchg;         // this handle's exchange buffer (layout `lay`)
+    XchgLayout lay{};
+    Peers peers{};                      // base[me] = xchg.p; the others are peers' buffers once attached
+    bool peers_attached = false;
+    std::vector<void*> ipc_opened;      // peer mappings to close
+    DevBuf<FusedPlan> fplan;
+    DevBuf<unsigned char> member;       // [FUSED_KB]
+    DevBuf<ClosePartial> close_partials;
+    DevBuf<unsigned long long> claim;   // [1]
+    unsigned long long fused_seq = 0;   // sharded runs so far (the flags of a run carry its number)
+    bool fused_pending = false;         // a fused run is enqueued; mc_fetch_result reads the pinned block
+    bool fused_dirty = true;            // accumulators (own histogram slots, claim counter) need zeroing
+    unsigned int edges_bins = 0;        // what h->edges currently holds
+    double edges_lo = 0.0, edges_hi = 0.0;
+    unsigned long long n_fused = 0, n_fused_fallback = 0;
+    int last_fused_status = 0;
+    // test knobs (mc_debug_set_tuning)
+    int side_cap_override = -1;
+    bool no_side_lists = false;
 };
 
 namespace {
@@ -138,6 +161,22 @@ int fail(mc_handle* h, int code, const std::string& msg) {
 int cuda_fail(mc_handle* h, cudaError_t e, const char* where) {
     return fail(h, MC_ERR_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
 }
+// Every entry point works on its handle's device and leaves the calling thread's current device as it found it
+// (a Streamlit session thread that asked for device 1 must not find itself on device 1 afterwards).
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess; else prev = -1;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceGuard(const DeviceGuard&) = delete;
+    DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+#define MC_DEVICE(h)                                                      \
+    DeviceGuard device_guard__((h)->device);                              \
+    if (!device_guard__.ok) return fail((h), MC_ERR_CUDA, "cudaSetDevice failed")
 #define MC_CUDA(h, call)                                                  \
     do {                                                                  \
         cudaError_t e__ = (call);                                         \
@@ -173,10 +212,10 @@ unsigned int ranks_of(const mc_params& p) { return p.n_ranks ? p.n_ranks : 1u; }
 // Side lists for an fp32 problem (mc_select.cuh: SideLists); a failed allocation just leaves them off.
 void attach_side(mc_handle* h, SelectProblem& sp, SideBuf& buf) {
     sp.side = SideLists{};
-    if (sp.dtype != MC_F32 || sp.n == 0 || sp.rows == 0 || getenv("MC_NO_SIDE_LISTS")) return;
+    if (sp.dtype != MC_F32 || sp.n == 0 || sp.rows == 0 || h->no_side_lists) return;
     const unsigned long long chunks = select_chunks_f32(sp, h->dev.sm_count);
     unsigned int cap = side_list_cap(sp.n, chunks);
-    if (const char* e = getenv("MC_SIDE_CAP")) cap = (unsigned int)strtoul(e, nullptr, 10);     // tests: force overflows
+    if (h->side_cap_override >= 0) cap = (unsigned int)h->side_cap_override;                  // tests: force overflows
     if (cap == 0) return;
     if (buf.values.reserve(side_list_floats(sp.rows, chunks, cap)) != cudaSuccess ||
         buf.counts.reserve((size_t)sp.rows * chunks * SIDE_WARPS) != cudaSuccess ||
@@ -208,13 +247,14 @@ int validate(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const voi
     if (p->shock < 0 || p->shock > MC_SHOCK_INJECTED) return fail(h, MC_ERR_INVALID, "bad shock mode");
     if (p->var_model != MC_VAR_GARCH && p->var_model != MC_VAR_CONST) return fail(h, MC_ERR_INVALID, "bad var model");
     if (p->n_assets < 1 || p->n_assets > MC_MAX_ASSETS) return fail(h, MC_ERR_INVALID, "n_assets out of range");
-    if (p->n_assets > 1 && (!pf || !pf->h_chol || !pf->h_sigma_step || !pf->h_drift_step || !pf->h_s0 || !pf->h_weights))
+    if (!(p->flags & MC_FLAG_TERMINAL_GIVEN) && p->n_assets > 1 && (!pf || !pf->h_chol || !pf->h_sigma_step || !pf->h_drift_step || !pf->h_s0 || !pf->h_weights))
         return fail(h, MC_ERR_INVALID, "portfolio description missing");
     if (p->n_assets > 1 && (p->shock == MC_SHOCK_BOOTSTRAP || p->var_model != MC_VAR_CONST))
         return fail(h, MC_ERR_INVALID, "portfolio mode supports normal/injected shocks with constant variance");
-    if (p->shock == MC_SHOCK_BOOTSTRAP && (!d_pool || p->pool_len == 0))
+    const bool simulates = !(p->flags & MC_FLAG_TERMINAL_GIVEN);
+    if (simulates && p->shock == MC_SHOCK_BOOTSTRAP && (!d_pool || p->pool_len == 0))
         return fail(h, MC_ERR_INVALID, "bootstrap needs a pool");
-    if (p->shock == MC_SHOCK_INJECTED && !d_shocks) return fail(h, MC_ERR_INVALID, "injected shocks missing");
+    if (simulates && p->shock == MC_SHOCK_INJECTED && !d_shocks) return fail(h, MC_ERR_INVALID, "injected shocks missing");
     if (!d_terminal && p->n_paths) return fail(h, MC_ERR_INVALID, "d_terminal is NULL");
     if ((p->flags & MC_FLAG_STORE_PATHS) && !d_paths && p->n_paths) return fail(h, MC_ERR_INVALID, "d_paths is NULL");
     if ((p->flags & MC_FLAG_FAN_CHART) && !(p->flags & MC_FLAG_STORE_PATHS))
@@ -223,6 +263,8 @@ int validate(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const voi
     if (p->n_pcts > MC_MAX_PCTS || p->n_path_pcts > MC_MAX_PATH_PCTS) return fail(h, MC_ERR_INVALID, "too many percentiles");
     if (p->hist_bins > (1u << 16)) return fail(h, MC_ERR_INVALID, "hist_bins > 65536");
     if (!(p->var0 >= 0.0) || !(p->s0 == p->s0)) return fail(h, MC_ERR_INVALID, "var0 must be >= 0");
+    if ((p->flags & MC_FLAG_TERMINAL_GIVEN) && (p->flags & (MC_FLAG_STORE_PATHS | MC_FLAG_FAN_CHART)))
+        return fail(h, MC_ERR_INVALID, "MC_FLAG_TERMINAL_GIVEN reduces terminal values only");
     return MC_OK;
 }
 
@@ -280,6 +322,218 @@ int select_rows(mc_handle* h, const void* d_x, int dtype, uint64_t rows, uint64_
     return MC_OK;
 }
 
+// ------------------------------------------------------------------ fused closing: host side
+constexpr unsigned int PEER_CAND_BYTES = 4u << 20;        // per rank, fixed once peers are attached
+
+bool fused_eligible(const mc_params& p) {
+    if (p.flags & (MC_FLAG_FAN_CHART | MC_FLAG_PATHS_VOLATILE | MC_FLAG_TERMINAL_GIVEN)) return false;
+    if (p.hist_bins && (!(p.hist_lo < p.hist_hi) || p.hist_bins > (unsigned)FUSED_MAX_NPH_BINS)) return false;   // range from the data: general path
+    if (ranks_of(p) > (unsigned)FUSED_MAX_RANKS) return false;
+    return true;
+}
+
+// The window of terminal values the key histogram resolves: s0 e^(drift T) times e^(+-W spread), where spread is
+// the standard deviation of the log return the model itself implies.  Only its placement depends on this
+// estimate, never a result: values outside it land in the two open-ended end bins, and a target that falls
+// into an over-full bin sends the run to the general selection.
+KeyWindow key_window(const mc_params& p, const mc_portfolio* pf) {
+    const double T = (double)p.n_steps;
+    double lo_ln, hi_ln;
+    if (p.n_assets > 1 && pf) {
+        double smax = 0.0, dmin = INFINITY, dmax = -INFINITY;
+        for (unsigned i = 0; i < p.n_assets; ++i) {
+            smax = fmax(smax, fabs(pf->h_sigma_step[i]));
+            dmin = fmin(dmin, pf->h_drift_step[i]);
+            dmax = fmax(dmax, pf->h_drift_step[i] + 0.5 * pf->h_sigma_step[i] * pf->h_sigma_step[i]);
+        }
+        const double spread = smax * sqrt(T), c = log(fabs(p.s0) > 0 ? fabs(p.s0) : 1.0);
+        lo_ln = c + T * dmin - 6.5 * spread;
+        hi_ln = c + T * dmax + 6.5 * spread;
+    } else {
+        double total = 0.0;
+        if (p.var_model == MC_VAR_CONST) {
+            total = p.var0 * T;
+        } else {                                   // E v_{t+1} = omega + (alpha + beta) E v_t  (E z^2 ~ 1: app.py:609)
+            double v = p.var0;
+            const double phi = p.alpha + p.beta;
+            for (unsigned t = 0; t < p.n_steps; ++t) { total += v; v = p.omega + phi * v; if (!(v < 1e6)) v = 1e6; }
+        }
+        const double spread = sqrt(total > 0 ? total : 0.0), W = p.var_model == MC_VAR_CONST ? 6.5 : 8.0;
+        const double c = log(fabs(p.s0) > 0 ? fabs(p.s0) : 1.0) + T * p.drift;
+        lo_ln = c - W * spread;
+        hi_ln = c + W * spread;
+    }
+    if (!(lo_ln == lo_ln) || !(hi_ln == hi_ln)) { lo_ln = -80.0; hi_ln = 80.0; }
+    lo_ln = fmax(lo_ln, -80.0); hi_ln = fmin(hi_ln, 80.0);
+    if (hi_ln < lo_ln) hi_ln = lo_ln;
+    const double lo = exp(lo_ln), hi = exp(hi_ln);
+    return p.dtype == MC_F64 ? make_window(key32_of(lo), key32_of(hi)) : make_window(key32_of((float)lo), key32_of((float)hi));
+}
+
+// (re)allocate this handle's exchange buffer; once peers are attached it must not move
+int ensure_xchg(mc_handle* h, unsigned int n_ranks, unsigned int cand_bytes) {
+    if (h->xchg.p && h->lay.n_ranks >= n_ranks && h->lay.cand_bytes >= cand_bytes) return MC_OK;
+    if (h->peers_attached) return fail(h, MC_ERR_STATE, "exchange buffer is attached to peers and cannot grow");
+    const XchgLayout L = xchg_layout(n_ranks, cand_bytes);
+    MC_CUDA(h, h->xchg.reserve(L.total));
+    MC_CUDA(h, cudaMemset(h->xchg.p, 0, L.total));
+    h->lay = L;
+    h->peers = Peers{};
+    h->peers.base[0] = h->xchg.p;
+    h->peers.n_ranks = 1; h->peers.me = 0; h->peers.seq = 0;
+    h->fused_dirty = true;
+    return MC_OK;
+}
+
+// workspace of the fused closing for up to `bins` histogram bins (allocations may wait for the device: a sharded
+// run must find everything in place, so mc_peer_export reserves for the largest request)
+int fused_reserve(mc_handle* h, unsigned int bins) {
+    MC_CUDA(h, h->fplan.reserve(1));
+    MC_CUDA(h, h->member.reserve(FUSED_KB));
+    MC_CUDA(h, h->close_partials.reserve(8 * (size_t)h->dev.sm_count + 8));
+    MC_CUDA(h, h->claim.reserve(1));
+    MC_CUDA(h, h->h_stage.reserve(sizeof(DeviceResult) + (size_t)bins * 8));
+    if (bins) {
+        const double* before = h->edges.p;
+        MC_CUDA(h, h->edges.reserve(2 * ((size_t)bins + 2)));
+        if (h->edges.p != before) h->edges_bins = 0;
+        MC_CUDA(h, h->hist_total.reserve(bins));
+    }
+    return MC_OK;
+}
+
+// enqueue a whole run with the fused closing; the result is read later by fused_fetch
+int fused_enqueue(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void* d_pool, const void* d_shocks,
+                  void* d_paths, void* d_terminal, bool sharded, cudaStream_t s) {
+    int rc = validate(h, p, pf, d_pool, d_shocks, d_paths, d_terminal);
+    if (rc) return rc;
+    MC_DEVICE(h);
+    const unsigned int R = ranks_of(*p);
+    if (sharded) {
+        if (!h->peers_attached || h->peers.n_ranks != R) return fail(h, MC_ERR_STATE, "mc_run_sharded: peers not attached for this many ranks");
+    } else {
+        if (R != 1) return fail(h, MC_ERR_INVALID, "single-rank call with n_ranks > 1");
+        if (h->peers_attached && h->peers.n_ranks != 1) return fail(h, MC_ERR_STATE, "handle is attached to peers: use mc_run_sharded");
+        unsigned long long want = p->n_paths * (p->dtype == MC_F64 ? 8ull : 4ull) / 8ull;
+        if (want < (1ull << 20)) want = 1ull << 20;
+        if (want > (1ull << 30)) want = 1ull << 30;
+        want = (want + 255ull) & ~255ull;
+        if ((rc = ensure_xchg(h, 1, (unsigned int)want))) return rc;
+    }
+    h->active = false;
+    h->p = *p;
+    h->launches = 0;
+    h->has_t = p->n_pcts > 0 && !(p->flags & MC_FLAG_NO_TERMINAL_SELECT);
+    h->has_f = false;
+    h->tail_idx = -1;
+    h->d_terminal = d_terminal;
+    h->prob_t = SelectProblem{};
+    if (h->has_t) {
+        if (!build_select_plan(p->pcts, (int)p->n_pcts, p->n_paths_global, p->dtype, &h->prob_t.plan))
+            return fail(h, MC_ERR_INVALID, "percentiles must be ascending and within [0, 100]");
+        if (p->tail_pct >= 0.0) {
+            for (unsigned k = 0; k < p->n_pcts; ++k) if (p->pcts[k] == p->tail_pct) h->tail_idx = (int)k;
+            if (h->tail_idx < 0) return fail(h, MC_ERR_INVALID, "tail_pct must be one of pcts");
+        }
+    } else {
+        build_select_plan(nullptr, 0, p->n_paths_global, p->dtype, &h->prob_t.plan);
+    }
+    if ((rc = upload_plan(h, h->prob_t, 0, s))) return rc;
+    if ((rc = fused_reserve(h, p->hist_bins))) return rc;
+    if (p->hist_bins) {
+        if (h->edges_bins != p->hist_bins || h->edges_lo != p->hist_lo || h->edges_hi != p->hist_hi) {
+            MC_CUDA(h, launch_hist_edges(p->hist_bins, p->hist_lo, p->hist_hi, h->res.p, h->edges.p, s));
+            h->edges_bins = p->hist_bins; h->edges_lo = p->hist_lo; h->edges_hi = p->hist_hi;
+            h->launches += 1;
+        }
+    }
+    unsigned char* mine = h->peers.base[h->peers.me];
+    unsigned int* my_hist = reinterpret_cast<unsigned int*>(mine + h->lay.off_hist) + (size_t)h->peers.me * FUSED_KB;
+    unsigned int* my_nph = reinterpret_cast<unsigned int*>(mine + h->lay.off_nph) + (size_t)h->peers.me * FUSED_MAX_NPH_BINS;
+    if (h->fused_dirty) {          // normally the last block of the previous run left these at zero
+        MC_CUDA(h, cudaMemsetAsync(my_hist, 0, (size_t)FUSED_KB * 4, s));
+        MC_CUDA(h, cudaMemsetAsync(my_nph, 0, (size_t)FUSED_MAX_NPH_BINS * 4, s));
+        MC_CUDA(h, cudaMemsetAsync(h->claim.p, 0, sizeof(unsigned long long), s));
+    }
+    h->fused_dirty = true;         // until this run has been enqueued completely
+
+    FusedArgs fa{};
+    fa.x = d_terminal; fa.dtype = p->dtype; fa.n = p->n_paths; fa.center = p->s0;
+    fa.win = key_window(*p, pf);
+    fa.lay = h->lay;
+    fa.peers = h->peers;
+    if (sharded) fa.peers.seq = ++h->fused_seq;
+    fa.d_plan = h->prob_t.d_plan;
+    fa.n_targets = h->prob_t.plan.n_targets; fa.n_pcts = h->has_t ? (int)p->n_pcts : 0; fa.tail_idx = h->tail_idx;
+    fa.plan = h->fplan.p; fa.member = h->member.p; fa.partials = h->close_partials.p;
+    fa.nph_bins = p->hist_bins; fa.edges = h->edges.p; fa.hist_lo = p->hist_lo; fa.hist_hi = p->hist_hi;
+    fa.res = h->res.p; fa.hist_total = h->hist_total.p; fa.host_out = h->h_stage.p; fa.claim = h->claim.p;
+
+    SinkArgs sink{};
+    const bool in_sim = sim_takes_sink(*p) && p->n_paths > 0;
+    if (in_sim) {
+        sink.win = fa.win; sink.g_khist = my_hist; sink.claim = h->claim.p;
+        if (p->hist_bins && p->hist_bins <= (unsigned)FUSED_SINK_NPH_BINS) {
+            sink.g_nphist = my_nph; sink.nph_bins = p->hist_bins;
+            sink.nph_edges = reinterpret_cast<const float*>(h->edges.p + p->hist_bins + 1);
+            fa.nph_in_sim = 1;
+        }
+    }
+    MC_CUDA(h, cudaEventRecord(h->ev[0], s));
+    SimBuffers b{};
+    b.d_pool = d_pool; b.d_shocks = d_shocks; b.d_paths = d_paths; b.d_terminal = d_terminal;
+    b.d_partials = h->partials.p; b.d_lut = h->lut.p; b.sink = in_sim ? &sink : nullptr;
+    int grid = 0;
+    if (p->n_paths) {
+        MC_CUDA(h, launch_simulation(*p, pf, b, h->dev, &grid, s));
+        h->launches += 1;
+    }
+    MC_CUDA(h, cudaEventRecord(h->ev[1], s));
+    if (!in_sim && p->n_paths) {
+        MC_CUDA(h, launch_terminal_hist(fa, h->dev.sm_count, s));
+        h->launches += 1;
+    }
+    MC_CUDA(h, launch_fused_plan(fa, s));
+    MC_CUDA(h, launch_fused_closing(fa, h->dev.sm_count, &grid, s));
+    MC_CUDA(h, launch_fused_select(fa, s));
+    h->launches += 3;
+    MC_CUDA(h, cudaEventRecord(h->ev[2], s));
+    h->fused_dirty = false;
+    h->fused_pending = true;
+    h->n_fused += 1;
+    return MC_OK;
+}
+
+// wait for the fused run and unpack the pinned result block; *status = FUSED_* of the run
+int fused_fetch(mc_handle* h, mc_result* r, uint64_t* h_hist, cudaStream_t s, int* status) {
+    MC_DEVICE(h);
+    MC_CUDA(h, cudaStreamSynchronize(s));
+    h->fused_pending = false;
+    const mc_params& p = h->p;
+    DeviceResult d;
+    memcpy(&d, h->h_stage.p, sizeof(d));
+    *status = (int)d.status;
+    h->last_fused_status = *status;
+    memset(r, 0, sizeof(*r));
+    r->n = d.n; r->n_above = d.n_above; r->mean = d.mean; r->std = d.std; r->min = d.vmin; r->max = d.vmax;
+    if (h->has_t) {
+        memcpy(r->pct, d.pct, sizeof(d.pct));
+        memcpy(r->pct_lo, d.pct_lo, sizeof(d.pct_lo));
+        memcpy(r->pct_hi, d.pct_hi, sizeof(d.pct_hi));
+    }
+    r->tail_count = d.tail_count; r->tail_sum = d.tail_sum;
+    r->hist_lo = d.hist_lo; r->hist_hi = d.hist_hi;
+    if (p.hist_bins && h_hist) memcpy(h_hist, h->h_stage.p + sizeof(DeviceResult), (size_t)p.hist_bins * 8);
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]) == cudaSuccess) r->sim_ms = ms;
+    if (cudaEventElapsedTime(&ms, h->ev[0], h->ev[2]) == cudaSuccess) r->total_ms = ms;
+    r->launches = h->launches;
+    r->status = (uint32_t)*status;
+    if (*status != FUSED_OK) { h->n_fused_fallback += 1; h->fused_dirty = true; }
+    if (*status == FUSED_PEER_TIMEOUT) return fail(h, MC_ERR_STATE, "a peer rank never delivered its part of the exchange (20 s)");
+    return MC_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -299,7 +553,8 @@ int mc_create(int device_ordinal, mc_handle** out) {
     if (!h) return fail(nullptr, MC_ERR_INVALID, "out of host memory");
     h->device = device_ordinal;
     cudaDeviceProp prop{};
-    if ((e = cudaSetDevice(device_ordinal)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, device_ordinal)) != cudaSuccess) {
+    DeviceGuard guard(device_ordinal);
+    if ((e = guard.ok ? cudaSuccess : cudaErrorInvalidDevice) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, device_ordinal)) != cudaSuccess) {
         delete h;
         return cuda_fail(nullptr, e, "cudaGetDeviceProperties");
     }
@@ -330,11 +585,13 @@ int mc_create(int device_ordinal, mc_handle** out) {
 
 int mc_destroy(mc_handle* h) {
     if (!h) return MC_OK;
-    cudaSetDevice(h->device);
+    DeviceGuard guard(h->device);
     h->partials.release(); h->lut.release(); h->res.release(); h->plans.release(); h->states_t.release(); h->states_f.release(); h->scratch_t.release(); h->scratch_f.release();
     h->pct_t.release(); h->fan.release(); h->tail_scratch.release(); h->edges.release(); h->hist_total.release();
     h->batch_pct.release(); h->batch_res.release(); h->side_t.release(); h->side_f.release();
     h->side_blocks.release(); h->h_side_blocks.release();
+    for (void* q : h->ipc_opened) cudaIpcCloseMemHandle(q);
+    h->xchg.release(); h->fplan.release(); h->member.release(); h->close_partials.release(); h->claim.release();
     h->stage.release(); h->h_stage.release(); h->pending.release(); h->h_pending.release();
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->ev_pending) cudaEventDestroy(h->ev_pending);
@@ -363,8 +620,9 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
                               uint64_t cap_words, cudaStream_t s) {
     int rc = validate(h, p, pf, d_pool, d_shocks, d_paths, d_terminal);
     if (rc) return rc;
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
     h->active = false;
+    h->fused_pending = false;
     h->p = *p;
     h->launches = 0;
     h->phase = 0;
@@ -406,6 +664,7 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
     if (p->hist_bins) {
         MC_CUDA(h, h->edges.reserve(2 * ((size_t)p->hist_bins + 2)));
         MC_CUDA(h, h->hist_total.reserve(p->hist_bins));
+        h->edges_bins = 0;                   // the closing stage writes its own edges: the fused path's cache is gone
     }
     const Stage0Layout L = layout_stage0(h);
     if (!d_stage_out || cap_words < (uint64_t)mc_stage_max_words(p))
@@ -417,8 +676,9 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
     b.d_pool = d_pool; b.d_shocks = d_shocks; b.d_paths = d_paths; b.d_terminal = d_terminal;
     b.d_partials = h->partials.p;
     b.d_lut = h->lut.p;
+    b.sink = nullptr;
     h->sim_buffers = b;
-    h->has_pf = p->n_assets > 1 && pf;
+    h->has_pf = p->n_assets > 1 && pf && !(p->flags & MC_FLAG_TERMINAL_GIVEN);
     if (h->has_pf) {
         const size_t d = p->n_assets;
         h->pf_chol.assign(pf->h_chol, pf->h_chol + d * d);
@@ -428,7 +688,10 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
         h->pf_w.assign(pf->h_weights, pf->h_weights + d);
     }
     int grid = 0;
-    if (p->n_paths) {
+    if (p->n_paths && (p->flags & MC_FLAG_TERMINAL_GIVEN)) {
+        MC_CUDA(h, launch_terminal_partials(d_terminal, p->dtype, p->n_paths, p->s0, h->partials.p, h->dev.sm_count, &grid, s));
+        h->launches += 1;
+    } else if (p->n_paths) {
         MC_CUDA(h, launch_simulation(*p, pf, b, h->dev, &grid, s));
         h->launches += 1;
     }
@@ -524,7 +787,7 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
     if (!h->active) return fail(h, MC_ERR_STATE, "mc_stage_next without mc_stage_begin");
     if (!d_gathered || !d_stage_out || n_ranks == 0 || !done) return fail(h, MC_ERR_INVALID, "bad stage arguments");
     if (n_ranks != ranks_of(h->p)) return fail(h, MC_ERR_INVALID, "n_ranks differs from mc_params.n_ranks");
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
     const unsigned long long* g = static_cast<const unsigned long long*>(d_gathered);
     unsigned long long* out = static_cast<unsigned long long*>(d_stage_out);
     const mc_params& p = h->p;
@@ -591,7 +854,7 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
 static int fetch_locked(mc_handle* h, mc_result* r, uint64_t* h_hist, double* h_fan, cudaStream_t s) {
     if (h->active) return fail(h, MC_ERR_STATE, "stages not finished");
     if (!r) return fail(h, MC_ERR_INVALID, "h_result is NULL");
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
     const mc_params& p = h->p;
     const size_t fan_n = h->has_f ? ((size_t)p.n_steps + 1) * p.n_path_pcts : 0;
     const size_t bytes = sizeof(DeviceResult) + (size_t)p.hist_bins * 8 + fan_n * 8;
@@ -673,7 +936,7 @@ int mc_stage_reads_paths(mc_handle* h) {
     if (h->p.flags & MC_FLAG_PATHS_VOLATILE) return 0;        // later passes: the handle restores the rows itself
     if (h->phase == 1) return h->pass_idx < 2 ? 1 : 0;        // scan, then pass 2 -- or the closing stage
     if (h->pending_unchecked) {                               // final stage, unless rows are still undecided
-        MC_CUDA(h, cudaSetDevice(h->device));
+        MC_DEVICE(h);
         MC_CUDA(h, cudaEventSynchronize(h->ev_pending));
         return *h->h_pending.p != 0 ? 1 : 0;
     }
@@ -684,14 +947,104 @@ int mc_stage_resimulate(mc_handle* h, void* stream) {
     if (!h) return MC_ERR_INVALID;
     std::lock_guard<std::mutex> lock(h->mu);
     if (!h->active) return fail(h, MC_ERR_STATE, "no staged run in flight");
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
     return resimulate_locked(h, static_cast<cudaStream_t>(stream));
 }
 
 int mc_fetch_result(mc_handle* h, mc_result* r, uint64_t* h_hist, double* h_fan, void* stream) {
     if (!h) return MC_ERR_INVALID;
     std::lock_guard<std::mutex> lock(h->mu);
+    if (h->fused_pending) {
+        if (!r) return fail(h, MC_ERR_INVALID, "h_result is NULL");
+        int status = 0;
+        return fused_fetch(h, r, h_hist, static_cast<cudaStream_t>(stream), &status);
+    }
     return fetch_locked(h, r, h_hist, h_fan, static_cast<cudaStream_t>(stream));
+}
+
+int mc_run_sharded(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void* d_pool, const void* d_shocks,
+                   void* d_paths, void* d_terminal, void* stream) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (!p) return fail(h, MC_ERR_INVALID, "params is NULL");
+    if (!fused_eligible(*p)) return fail(h, MC_ERR_INVALID, "mc_run_sharded: this request needs the staged protocol (fan chart, data-dependent histogram range)");
+    return fused_enqueue(h, p, pf, d_pool, d_shocks, d_paths, d_terminal, true, static_cast<cudaStream_t>(stream));
+}
+
+int mc_peer_export(mc_handle* h, uint32_t n_ranks, void* out_ipc_handle, void** out_local_ptr, uint64_t* out_bytes) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (n_ranks < 1 || n_ranks > (uint32_t)FUSED_MAX_RANKS) return fail(h, MC_ERR_INVALID, "mc_peer_export: 1..16 ranks");
+    if (h->peers_attached) return fail(h, MC_ERR_STATE, "mc_peer_export: already attached");
+    MC_DEVICE(h);
+    h->xchg.release();                       // a fresh allocation: its IPC handle names exactly this buffer
+    h->lay = XchgLayout{};
+    int rc = ensure_xchg(h, n_ranks, PEER_CAND_BYTES);
+    if (rc) return rc;
+    if ((rc = fused_reserve(h, FUSED_MAX_NPH_BINS))) return rc;
+    h->edges_bins = 0;                       // the edge buffer may have moved
+    MC_CUDA(h, cudaDeviceSynchronize());
+    if (out_ipc_handle) {
+        cudaIpcMemHandle_t ih;
+        MC_CUDA(h, cudaIpcGetMemHandle(&ih, h->xchg.p));
+        static_assert(sizeof(ih) == 64, "cudaIpcMemHandle_t is 64 bytes");
+        memcpy(out_ipc_handle, &ih, sizeof(ih));
+    }
+    if (out_local_ptr) *out_local_ptr = h->xchg.p;
+    if (out_bytes) *out_bytes = h->lay.total;
+    return MC_OK;
+}
+
+int mc_peer_attach(mc_handle* h, uint32_t rank, uint32_t n_ranks, const void* ipc_handles, void* const* local_ptrs) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (!h->xchg.p || h->lay.n_ranks != n_ranks || rank >= n_ranks) return fail(h, MC_ERR_STATE, "mc_peer_attach: call mc_peer_export(n_ranks) first");
+    if (h->peers_attached) return fail(h, MC_ERR_STATE, "mc_peer_attach: already attached");
+    if (!ipc_handles && !local_ptrs) return fail(h, MC_ERR_INVALID, "mc_peer_attach: no peer buffers given");
+    MC_DEVICE(h);
+    Peers P{};
+    P.n_ranks = n_ranks; P.me = rank; P.seq = 0;
+    for (uint32_t r = 0; r < n_ranks; ++r) {
+        if (r == rank) { P.base[r] = h->xchg.p; continue; }
+        if (local_ptrs) { P.base[r] = static_cast<unsigned char*>(local_ptrs[r]); continue; }
+        cudaIpcMemHandle_t ih;
+        memcpy(&ih, static_cast<const unsigned char*>(ipc_handles) + 64 * (size_t)r, 64);
+        void* q = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&q, ih, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            for (void* o : h->ipc_opened) cudaIpcCloseMemHandle(o);
+            h->ipc_opened.clear();
+            return cuda_fail(h, e, "cudaIpcOpenMemHandle");
+        }
+        h->ipc_opened.push_back(q);
+        P.base[r] = static_cast<unsigned char*>(q);
+    }
+    h->peers = P;
+    h->peers_attached = true;
+    h->fused_seq = 0;
+    h->fused_dirty = true;
+    return MC_OK;
+}
+
+int mc_debug_set_tuning(mc_handle* h, int side_cap, int no_side_lists, int waves, int nblock) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    h->side_cap_override = side_cap;
+    h->no_side_lists = no_side_lists != 0;
+    set_sim_tuning(waves, nblock);
+    return MC_OK;
+}
+
+int64_t mc_debug_counter(mc_handle* h, int which) {
+    if (!h) return -1;
+    std::lock_guard<std::mutex> lock(h->mu);
+    switch (which) {
+        case 0: return (int64_t)h->n_fused;
+        case 1: return (int64_t)h->n_fused_fallback;
+        case 2: return (int64_t)h->last_fused_status;
+        case 3: return (int64_t)h->resimulations;
+        default: return -1;
+    }
 }
 
 int mc_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void* d_pool, const void* d_shocks,
@@ -703,7 +1056,22 @@ int mc_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void*
     if (p->struct_size != sizeof(mc_params)) return fail(h, MC_ERR_VERSION, "mc_params struct_size mismatch");
     if (p->n_paths != p->n_paths_global || p->path_offset + p->n_paths < p->n_paths || p->n_ranks > 1)
         return fail(h, MC_ERR_INVALID, "mc_run is single-rank: n_paths must equal n_paths_global");
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
+    mc_params generic = *p;
+    if (fused_eligible(*p) && !(h->peers_attached && h->peers.n_ranks != 1)) {
+        if (!h_result) return fail(h, MC_ERR_INVALID, "h_result is NULL");
+        int rc = fused_enqueue(h, p, pf, d_pool, d_shocks, d_paths, d_terminal, false, s);
+        if (rc) return rc;
+        int status = 0;
+        if ((rc = fused_fetch(h, h_result, h_hist, s, &status))) return rc;
+        if (status == FUSED_OK) return MC_OK;
+        // the window missed or a bin was too full: the terminal values are there, reduce them the general way
+        generic.flags |= MC_FLAG_TERMINAL_GIVEN;
+        generic.flags &= ~(uint32_t)MC_FLAG_STORE_PATHS;
+    }
+    p = &generic;
+    const float fused_sim_ms = (generic.flags & MC_FLAG_TERMINAL_GIVEN) ? h_result->sim_ms : 0.f;
+    const unsigned fused_launches = (generic.flags & MC_FLAG_TERMINAL_GIVEN) ? h->launches : 0u;
     const size_t cap = (size_t)mc_stage_max_words(p);
     MC_CUDA(h, h->stage.reserve(cap));
     int rc = stage_begin_locked(h, p, pf, d_pool, d_shocks, d_paths, d_terminal, h->stage.p, cap, s);
@@ -713,7 +1081,12 @@ int mc_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void*
         rc = stage_next_locked(h, h->stage.p, 1, h->stage.p, &done, s);
         if (rc) return rc;
     }
-    return fetch_locked(h, h_result, h_hist, h_fan, s);
+    rc = fetch_locked(h, h_result, h_hist, h_fan, s);
+    if (rc == MC_OK && (generic.flags & MC_FLAG_TERMINAL_GIVEN)) {
+        h_result->sim_ms = fused_sim_ms;
+        h_result->launches += fused_launches;
+    }
+    return rc;
 }
 
 int mc_debug_shocks(mc_handle* h, const mc_params* p, const void* d_pool, void* d_out, void* stream) {
@@ -721,7 +1094,7 @@ int mc_debug_shocks(mc_handle* h, const mc_params* p, const void* d_pool, void* 
     std::lock_guard<std::mutex> lock(h->mu);
     if (!p || p->struct_size != sizeof(mc_params)) return fail(h, MC_ERR_VERSION, "mc_params mismatch");
     if (p->shock == MC_SHOCK_BOOTSTRAP && !d_pool) return fail(h, MC_ERR_INVALID, "pool missing");
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
     MC_CUDA(h, launch_debug_shocks(*p, d_pool, h->lut.p, d_out, static_cast<cudaStream_t>(stream)));
     return MC_OK;
 }
@@ -730,7 +1103,7 @@ int mc_debug_philox(mc_handle* h, const uint32_t* d_ctr, uint32_t n, uint32_t ke
                     void* stream) {
     if (!h) return MC_ERR_INVALID;
     std::lock_guard<std::mutex> lock(h->mu);
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
     MC_CUDA(h, launch_debug_philox(d_ctr, n, key0, key1, d_out, static_cast<cudaStream_t>(stream)));
     return MC_OK;
 }
@@ -744,7 +1117,7 @@ int mc_percentiles(mc_handle* h, const void* d_x, int32_t dtype, uint64_t rows, 
         (dtype != MC_F32 && dtype != MC_F64))
         return fail(h, MC_ERR_INVALID, "bad mc_percentiles arguments");
     if (h->active) return fail(h, MC_ERR_STATE, "a staged run is in flight on this handle");
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
     MC_CUDA(h, h->fan.reserve(rows * n_pcts));
     int rc = select_rows(h, d_x, dtype, rows, n, ld, pcts, n_pcts, false, h->fan.p, nullptr, nullptr, nullptr, s);
     if (rc) return rc;
@@ -762,8 +1135,9 @@ int mc_histogram(mc_handle* h, const void* d_x, int32_t dtype, uint64_t n, uint3
         (dtype != MC_F32 && dtype != MC_F64))
         return fail(h, MC_ERR_INVALID, "bad mc_histogram arguments (explicit lo < hi required)");
     if (h->active) return fail(h, MC_ERR_STATE, "a staged run is in flight on this handle");
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
     MC_CUDA(h, h->edges.reserve(2 * ((size_t)bins + 2)));
+    h->edges_bins = 0;
     MC_CUDA(h, h->stage.reserve(2 + (size_t)bins));
     MC_CUDA(h, launch_tail_hist(d_x, dtype, n, false, bins, lo, hi, h->res.p, h->edges.p, h->tail_scratch.p,
                                 h->stage.p, h->dev.sm_count, s));
@@ -783,7 +1157,7 @@ int mc_prepare_inputs(mc_handle* h, const double* d_close, const uint32_t* d_len
     const uint32_t start = first_row > 20u ? first_row : 20u;
     if (n_obs > start && pool_ld < (uint64_t)(n_obs - start))
         return fail(h, MC_ERR_INVALID, "mc_prepare_inputs: pool_ld < n_obs - max(first_row, 20)");
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
     MC_CUDA(h, launch_prepare_inputs(d_close, d_lengths, n_series, n_obs, close_ld, first_row, pool_dtype, d_pool, pool_ld,
                                      d_inputs, static_cast<cudaStream_t>(stream)));
     return MC_OK;
@@ -795,7 +1169,7 @@ int mc_calibrate_garch(mc_handle* h, const double* d_pool, uint64_t pool_ld, con
     std::lock_guard<std::mutex> lock(h->mu);
     if (n_series && (!d_pool || !d_inputs || !d_fit)) return fail(h, MC_ERR_INVALID, "mc_calibrate_garch: NULL buffer");
     if (levels < 1 || levels > 16) return fail(h, MC_ERR_INVALID, "mc_calibrate_garch: levels must be 1..16");
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
     MC_CUDA(h, launch_calibrate_garch(d_pool, pool_ld, d_inputs, n_series, min_history, levels, d_fit,
                                       static_cast<cudaStream_t>(stream)));
     return MC_OK;
@@ -824,7 +1198,7 @@ int mc_run_batch(mc_handle* h, const mc_batch_params* p, const void* d_pool, uin
         for (unsigned k = 0; k < p->n_pcts; ++k) if (p->pcts[k] == p->tail_pct) tail_idx = (int)k;
         if (tail_idx < 0) return fail(h, MC_ERR_INVALID, "tail_pct must be one of pcts");
     }
-    MC_CUDA(h, cudaSetDevice(h->device));
+    MC_DEVICE(h);
     const size_t B = p->n_series, np = p->n_pcts ? p->n_pcts : 1;
     MC_CUDA(h, h->batch_pct.reserve(3 * B * np));
     MC_CUDA(h, h->batch_res.reserve(B));
@@ -878,7 +1252,7 @@ int mc_run_batch(mc_handle* h, const mc_batch_params* p, const void* d_pool, uin
     MC_CUDA(h, cudaEventElapsedTime(&total_ms, h->ev[0], h->ev[2]));
     for (size_t b = 0; b < B; ++b) {
         h_results[b].sim_ms = sim_ms; h_results[b].total_ms = total_ms;
-        h_results[b].launches = launches; h_results[b].reserved = 0;
+        h_results[b].launches = launches; h_results[b].status = 0;
     }
     return MC_OK;
 }

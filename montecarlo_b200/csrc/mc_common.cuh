@@ -87,7 +87,16 @@ struct DeviceResult {
     double tail_sum;
     double hist_lo, hist_hi;
     double center;        // s0: moments are accumulated about it
+    unsigned long long status;   // fused closing (mc_fused.cuh): 0 ok, else the reductions must be redone by the staged selection
 };
+
+// numpy/lib/_function_base_impl.py:_lerp -- explicit _rn ops: no FMA contraction, bit-identical to np.percentile
+__device__ __forceinline__ double numpy_lerp(double a, double b, double t) {
+    const double diff = __dsub_rn(b, a);
+    double r = __dadd_rn(a, __dmul_rn(diff, t));
+    if (t >= 0.5) r = __dsub_rn(b, __dmul_rn(diff, __dsub_rn(1.0, t)));
+    return r;
+}
 
 // ---- exact selection by interval narrowing ------------------------------------------
 // One SelectPlan per problem (terminal values, or the rows of the stored paths).

@@ -1229,14 +1229,6 @@ cudaError_t launch_select_scan(const SelectProblem& sp, const void* d_gathered_p
 }
 
 // ------------------------------------------------------------------ finish: keys -> values -> percentiles
-__device__ __forceinline__ double numpy_lerp(double a, double b, double t) {
-    // numpy/lib/_function_base_impl.py:_lerp -- explicit _rn ops: no FMA contraction
-    const double diff = __dsub_rn(b, a);
-    double r = __dadd_rn(a, __dmul_rn(diff, t));
-    if (t >= 0.5) r = __dsub_rn(b, __dmul_rn(diff, __dsub_rn(1.0, t)));
-    return r;
-}
-
 __global__ void select_finish_kernel(const SelectPlan* __restrict__ plan, const RowSel* __restrict__ states,
                                      unsigned long long rows, double* __restrict__ out, double* __restrict__ out_lo,
                                      double* __restrict__ out_hi) {
@@ -1429,6 +1421,12 @@ __global__ void __launch_bounds__(256) tail_reduce_kernel(const double* scratch,
         __syncthreads();
     }
     if (threadIdx.x == 0) { words[0] = s_cnt[0]; words[1] = (unsigned long long)__double_as_longlong(s_sum[0]); }
+}
+
+cudaError_t launch_hist_edges(unsigned int bins, double lo, double hi, DeviceResult* d_res, double* d_edges, cudaStream_t s) {
+    if (!bins) return cudaSuccess;
+    hist_edges_kernel<<<(bins + 256) / 256, 256, 0, s>>>(bins, lo, hi, d_res, d_edges, reinterpret_cast<float*>(d_edges + bins + 1));
+    return cudaGetLastError();
 }
 
 cudaError_t launch_tail_hist(const void* x, int dtype, unsigned long long n, bool want_tail, unsigned int bins,

@@ -19,7 +19,7 @@
 // pre-multiplies drift, omega and var0 by log2(e) or its square; GARCH is
 // homogeneous so the recursion is unchanged) so that price = s0 * ex2(y) is a
 // single MUFU.EX2.  The fp64 kernels work in natural units with exp().
-#include <cstdlib>
+#include <atomic>
 
 #include "mc_launch.cuh"
 #include "mc_rng.cuh"
@@ -551,6 +551,12 @@ static SimArgs<Real> make_args(const mc_params& p, const SimBuffers& b) {
     return a;
 }
 
+static std::atomic<int> g_tune_waves{24}, g_tune_nblock{512};
+void set_sim_tuning(int waves, int nblock) {
+    g_tune_waves.store(waves >= 1 ? waves : 24);
+    g_tune_nblock.store((nblock == 128 || nblock == 256 || nblock == 512) ? nblock : 512);
+}
+
 template <typename Kernel>
 static cudaError_t pick_grid(Kernel kernel, int block, size_t smem, const DeviceInfo& dev,
                              unsigned long long n, int* grid) {
@@ -568,7 +574,7 @@ static cudaError_t pick_grid(Kernel kernel, int block, size_t smem, const Device
         // More blocks than fit at once: let the hardware block scheduler balance the load.  Warps of a
         // resident block do not finish together (the issue arbiter is not fair), so a persistent grid
         // drains unevenly; ~24 waves of short blocks keep every SM full until the last few percent.
-        static const unsigned long long waves = getenv("MC_WAVES") ? strtoull(getenv("MC_WAVES"), nullptr, 10) : 24ull;
+        const unsigned long long waves = (unsigned long long)g_tune_waves.load();
         unsigned long long per_thread = n / ((unsigned long long)block * resident * waves);
         if (per_thread < 1) per_thread = 1;
         g = (n + block * per_thread - 1) / (block * per_thread);
@@ -660,22 +666,41 @@ static Sim32Args make_args32(const mc_params& p, const SimBuffers& b) {
     a.sig = (float)(sqrt(p.var0) * LOG2E);
     a.center = p.s0;
     a.partials = b.d_partials;
+    if (b.sink && !(p.flags & MC_FLAG_STORE_PATHS)) a.sink = *b.sink;
     return a;
 }
 
-template <int SHOCK, int VAR, bool STORE, int V, int TAB>
+template <int SHOCK, int VAR, bool STORE, int V, int TAB, bool SINK = false>
 static cudaError_t launch32_t(Sim32Args& a, const DeviceInfo& dev, int* grid, cudaStream_t stream) {
-    auto kernel = sim32_kernel<SHOCK, VAR, STORE, V, TAB>;
+    auto kernel = sim32_kernel<SHOCK, VAR, STORE, V, TAB, SINK>;
     const unsigned long long items = (a.n_paths + V - 1) / V;      // threads' worth of work
     int block;
     size_t smem;
     if (SHOCK == MC_SHOCK_NORMAL) {
         smem = (size_t)DIR_COUNT * sizeof(float2);
-        static const int nb = getenv("MC_NBLOCK") ? atoi(getenv("MC_NBLOCK")) : 512;
-        block = items >= 512ull * dev.sm_count ? nb : 128;
+        block = items >= 512ull * dev.sm_count ? g_tune_nblock.load() : 128;
     } else {
         block = items >= 1024ull * dev.sm_count ? 1024 : 256;
         smem = TAB != TAB_GLOBAL ? ((size_t)a.pool_len << a.table_lc) * sizeof(float2) : 0;
+    }
+    if (SINK) {
+        // persistent blocks: as many as stay resident, their warps claim paths as they go
+        smem = (smem + 15) & ~(size_t)15;
+        a.sink.smem_off = (unsigned int)smem;
+        smem += sink_smem_bytes(a.sink.g_nphist ? a.sink.nph_bins : 0u);
+        cudaError_t e = ensure_dynamic_smem(kernel, smem);
+        if (e != cudaSuccess) return e;
+        int per_sm = 0;
+        if ((e = resident_blocks_per_sm(kernel, block, smem, &per_sm)) != cudaSuccess) return e;
+        if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+        const unsigned long long resident = (unsigned long long)dev.sm_count * per_sm;
+        a.sink.claim_paths = a.n_paths >= 16ull * resident * block ? 64u : 32u;
+        const unsigned long long warps = (a.n_paths + a.sink.claim_paths - 1) / a.sink.claim_paths;
+        unsigned long long need = (warps + block / 32 - 1) / (block / 32);
+        if (need < 1) need = 1;
+        *grid = (int)(need < resident ? need : resident);
+        kernel<<<*grid, block, smem, stream>>>(a);
+        return cudaGetLastError();
     }
     cudaError_t e = pick_grid(kernel, block, smem, dev, items, grid);
     if (e != cudaSuccess) return e;
@@ -685,7 +710,9 @@ static cudaError_t launch32_t(Sim32Args& a, const DeviceInfo& dev, int* grid, cu
 
 template <int SHOCK, int VAR, int TAB>
 static cudaError_t launch32_store(Sim32Args& a, const mc_params& p, const DeviceInfo& dev, int* grid, cudaStream_t s) {
-    if (!(p.flags & MC_FLAG_STORE_PATHS)) return launch32_t<SHOCK, VAR, false, 1, TAB>(a, dev, grid, s);
+    if (!(p.flags & MC_FLAG_STORE_PATHS))
+        return a.sink.g_khist ? launch32_t<SHOCK, VAR, false, 1, TAB, true>(a, dev, grid, s)
+                              : launch32_t<SHOCK, VAR, false, 1, TAB>(a, dev, grid, s);
     // 16-byte stores need rows and base pointers that keep every group of four paths aligned
     const bool vec = a.ld_paths % 4 == 0 && ((uintptr_t)a.paths & 15u) == 0 && ((uintptr_t)a.terminal & 15u) == 0 &&
                      a.n_paths >= 4;
@@ -707,7 +734,8 @@ static cudaError_t launch_sim32(const mc_params& p, const SimBuffers& b, const D
         return launch32_var<MC_SHOCK_NORMAL, TAB_SMEM>(a, p, dev, grid, s);
     }
     // bootstrap: widest replication (<= 8 copies: a half-warp's LDS.64 then rarely collides) that fits
-    const size_t budget = (size_t)dev.max_smem_optin - 4 * 1024;
+    const size_t budget = (size_t)dev.max_smem_optin - 4 * 1024 -
+                          (a.sink.g_khist ? sink_smem_bytes(a.sink.g_nphist ? a.sink.nph_bins : 0u) : 0);
     int lc = 3;
     while (lc >= 0 && ((size_t)p.pool_len << lc) * sizeof(float2) > budget) --lc;
     if (lc < 0) return launch32_var<MC_SHOCK_BOOTSTRAP, TAB_GLOBAL>(a, p, dev, grid, s);   // gather from global/L1
@@ -782,6 +810,11 @@ static cudaError_t launch_portfolio(const mc_params& p, const mc_portfolio& pf, 
     if (d <= 16) return launch_portfolio_d<Real, 16>(p, pf, b, dev, grid, s);
     if (d <= 32) return launch_portfolio_d<Real, 32>(p, pf, b, dev, grid, s);
     return cudaErrorInvalidValue;
+}
+
+bool sim_takes_sink(const mc_params& p) {
+    return p.n_assets == 1 && p.dtype == MC_F32 && !(p.flags & MC_FLAG_STORE_PATHS) &&
+           (p.shock == MC_SHOCK_NORMAL || (p.shock == MC_SHOCK_BOOTSTRAP && boot32_eligible(p)));
 }
 
 cudaError_t launch_simulation(const mc_params& p, const mc_portfolio* pf, const SimBuffers& b,

@@ -1,6 +1,7 @@
 // mc_sim.cuh -- launch interface of the path-stepping kernels (mc_sim.cu).
 #pragma once
 #include "mc_common.cuh"
+#include "mc_fused.cuh"
 
 namespace mc {
 
@@ -11,7 +12,16 @@ struct SimBuffers {
     void* d_terminal;
     BlockPartial* d_partials;     // [max_grid]
     const float2* d_lut;          // Box-Muller direction table (fp32 normal shocks), [4096]
+    const SinkArgs* sink;         // non-null: bin the terminal values inside the kernel (only if sim_takes_sink(p))
 };
+
+// true when the kernel launch_simulation picks for `p` can bin its terminal values itself (sim32_kernel<..., SINK>:
+// fp32, one asset, shocks generated on the device, no stored paths); it then leaves NO per-block moments behind
+bool sim_takes_sink(const mc_params& p);
+
+// Test / tuning knobs (mc_debug_set_tuning): waves of blocks per launch of the non-persistent kernels (>= 1),
+// threads per block of the fused GBM kernel (128, 256 or 512).  0 restores the default.  Process-wide.
+void set_sim_tuning(int waves, int nblock);
 
 constexpr int MAX_SIM_GRID = 1 << 16;     // per-block partials are reduced in fixed order afterwards
 

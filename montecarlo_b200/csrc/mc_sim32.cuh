@@ -29,6 +29,7 @@ struct Sim32Args {
     float s0, var0, omega, alpha, beta, drift, sig;   // kernel units (log2)
     double center;
     BlockPartial* partials;
+    SinkArgs sink;                 // SINK kernels only (mc_fused.cuh)
 };
 
 __device__ __forceinline__ float price_of(const Sim32Args& a, uint32_t steps_done, float y) {
@@ -100,10 +101,16 @@ __device__ __forceinline__ void advance(const Sim32Args& a, const u32x4& w, uint
 // V paths per thread: 1, or 4 consecutive paths whose prices leave as one 16-byte store per step
 // (a warp then writes 512 contiguous bytes of a time-major row: measured 6.0 TB/s against 4.4 TB/s
 // for 4-byte stores at the config-5 shape, profiles/r01/microbench2_sm100a_v3.txt).
-template <int SHOCK, int VAR, bool STORE, int V, int TAB>
+// SINK (runs without a fan chart, mc_fused.cuh): the block is persistent, its warps claim paths from a global
+// counter (warps of a block do not advance at the same pace -- the issue arbiter is not fair -- so a static
+// split would leave SMs idle at the end), and every terminal value is binned on the spot into a key histogram
+// and, optionally, the caller's fixed-bin histogram, both in shared memory: one shared atomic per PATH each,
+// flushed once per block.  Moments are then taken by the closing pass, not here.
+template <int SHOCK, int VAR, bool STORE, int V, int TAB, bool SINK>
 __global__ void __launch_bounds__(SHOCK == MC_SHOCK_NORMAL ? 512 : 1024) sim32_kernel(const __grid_constant__ Sim32Args a) {
+    static_assert(!SINK || (!STORE && V == 1), "the sink rides on the kernels that keep no paths");
     extern __shared__ __align__(16) unsigned char smem_dyn[];
-    __shared__ BlockPartial s_warp[32];
+    __shared__ BlockPartial s_warp[SINK ? 1 : 32];
     constexpr int K = SHOCK == MC_SHOCK_NORMAL ? 8 : 5;
     constexpr bool FUSED_SUM = SHOCK == MC_SHOCK_NORMAL && VAR == MC_VAR_CONST && !STORE;
 
@@ -123,7 +130,24 @@ __global__ void __launch_bounds__(SHOCK == MC_SHOCK_NORMAL ? 512 : 1024) sim32_k
         const uint32_t wrap = (uint32_t)(((unsigned long long)0x4B000000u << table_shift) & 0xFFFFFFFFull);
         table_base += (threadIdx.x & ((1u << lc) - 1u)) * 8u - (1u << table_shift) - wrap;
     }
+    unsigned int* s_kh = nullptr;          // SINK: key histogram [FUSED_KB], fixed-bin counts [nph], edges [nph + 1]
+    unsigned int* s_nph = nullptr;
+    float* s_edge = nullptr;
+    int nph = 0;
+    if constexpr (SINK) {
+        s_kh = reinterpret_cast<unsigned int*>(smem_dyn + a.sink.smem_off);
+        for (int i = threadIdx.x; i < FUSED_KB; i += blockDim.x) s_kh[i] = 0u;
+        nph = a.sink.g_nphist ? (int)a.sink.nph_bins : 0;
+        if (nph) {
+            s_nph = s_kh + FUSED_KB;
+            s_edge = reinterpret_cast<float*>(s_nph + nph);
+            for (int i = threadIdx.x; i < nph; i += blockDim.x) s_nph[i] = 0u;
+            for (int i = threadIdx.x; i <= nph; i += blockDim.x) s_edge[i] = a.sink.nph_edges[i];
+        }
+    }
     __syncthreads();
+    float h_lo = 0.0f, h_top = 0.0f, h_inv = 0.0f;
+    if (SINK && nph) { h_lo = s_edge[0]; h_top = s_edge[nph]; h_inv = (float)nph / (h_top - h_lo); }
 
     BlockPartial acc = empty_partial();
     const float sigr = (VAR == MC_VAR_CONST && !FUSED_SUM) ? a.sig * BM_RADIUS_SCALE_F
@@ -132,8 +156,7 @@ __global__ void __launch_bounds__(SHOCK == MC_SHOCK_NORMAL ? 512 : 1024) sim32_k
     const uint32_t n_full = a.n_steps / K;
     const int n_tail = (int)(a.n_steps - n_full * K);
 
-    for (unsigned long long i0 = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * V; i0 < a.n_paths;
-         i0 += stride) {
+    auto run_paths = [&](const unsigned long long i0) {       // the V paths i0 .. i0 + V - 1, all steps
         const bool full = V == 1 || i0 + V <= a.n_paths;          // all V paths of this thread exist
         float y[V], v[V];
 #pragma unroll
@@ -212,11 +235,44 @@ __global__ void __launch_bounds__(SHOCK == MC_SHOCK_NORMAL ? 512 : 1024) sim32_k
             for (int p = 0; p < V; ++p)
                 if (i0 + p < a.n_paths) a.terminal[i0 + p] = fin[p];
         }
+        if constexpr (SINK) {
+            atomicAdd(&s_kh[window_bin(a.sink.win, key_of(fin[0]))], 1u);
+            if (nph) {
+                const int b = np_hist_bin<float>(fin[0], s_edge, nph, h_lo, h_top, h_inv);
+                if (b >= 0) atomicAdd(&s_nph[b], 1u);
+            }
+        } else {
 #pragma unroll
-        for (int p = 0; p < V; ++p)
-            if (i0 + p < a.n_paths) account<float>(acc, fin[p], a.center);
+            for (int p = 0; p < V; ++p)
+                if (i0 + p < a.n_paths) account<float>(acc, fin[p], a.center);
+        }
+    };
+    if constexpr (SINK) {
+        const unsigned int lane = threadIdx.x & 31u;
+        // the claim of the NEXT batch is in flight while this one is simulated: the atomic's round trip is never waited for
+        unsigned long long next = 0ull;
+        if (lane == 0u) next = atomicAdd(a.sink.claim, (unsigned long long)a.sink.claim_paths);
+        for (;;) {
+            const unsigned long long base = __shfl_sync(0xffffffffu, next, 0);
+            if (base >= a.n_paths) break;
+            if (lane == 0u) next = atomicAdd(a.sink.claim, (unsigned long long)a.sink.claim_paths);
+            const unsigned long long lim = base + a.sink.claim_paths < a.n_paths ? base + a.sink.claim_paths : a.n_paths;
+            for (unsigned long long i0 = base + lane; i0 < lim; i0 += 32ull) run_paths(i0);
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < FUSED_KB; i += blockDim.x) {
+            const unsigned int c = s_kh[i];
+            if (c) atomicAdd(&a.sink.g_khist[i], c);
+        }
+        for (int i = threadIdx.x; i < nph; i += blockDim.x) {
+            const unsigned int c = s_nph[i];
+            if (c) atomicAdd(&a.sink.g_nphist[i], c);
+        }
+    } else {
+        for (unsigned long long i0 = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * V; i0 < a.n_paths; i0 += stride)
+            run_paths(i0);
+        finish_block(acc, s_warp, a.partials);
     }
-    finish_block(acc, s_warp, a.partials);
 }
 
 // (cos, sin) of the 4096 Box-Muller directions, rounded once from fp64

@@ -131,14 +131,16 @@ class Engine:
         self.device_index = torch.cuda.current_device() if device is None else int(device)
         self.device = torch.device("cuda", self.device_index)
         h = C.c_void_p()
-        rc = self.lib.mc_create(self.device_index, C.byref(h))
+        with torch.cuda.device(self.device):       # the C entry points select their handle's device: restore the caller's
+            rc = self.lib.mc_create(self.device_index, C.byref(h))
         if rc != 0:
             raise RuntimeError(f"mc_create failed: {self.lib.mc_last_error(None).decode()}")
         self.handle = h
 
     def close(self):
         if getattr(self, "handle", None):
-            self.lib.mc_destroy(self.handle)
+            with torch.cuda.device(self.device):
+                self.lib.mc_destroy(self.handle)
             self.handle = None
 
     def __del__(self):
@@ -213,10 +215,67 @@ class Engine:
                                            ptr(shocks_t), ptr(paths), ptr(terminal), C.byref(res), hist_p, fan_p,
                                            self.stream_ptr()))
             else:
-                backend = _CudaStageBackend(self, params, pf, pool_t, shocks_t, paths, terminal, world)
-                run_stages(backend, group)
-                self.check(self.lib.mc_fetch_result(self.handle, C.byref(res), hist_p, fan_p, self.stream_ptr()))
+                staged = True
+                if self.fused_request(spec, world) and self.attach_peers(group):
+                    # two exchanges, both carried out by the kernels through peer-mapped memory: no stage calls
+                    self.check(self.lib.mc_run_sharded(self.handle, C.byref(params), C.byref(pf) if pf else None,
+                                                       ptr(pool_t), ptr(shocks_t), ptr(paths), ptr(terminal),
+                                                       self.stream_ptr()))
+                    self.check(self.lib.mc_fetch_result(self.handle, C.byref(res), hist_p, fan_p, self.stream_ptr()))
+                    staged = res.status != 0       # identical on every rank: redo the reductions the general way
+                    if staged:
+                        params.flags = (params.flags | L.FLAG_TERMINAL_GIVEN) & ~L.FLAG_STORE_PATHS
+                if staged:
+                    backend = _CudaStageBackend(self, params, pf, pool_t, shocks_t, paths, terminal, world)
+                    run_stages(backend, group)
+                    self.check(self.lib.mc_fetch_result(self.handle, C.byref(res), hist_p, fan_p, self.stream_ptr()))
         return self._pack(spec, res, hist, fan, terminal, paths if keep_paths else None, offset)
+
+    # ------------------------------------------------------------------ peers (runs sharded without host round trips)
+    @staticmethod
+    def fused_request(spec: SimSpec, world: int) -> bool:
+        """What `mc_run_sharded` accepts (include/mc_b200.h): no fan chart, an explicit histogram range."""
+        if spec.fan_chart or world > 16:
+            return False
+        return not spec.hist_bins or (spec.hist_range is not None and spec.hist_bins <= 16384)
+
+    def attach_peers(self, group) -> bool:
+        """Collective over `group`, once per engine: every rank allocates its exchange buffer, the 64-byte CUDA IPC
+        handles are all-gathered (the one NCCL call of this engine's sharded runs) and every rank maps its peers'
+        buffers.  False -- on every rank alike -- when any rank could not, and the staged protocol is used instead."""
+        import torch.distributed as dist
+        key = id(group)
+        state = getattr(self, "_peer_state", None)
+        if state is not None:
+            return state[0] == key and state[1]
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        ok = 1
+        with torch.cuda.device(self.device):
+            raw = (C.c_ubyte * 64)()
+            local, nbytes = C.c_void_p(), C.c_uint64()
+            if self.lib.mc_peer_export(self.handle, world, raw, C.byref(local), C.byref(nbytes)) != 0:
+                ok = 0
+            mine = torch.tensor(list(raw), dtype=torch.uint8, device=self.device)
+            everyone = torch.empty(64 * world, dtype=torch.uint8, device=self.device)
+            dist.all_gather_into_tensor(everyone, mine, group=group)
+            handles = bytes(everyone.cpu().numpy().tobytes())
+            if ok and self.lib.mc_peer_attach(self.handle, rank, world, handles, None) != 0:
+                ok = 0
+            flag = torch.tensor([ok], dtype=torch.int32, device=self.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+            ok = int(flag.item())
+        self._peer_state = (key, bool(ok))
+        return bool(ok)
+
+    def debug_set_tuning(self, side_cap: int = -1, no_side_lists: bool = False, waves: int = 0, nblock: int = 0):
+        """Test knobs (`mc_debug_set_tuning`), applied to this engine and the chunk engines it spawned."""
+        self._tuning = (int(side_cap), int(bool(no_side_lists)), int(waves), int(nblock))
+        for e in [self] + [x for x in getattr(self, "_chunk_engines", []) if x is not self]:
+            e.check(e.lib.mc_debug_set_tuning(e.handle, *self._tuning))
+
+    def debug_counter(self, which: int) -> int:
+        """0 fused runs, 1 fused runs redone by the staged selection, 2 status of the last one, 3 re-simulations."""
+        return int(self.lib.mc_debug_counter(self.handle, int(which)))
 
     def _simulate_regenerating(self, spec, pool_t, group, world, rank, offset, n_local, dt) -> RunOutput:
         """Fan chart (app.py:643-645) for a path range whose [(T+1), N] matrix does not fit: chunks of
@@ -234,6 +293,8 @@ class Engine:
         engines = getattr(self, "_chunk_engines", [])
         while len(engines) < n_chunks:
             engines.append(self if not engines else Engine(self.device_index))
+            if engines[-1] is not self and getattr(self, "_tuning", None):
+                engines[-1].check(engines[-1].lib.mc_debug_set_tuning(engines[-1].handle, *self._tuning))
         self._chunk_engines = engines
         with torch.cuda.device(self.device):
             terminal = torch.empty(n_local, dtype=dt, device=self.device)

@@ -259,7 +259,7 @@ def test_fan_chart_by_regeneration_equals_stored_paths(engine, mode, dtype):
     assert abs(a.tail_sum - b.tail_sum) < 1e-12 * abs(a.tail_sum)
 
 
-def test_regeneration_restores_rows_when_the_side_lists_do_not_cover_a_pass(engine, monkeypatch):
+def test_regeneration_restores_rows_when_the_side_lists_do_not_cover_a_pass(engine):
     """MC_FLAG_PATHS_VOLATILE: from the second narrowing pass on a chunk works from the values pass 1 kept; with
     32-entry lists they overflow, and the handle must simulate the chunk again by itself -- same fan chart."""
     kw = dict(dtype="float32", seed=77, store_paths=True, fan_chart=True)
@@ -268,14 +268,16 @@ def test_regeneration_restores_rows_when_the_side_lists_do_not_cover_a_pass(engi
     a = engine.simulate(full)
     ref_fan = np.percentile(a.paths.cpu().numpy().astype(np.float64), port.REF_PATH_PCTS, axis=1)
     launches = {}
-    for cap in (None, "32"):
-        if cap:
-            monkeypatch.setenv("MC_SIDE_CAP", cap)
-        b = engine.simulate(SimSpec.gbm(n, t, 100.0, 0.05, 0.2, 1 / 252, fan_chunk_paths=100_000, **kw))
-        assert np.array_equal(np.stack([b.fan[f"p{p}"] for p in port.REF_PATH_PCTS]), ref_fan)
-        assert a.pct == b.pct and torch.equal(a.terminal, b.terminal)
-        launches[cap] = b.launches
-    assert launches["32"] > launches[None]          # the extra simulations
+    try:
+        for cap in (None, 32):
+            engine.debug_set_tuning(side_cap=-1 if cap is None else cap)
+            b = engine.simulate(SimSpec.gbm(n, t, 100.0, 0.05, 0.2, 1 / 252, fan_chunk_paths=100_000, **kw))
+            assert np.array_equal(np.stack([b.fan[f"p{p}"] for p in port.REF_PATH_PCTS]), ref_fan)
+            assert a.pct == b.pct and torch.equal(a.terminal, b.terminal)
+            launches[cap] = b.launches
+    finally:
+        engine.debug_set_tuning()
+    assert launches[32] > launches[None]          # the extra simulations
 
 
 def test_drop_in_without_paths_still_has_the_fan_chart():

@@ -81,25 +81,25 @@ def test_percentiles_rows_and_degenerate(engine):
 
 
 @pytest.mark.parametrize("mode", ["default", "tiny_lists", "off"])
-def test_percentiles_side_lists_and_their_fallbacks(engine, mode, monkeypatch):
+def test_percentiles_side_lists_and_their_fallbacks(engine, mode):
     """fp32 pass 1 keeps the in-bracket values in side lists that the later passes read instead of the rows;
     a list that overflows (forced here with 32-entry lists) or side lists switched off fall back to streaming
     the rows: the result is the exact np.percentile either way."""
-    if mode == "tiny_lists":
-        monkeypatch.setenv("MC_SIDE_CAP", "32")
-    elif mode == "off":
-        monkeypatch.setenv("MC_NO_SIDE_LISTS", "1")
-    rs = np.random.RandomState(17)
-    x = (50 * np.exp(0.3 * rs.standard_normal((11, 600_000)))).astype(np.float32)
-    x[3, ::7] = x[3, 0]                                    # heavy ties
-    x[4, :] = np.sort(x[4, :])                             # sorted row: the leading pilot sample misses every bracket
-    x[5, :300_000] = 1.0                                   # half the row is one value
-    xt = torch.tensor(x, device=engine.device)
-    for pcts in ([5, 25, 50, 75, 95], [1, 5, 10, 25, 50, 75, 90, 95, 99]):
-        ref = np.percentile(x.astype(np.float64), pcts, axis=1).T
-        assert np.array_equal(engine.percentiles(xt, pcts), ref)
-    one = torch.tensor(x[0], device=engine.device)
-    assert np.array_equal(engine.percentiles(one, [1, 50, 99])[0], np.percentile(x[0].astype(np.float64), [1, 50, 99]))
+    engine.debug_set_tuning(side_cap=32 if mode == "tiny_lists" else -1, no_side_lists=mode == "off")
+    try:
+        rs = np.random.RandomState(17)
+        x = (50 * np.exp(0.3 * rs.standard_normal((11, 600_000)))).astype(np.float32)
+        x[3, ::7] = x[3, 0]                                    # heavy ties
+        x[4, :] = np.sort(x[4, :])                             # sorted row: the leading pilot sample misses every bracket
+        x[5, :300_000] = 1.0                                   # half the row is one value
+        xt = torch.tensor(x, device=engine.device)
+        for pcts in ([5, 25, 50, 75, 95], [1, 5, 10, 25, 50, 75, 90, 95, 99]):
+            ref = np.percentile(x.astype(np.float64), pcts, axis=1).T
+            assert np.array_equal(engine.percentiles(xt, pcts), ref)
+        one = torch.tensor(x[0], device=engine.device)
+        assert np.array_equal(engine.percentiles(one, [1, 50, 99])[0], np.percentile(x[0].astype(np.float64), [1, 50, 99]))
+    finally:
+        engine.debug_set_tuning()
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
