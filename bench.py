@@ -44,19 +44,30 @@ WORKLOADS = {
                                                      "(SURVEY 8f N1)"),
     "ref": dict(paths=10_000_000, steps=252, desc="reference model (bootstrap + GARCH(1,1), app.py:618-633) "
                                                   "10M paths x 252 steps fp32"),
+    "ref64": dict(paths=10_000_000, steps=252, desc="reference model in the reference's own precision (float64, app.py:612-633) "
+                                                    "10M paths x 252 steps, terminal statistics, no paths kept"),
+    "c1": dict(paths=10_000, steps=252, desc="BASELINE configs[0]: the reference's whole routine (app.py:586-657) at 10k paths x "
+                                             "252 steps, float64, paths matrix + per-step fan chart + terminal statistics"),
 }
+FP64_WORKLOADS = ("ref64", "c1")
 # algorithmic work per path-step of the fused kernels -> path-steps per SM-clock
-# (fused GBM: 16 ALU lane-ops / 128 lanes = 2 MUFU / 16 lanes = 1/8 clk per path-step).
-STEPS_PER_SM_CLK = {"c2": 8.0, "c4": 8.0, "ref": 7.5, "c3": 0.33}
-# The kernels as built: what the binding pipe allows at the MEASURED issue rates of
-# sm_100a (tools/microbench*.cu: IMAD.WIDE 31.6 lanes/clk/SM, MUFU 15.9).  Philox-4x32-10 costs 20
-# IMAD.WIDE per call; a call feeds 8 normals (fp32), 5 bootstrap indices, or half a 16-asset step.
-OWN_BOUND_PER_SM_CLK = {"c2": 31.6 * 8 / 20, "c4": 31.6 * 8 / 20, "ref": 31.6 * 5 / 20, "c3": 128.0 / 300}
-OWN_BOUND_PIPE = {"c2": "IMAD.WIDE (Philox): 2.5 per normal at 31.6 lanes/clk/SM",
-                  "c4": "IMAD.WIDE (Philox): 2.5 per normal at 31.6 lanes/clk/SM",
-                  "ref": "IMAD.WIDE (Philox): 4 per bootstrap index at 31.6 lanes/clk/SM",
-                  "c3": "issue: ~300 instructions per 16-asset step (2 Philox calls, 8 Box-Muller pairs, "
-                        "72 FFMA2 + 16 FFMA; ncu v5: 302) at 128 lane-instr/clk/SM"}
+# (fused GBM: 16 ALU lane-ops / 128 lanes = 2 MUFU / 16 lanes = 1/8 clk per path-step).  Kept as `survey_8d`.
+STEPS_PER_SM_CLK = {"c2": 8.0, "c4": 8.0, "ref": 7.5, "c3": 0.33, "ref64": 4.8, "c1": 4.8}
+# The headline roofline: what the BINDING resource of the kernel AS BUILT allows, from the instruction mix of its
+# hot loop (tools/sass_loops.py -> profiles/r02/sass_hot_loops.txt) at the issue rates MEASURED on sm_100a
+# (tools/microbench*.cu, per SM per clock: IMAD.WIDE / IMAD.HI 31.6, IMAD 63, FFMA2 / FMUL2 62.3 -- all on the heavy
+# FMA pipe, which they hold one after the other --, DFMA 62.7, 128 thread-instructions issued).
+#   fused GBM      per normal: 2.12 IMAD.WIDE + 0.94 IMAD + 0.75 FFMA2 = 0.0940 clk of heavy pipe; 9.8 instr = 0.0766 clk of issue
+#   Mode R fp32    per step:   3.40 IMAD.WIDE + 1.20 IMAD + 0.40 FFMA2 = 0.1330 clk;              17.6 instr = 0.1375 clk of issue
+#   portfolio d=16 per step:   76 FFMA2 + 8 FMUL2 + 36 IMAD.WIDE + 5 IMAD = 2.566 clk;             288 instr = 2.25 clk of issue
+#   Mode R fp64    per step:   13 DFMA/DMUL/DADD = 0.207 clk, 7.25 IMAD.WIDE/HI = 0.229 clk;      50.5 instr = 0.395 clk of issue
+BOUND_PER_SM_CLK = {"c2": 1 / 0.0940, "c4": 1 / 0.0940, "ref": 1 / 0.1375, "c3": 1 / 2.566, "ref64": 1 / 0.395, "c1": 1 / 0.395}
+BOUND_PIPE = {"c2": "heavy FMA pipe: 2.12 IMAD.WIDE + 0.94 IMAD + 0.75 FFMA2 per normal",
+              "c4": "heavy FMA pipe: 2.12 IMAD.WIDE + 0.94 IMAD + 0.75 FFMA2 per normal",
+              "ref": "issue: 17.6 instructions per path-step (heavy FMA pipe close behind: 3.4 IMAD.WIDE + 1.2 IMAD)",
+              "c3": "heavy FMA pipe: 76 FFMA2 + 8 FMUL2 + 36 IMAD.WIDE per 16-asset step",
+              "ref64": "issue: 50.5 instructions per path-step (13 on the FP64 pipe, 7.25 IMAD.WIDE/HI)",
+              "c1": "issue: 50.5 instructions per path-step; at 10k paths the job is launch-latency bound"}
 
 
 class ClockSampler:
@@ -147,6 +158,12 @@ def make_spec(workload, world):
         _, _, chunk = _fan_plan(False, True, n, t, "float32")
         spec = SimSpec.gbm(n, t, S0, MU, SIGMA, DT, seed=SEED, hist_bins=2048, hist_range=hist_range(t),
                            store_paths=True, fan_chart=True, fan_chunk_paths=chunk)
+    elif workload in FP64_WORKLOADS:
+        returns, rvol = synthetic_history()
+        pool = bootstrap_pool(returns)
+        full = workload == "c1"
+        spec = SimSpec(n_paths=n, n_steps=t, s0=S0, var0=rvol ** 2 / 252, seed=SEED, dtype="float64", store_paths=full,
+                       fan_chart=full)
     elif workload == "c3":
         d = 16
         corr = np.full((d, d), 0.3) + 0.7 * np.eye(d)
@@ -181,6 +198,10 @@ def api_call(workload, world, group):
     import pandas as pd
     returns, rvol = synthetic_history()
     df = pd.DataFrame({"log_ret": returns, "rvol_20": rvol})
+    if workload == "c1":        # the drop-in exactly as app.py:1240 calls it (host NumPy paths, fan chart, float64)
+        return mc.garch_monte_carlo(df, n, t, S0, seed=SEED, group=group)
+    if workload == "ref64":
+        return mc.garch_monte_carlo(df, n, t, S0, seed=SEED, return_paths=False, fan_chart=False, group=group)
     return mc.garch_monte_carlo(df, n, t, S0, seed=SEED, dtype="float32", return_paths=False, fan_chart=False,
                                 hist_bins=2048, hist_range=hist_range(t), group=group)
 
@@ -192,12 +213,15 @@ def io_bytes(workload, spec, pool):
     from montecarlo_b200 import _lib
     plan_bytes = 592                      # sizeof(mc::SelectPlan)
     h2d = ctypes.sizeof(_lib.McParams) + plan_bytes * (2 if spec.fan_chart else 1)
+    itemsize = 8 if spec.dtype == "float64" else 4
     if pool is not None:
-        h2d += pool.size * 4
+        h2d += pool.size * itemsize
     if spec.portfolio is not None:
         d = len(spec.portfolio.s0)
         h2d += 4 * (d * (d + 1) // 2 + 2 * d)
-    d2h = 496 + 8 * spec.hist_bins + (8 * len(spec.path_pcts) * (spec.n_steps + 1) if spec.fan_chart else 0)
+    d2h = 504 + 8 * spec.hist_bins + (8 * len(spec.path_pcts) * (spec.n_steps + 1) if spec.fan_chart else 0)
+    if workload == "c1":        # the drop-in hands the paths matrix back as host NumPy, like the reference
+        d2h += 8 * spec.n_paths * (spec.n_steps + 1)
     return h2d, d2h
 
 
@@ -207,7 +231,7 @@ def run_workload(workload, steps, warmup, world, rank, group, device, sample_clo
     from montecarlo_b200.engine import get_engine
     eng = get_engine(device)
     spec, pool = make_spec(workload, world)
-    pool_dev = eng.to_device(pool, torch.float32) if pool is not None else None
+    pool_dev = eng.to_device(pool, torch.float64 if spec.dtype == "float64" else torch.float32) if pool is not None else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=eng.device)       # > 126 MB L2
     n_local = WORKLOADS[workload]["paths"]
     t = spec.n_steps
@@ -241,6 +265,9 @@ def run_workload(workload, steps, warmup, world, rank, group, device, sample_clo
     for a, b in ev:
         flush.zero_()                     # L2 flush between timed iterations (untimed)
         torch.cuda.synchronize(eng.device)
+        if world > 1:                     # ranks enter the step together: a step ends at its (device-side) exchanges,
+            dist.barrier(group)           # so a rank that started late would bill its lateness to the others
+            torch.cuda.synchronize(eng.device)
         a.record()
         last = one_step()
         b.record()
@@ -312,20 +339,24 @@ def _roofline_for(workload, r, n_sm, clocks, peaks, peaks_kind):
                 "algorithmic_bytes_per_launch": bytes_}
     mhz_max = float(peaks.get("sm_max_mhz", 1965.0))
     mhz = (clocks or {}).get("sm_mhz") or mhz_max
-    per_clk = STEPS_PER_SM_CLK[workload]
     ach = n * t / sim_s
-    peak = per_clk * n_sm * mhz * 1e6
-    own = OWN_BOUND_PER_SM_CLK[workload] * n_sm * mhz * 1e6
-    lane_ops = {"c2": 16, "c4": 16, "ref": 17, "c3": 388}[workload]
-    return {"bound": "fp32-alu+mufu issue (not hbm, not tensor)", "kernel": "sim32_kernel / portfolio_kernel (fused RNG + step + moments)",
-            "achieved": ach / 1e9, "peak": peak / 1e9, "unit": "Gpath-steps/s", "frac": ach / peak,
-            "traffic": None, "peak_source": f"SURVEY 8d: {per_clk} path-steps/SM-clk x {n_sm} SMs x {mhz:.0f} MHz "
-                                            "(median SM clock sampled during the timed region)",
-            "frac_at_max_clock": ach / (per_clk * n_sm * mhz_max * 1e6),
-            "own_pipe_bound": {"peak": own / 1e9, "frac": ach / own, "pipe": OWN_BOUND_PIPE[workload],
-                               "note": "SURVEY 8d assumed 2 MUFU per normal; the kernels as built take sin/cos from a "
-                                       "shared-memory table (1 MUFU per normal), so the measured-rate Philox multiply binds"},
-            "fp32_lane_tflops": ach * lane_ops * 1e-12, "lane_ops_per_path_step": lane_ops}
+    peak = BOUND_PER_SM_CLK[workload] * n_sm * mhz * 1e6
+    survey = STEPS_PER_SM_CLK[workload] * n_sm * mhz * 1e6
+    frac = ach / peak
+    out = {"bound": "fp32 issue / heavy FMA pipe (not hbm, not tensor)" if workload not in FP64_WORKLOADS else "issue / FP64 pipe",
+           "kernel": {"c3": "portfolio_kernel<float,16>", "ref64": "sim_kernel<double,BOOTSTRAP,GARCH>",
+                      "c1": "sim_kernel<double,BOOTSTRAP,GARCH,STORE>"}.get(workload, "sim32_kernel<...,SINK> (fused RNG + step + histograms)"),
+           "achieved": ach / 1e9, "peak": peak / 1e9, "unit": "Gpath-steps/s", "frac": min(frac, 1.0), "traffic": None,
+           "peak_source": f"{BOUND_PIPE[workload]}: {BOUND_PER_SM_CLK[workload]:.2f} path-steps/SM-clk x {n_sm} SMs x {mhz:.0f} MHz "
+                          "(instruction mix of the hot loop from the shipped SASS, issue rates measured on sm_100a; median SM "
+                          "clock sampled during the timed region)",
+           "survey_8d": {"peak": survey / 1e9, "frac": ach / survey,
+                         "note": f"SURVEY 8d's model of the algorithm ({STEPS_PER_SM_CLK[workload]} path-steps/SM-clk): it assumed 4 "
+                                 "normals per Philox call and 2 MUFU per normal; the kernels draw 8 per call and read sin/cos "
+                                 "from a shared-memory table, so this fraction can exceed 1 and is not the headline"}}
+    if frac > 1.0:
+        out["frac_unclamped"] = frac        # the bound is wrong if this ever shows up
+    return out
 
 
 def callers_leg():
@@ -358,52 +389,125 @@ def callers_leg():
 
 
 # --------------------------------------------------------------------------- CPU arms
+# kind of loop the oracle port times for a workload that the reference itself cannot run (it has no GBM / portfolio)
 CPU_KIND = {"c2": "gbm", "c4": "gbm", "c5": "gbm", "c3": "gbm", "ref": "garch", "c4fan": "gbm"}
+# workloads that ARE the reference's routine: timed with the unmodified function when it travelled (oracle/_ref)
+REFERENCE_WORKLOADS = ("c1", "ref64")
+
+
+def _reference_function():
+    """The unmodified `garch_monte_carlo` (app.py:586-657): from /root/reference in the build container, from the
+    AST-extracted copy under oracle/_ref/ (git-ignored, written by __graft_entry__.build) on the GPU box."""
+    from oracle import ref_loader
+    path = ref_loader.reference_path()
+    return (ref_loader.load_reference_function(path), path) if path else (None, None)
+
+
+def _reference_chunk(args):
+    n, t, seed = args
+    import numpy as np
+    import pandas as pd
+    fn, _ = _reference_function()
+    returns, rvol = synthetic_history()
+    df = pd.DataFrame({"log_ret": returns, "rvol_20": rvol})
+    np.random.seed(seed)
+    return float(fn(df, n, t, S0)["expected_return"])
+
+
+def time_reference(n, t, processes=1, repeats=1):
+    """(best seconds, path-steps/s) of `processes` concurrent calls of the unmodified reference, n paths each."""
+    jobs = [(n, t, 1000 + i) for i in range(processes)]
+    best = float("inf")
+    if processes == 1:
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            _reference_chunk(jobs[0])
+            best = min(best, time.perf_counter() - t0)
+    else:
+        import multiprocessing as mp
+        with mp.get_context("fork").Pool(processes) as pool:
+            pool.map(_reference_chunk, [(200, 2, 0)] * processes)
+            for _ in range(repeats):
+                t0 = time.perf_counter()
+                pool.map(_reference_chunk, jobs)
+                best = min(best, time.perf_counter() - t0)
+    return best, n * t * processes / best
 
 
 def cpu_baseline_leg(workload, target_seconds=8.0):
-    """Oracle port (NumPy, one core like the reference's own loop) on a bounded sample."""
+    """The CPU beside the GPU number, one core (NumPy's elementwise ops, choice and percentile are single-threaded).
+    c1 / ref64: the UNMODIFIED reference function at BASELINE configs[0]'s size (10k x 252, all of app.py:586-657
+    incl. the paths matrix and the axis=1 percentiles that are 61-72 % of its time).  Other workloads: the oracle
+    port's loop for the model the reference does not have (GBM), terminal statistics only -- no paths matrix, no
+    fan chart, so ~10x faster per path-step than the reference's own routine."""
     from oracle import cpu_baseline as cb
-    kind = CPU_KIND[workload]
+    if workload in REFERENCE_WORKLOADS and _reference_function()[0] is not None:
+        n, t = 10_000, 252
+        sec, rate = time_reference(n, t, 1, repeats=3)
+        total, runs = sec * 3, 3
+        while total < target_seconds and runs < 40:
+            s2, r2 = time_reference(n, t, 1)
+            total += s2; runs += 1
+            if s2 < sec:
+                sec, rate = s2, r2
+        return {"value": rate, "unit": "path-steps/s", "cores": 1, "kind": "reference",
+                "sample": f"unmodified garch_monte_carlo (app.py:586-657, AST-extracted), {n} paths x {t} steps per call "
+                          f"(BASELINE configs[0]), best of {runs} calls, {sec:.3f} s each"}
+    kind = "reference" if workload in REFERENCE_WORKLOADS else CPU_KIND[workload]
     t = min(WORKLOADS[workload]["steps"], 252)
-    n = 200_000
+    n = 200_000 if kind != "reference" else 10_000
     sec, rate, cores = cb.time_cpu(kind, n, t, processes=1)
-    if sec < target_seconds / 4:                 # grow the sample towards ~target_seconds
+    if sec < target_seconds / 4 and kind != "reference":     # grow the sample towards ~target_seconds
         n = int(min(2_000_000, n * target_seconds / max(sec, 1e-3) / 2))
         sec, rate, cores = cb.time_cpu(kind, n, t, processes=1)
+    what = ("full routine of app.py:612-657 incl. paths matrix and fan chart" if kind == "reference" else
+            f"{kind} loop of app.py:618-633 + terminal statistics ONLY (no paths matrix, no axis=1 percentiles: the "
+            "reference's own routine is ~10x slower per path-step)")
     return {"value": rate, "unit": "path-steps/s", "cores": cores, "kind": "port",
-            "sample": f"oracle NumPy port ({kind} loop of app.py:618-633 + terminal statistics), "
-                      f"{n} paths x {t} steps, {sec:.2f} s, single process"}
+            "sample": f"oracle NumPy port ({what}), {n} paths x {t} steps, {sec:.2f} s, single process"}
 
 
 def reference_arm(args, rank):
-    """--impl reference: the reference's CPU algorithm for this path (the oracle port: the reference
-    is pure Python/NumPy and does not travel to the GPU box) on all host cores."""
+    """--impl reference: the reference's CPU implementation of the path on all host cores.  c1 / ref64: the
+    unmodified function (oracle/_ref) in one process per core; the GBM workloads: the oracle port's GBM loop."""
     if rank != 0:
         return
     from oracle import cpu_baseline as cb
     workload = args.workload
-    kind = CPU_KIND[workload]
     cores = cb.host_cores()
     procs = max(1, min(cores, 64))
+    real = workload in REFERENCE_WORKLOADS and _reference_function()[0] is not None
     t = min(WORKLOADS[workload]["steps"], 252)
-    per_proc = 50_000
-    for _ in range(args.warmup):
-        cb.time_cpu(kind, 2_000 * procs, 8, processes=procs)
     total_s, total_steps = 0.0, 0
-    for _ in range(args.steps):
-        sec, rate, _ = cb.time_cpu(kind, per_proc * procs, t, processes=procs)
-        total_s += sec
-        total_steps += per_proc * procs * t
+    if real:
+        per_proc = 10_000
+        for _ in range(args.warmup):
+            time_reference(500, 8, procs)
+        for _ in range(args.steps):
+            sec, _ = time_reference(per_proc, t, procs)
+            total_s += sec
+            total_steps += per_proc * procs * t
+        kind, what = "reference", "unmodified garch_monte_carlo (app.py:586-657, AST-extracted)"
+    else:
+        kind = "reference" if workload in REFERENCE_WORKLOADS else CPU_KIND[workload]
+        per_proc = 50_000 if kind != "reference" else 10_000
+        for _ in range(args.warmup):
+            cb.time_cpu(kind, 2_000 * procs, 8, processes=procs)
+        for _ in range(args.steps):
+            sec, rate, _ = cb.time_cpu(kind, per_proc * procs, t, processes=procs)
+            total_s += sec
+            total_steps += per_proc * procs * t
+        what = (f"oracle NumPy port ({kind}" + (": loop + terminal statistics only, no paths matrix / fan chart -- ~10x faster "
+                                                "per path-step than the reference's own routine)" if kind != "reference" else ")"))
+        kind = "port"
     value = total_steps / total_s
     line = {"impl": "reference", "metric": "path-steps/sec", "value": value, "unit": "path-steps/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"{workload}: {WORKLOADS[workload]['desc']}",
                        "sample": f"{per_proc * procs} paths x {t} steps per step"},
-            "cpu_baseline": {"value": value, "unit": "path-steps/s", "cores": procs, "kind": "port",
-                             "sample": f"oracle NumPy port ({kind}), {per_proc} paths x {t} steps in each of "
-                                       f"{procs} processes per step"},
+            "cpu_baseline": {"value": value, "unit": "path-steps/s", "cores": procs, "kind": kind,
+                             "sample": f"{what}, {per_proc} paths x {t} steps in each of {procs} processes per step"},
             "e2e": {"value": value, "unit": "path-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -447,25 +551,36 @@ def main():
             "e2e": r["e2e"], "gpu_launches": r["gpu_launches"], "clocks": r["clocks"],
             "roofline": roofline_for(args.workload, r, n_sm, r["clocks"], peaks, peaks_kind),
             "sim_kernel_ms": r["sim_ms"], "result": r["summary"]}
-    if rank == 0 and world == 1 and not args.no_extras:
-        line["cpu_baseline"] = cpu_baseline_leg(args.workload)
+    if args.workload in FP64_WORKLOADS:
+        line["dtype"] = "f64"
+    if not args.no_extras:
+        # the other BASELINE configs ride along.  One GPU: all of them + the CPU leg + the callers.  Several ranks: the
+        # configuration BASELINE quotes for 2/4/8 GPUs (config 4: 12.5M paths x 2520 steps per rank = 100M at 8) with
+        # and without the per-step fan chart -- every rank runs them, rank 0 reports.
+        if world == 1 and rank == 0:
+            line["cpu_baseline"] = cpu_baseline_leg(args.workload)
+        names = ("c4", "c5", "c3", "ref", "ref64", "c1", "c4fan", "c2") if world == 1 else ("c4", "c4fan")
         extras = {}
-        for wl in ("c4", "c5", "c3", "ref", "c4fan", "c2"):
+        for wl in names:
             if wl == args.workload:
                 continue
             try:
-                x = run_workload(wl, 3 if wl != "c4fan" else 2, 3 if wl != "c4fan" else 1, 1, 0, None, local_rank,
+                x = run_workload(wl, 3 if wl != "c4fan" else 2, 3 if wl != "c4fan" else 1, world, rank, group, local_rank,
                                  sample_clocks=True)
                 extras[wl] = {"workload": WORKLOADS[wl]["desc"], "value": x["value"], "ms_per_step": x["ms_per_step"],
-                              "e2e": x["e2e"]["value"], "sim_kernel_ms": x["sim_ms"], "clocks": x["clocks"],
+                              "n_gpus": world, "e2e": x["e2e"]["value"], "sim_kernel_ms": x["sim_ms"], "clocks": x["clocks"],
+                              "gpu_launches_per_step": x["gpu_launches"] / (3 if wl != "c4fan" else 2),
                               "roofline": roofline_for(wl, x, n_sm, x["clocks"], peaks, peaks_kind)}
+                if world == 1 and wl in REFERENCE_WORKLOADS:
+                    extras[wl]["cpu_baseline"] = cpu_baseline_leg(wl, target_seconds=4.0)
             except Exception as exc:      # an extra must never lose the headline line
                 extras[wl] = {"error": repr(exc)[:200]}
             torch.cuda.empty_cache()
-        try:
-            extras["callers"] = callers_leg()
-        except Exception as exc:
-            extras["callers"] = {"error": repr(exc)[:200]}
+        if world == 1:
+            try:
+                extras["callers"] = callers_leg()
+            except Exception as exc:
+                extras["callers"] = {"error": repr(exc)[:200]}
         line["extras"] = extras
     if rank == 0:
         print(json.dumps(line), flush=True)

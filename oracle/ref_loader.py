@@ -19,8 +19,36 @@ import numpy as np
 DEFAULT_REFERENCE = os.environ.get("MC_REFERENCE", "/root/reference/app.py")
 
 
+# the function as it travels to the GPU box: extracted from the reference by `write_extracted_copy` (called from
+# __graft_entry__.build in the build container) into a git-ignored directory; never committed
+EXTRACTED_COPY = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "garch_monte_carlo_from_app_py.py")
+
+
 def reference_available(path: str = DEFAULT_REFERENCE) -> bool:
     return os.path.isfile(path)
+
+
+def reference_path():
+    """The reference itself if it is mounted here, else the extracted copy, else None."""
+    if os.path.isfile(DEFAULT_REFERENCE):
+        return DEFAULT_REFERENCE
+    return EXTRACTED_COPY if os.path.isfile(EXTRACTED_COPY) else None
+
+
+def write_extracted_copy(path: str = DEFAULT_REFERENCE) -> str:
+    """oracle/_ref/: the FunctionDef `garch_monte_carlo` (app.py:586-657) exactly as the reference has it, unparsed
+    from its AST, so that the GPU box (which has no /root/reference) can time the UNMODIFIED routine on its host."""
+    with open(path, "r") as fh:
+        src = fh.read()
+    tree = ast.parse(src, filename=path)
+    node = next(n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == "garch_monte_carlo")
+    text = ast.get_source_segment(src, node)
+    os.makedirs(os.path.dirname(EXTRACTED_COPY), exist_ok=True)
+    with open(EXTRACTED_COPY, "w") as fh:
+        fh.write("# extracted verbatim from the reference's app.py:%d-%d by oracle/ref_loader.write_extracted_copy -- not "
+                 "part of this repository's sources (git-ignored)\n" % (node.lineno, node.end_lineno))
+        fh.write(text + "\n")
+    return EXTRACTED_COPY
 
 
 def load_reference_function(path: str = DEFAULT_REFERENCE, np_module=np):

@@ -57,8 +57,10 @@ for name, (spec, p) in cases.items():
                             moments_equal_to_rounding=bool(close), p50=shard.pct.get("p50"))
     dist.barrier()
 if rank == 0:
+    report["_exchange"] = dict(peer_memory_attached=bool(getattr(eng, "_peer_state", (0, False))[1]),
+                               fused_runs=eng.debug_counter(0), fused_runs_redone_by_staged_selection=eng.debug_counter(1))
     print(json.dumps(report, indent=1))
     ok = all(v["identical_on_every_rank"] and v["order_statistics_and_counts_equal_one_gpu"] and v["moments_equal_to_rounding"]
-             for v in report.values())
+             for k, v in report.items() if not k.startswith("_"))
     print("NCCL PARITY", "OK" if ok else "FAILED")
 dist.destroy_process_group()
