@@ -323,7 +323,7 @@ int select_rows(mc_handle* h, const void* d_x, int dtype, uint64_t rows, uint64_
 }
 
 // ------------------------------------------------------------------ fused closing: host side
-constexpr unsigned int PEER_CAND_BYTES = 4u << 20;        // per rank, fixed once peers are attached
+constexpr unsigned int PEER_CAND_BYTES = 16u << 20;       // a rank's candidate lists, fixed once peers are attached
 
 bool fused_eligible(const mc_params& p) {
     if (p.flags & (MC_FLAG_FAN_CHART | MC_FLAG_PATHS_VOLATILE | MC_FLAG_TERMINAL_GIVEN)) return false;

@@ -44,9 +44,10 @@ __device__ __forceinline__ unsigned long long* hdr_in(const FusedArgs& a, unsign
 __device__ __forceinline__ unsigned int* nph_in(const FusedArgs& a, unsigned int owner, unsigned int from) {
     return reinterpret_cast<unsigned int*>(a.peers.base[owner] + a.lay.off_nph) + (size_t)from * FUSED_MAX_NPH_BINS;
 }
+// rank `owner`'s candidate lists live in its own buffer only; the peers read them there
 template <typename Key>
-__device__ __forceinline__ Key* cand_in(const FusedArgs& a, unsigned int owner, unsigned int from) {
-    return reinterpret_cast<Key*>(a.peers.base[owner] + a.lay.off_cand + (size_t)from * a.lay.cand_bytes);
+__device__ __forceinline__ Key* cand_of(const FusedArgs& a, unsigned int owner) {
+    return reinterpret_cast<Key*>(a.peers.base[owner] + a.lay.off_cand);
 }
 // header words a rank publishes with X2
 enum { HW_N = 0, HW_ABOVE, HW_SUM_D, HW_SUM_D2, HW_MIN, HW_MAX, HW_TAIL_CNT, HW_TAIL_SUM, HW_OVERFLOW, HW_STATUS, HW_CAND = 10 };
@@ -311,7 +312,7 @@ __global__ void __launch_bounds__(CLOSE_THREADS, 4) fused_closing_kernel(const F
     if (bins) { h_lo = edge[0]; h_top = edge[bins]; h_inv = (Real)bins / (h_top - h_lo); }
     unsigned int* my_nph = nph_in(a, me, me);
 
-    // append the staged candidates to the slots' lists: in this rank's inbox and in every peer's
+    // append the staged candidates to this rank's lists (one per slot)
     auto flush = [&]() {
         const unsigned int n_stg = s_stg_n;
         if (n_stg == 0u) return;                   // uniform: read behind a barrier
@@ -328,8 +329,7 @@ __global__ void __launch_bounds__(CLOSE_THREADS, 4) fused_closing_kernel(const F
             const unsigned int idx = s_slot_base[sl] + s_stg_pos[i];
             if (idx < P.cap[sl]) {
                 const size_t e = (size_t)P.off[sl] + idx;
-                const Key k = s_stg_key[i];
-                for (unsigned int r = 0; r < R; ++r) cand_in<Key>(a, r, me)[e] = k;
+                cand_of<Key>(a, me)[e] = s_stg_key[i];       // peers read the list over NVLink in K5
             } else {
                 atomicOr(&P.overflow, 1u);
             }
@@ -402,7 +402,7 @@ __global__ void __launch_bounds__(CLOSE_THREADS, 4) fused_closing_kernel(const F
     mine.tail_sum = acc.tail_sum; mine.n = acc.n; mine.n_above = acc.n_above; mine.tail_cnt = acc.tail_cnt;
     const ClosePartial blockp = block_reduce(mine, s_part);
     if (tid == 0) a.partials[blockIdx.x] = blockp;
-    if (R > 1) __threadfence_system(); else __threadfence();      // the candidates went to the peers, too
+    __threadfence();
     __syncthreads();
     if (tid == 0) s_last = atomicAdd(&P.ticket4, 1u) == gridDim.x - 1 ? 1 : 0;
     __syncthreads();
@@ -560,7 +560,7 @@ __global__ void __launch_bounds__(SEL_THREADS) fused_select_kernel(const FusedAr
         // first such sweep has copied them -- from shared memory
         auto sweep_lists = [&](auto f) {
             for (unsigned int r = 0; r < R; ++r) {
-                const Key* src = cand_in<Key>(a, me, r) + off;
+                const Key* src = cand_of<Key>(a, r) + off;      // rank r's own list, in rank r's memory
                 const unsigned int cnt = s_cnt[r];
                 for (unsigned int j = tid; j < cnt; j += 4u * SEL_THREADS) {
                     Key k[4];

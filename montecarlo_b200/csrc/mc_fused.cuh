@@ -11,11 +11,13 @@
 //       (method='linear': ranks floor(h), floor(h) + 1), exact populations below each such bin.
 //   K4  ONE pass over the terminal values: moments about s0, exceedance count, min / max, tail sums below the
 //       CVaR bin, the fixed-bin histogram when K1 did not take it, and the values of the target bins
-//       ("candidates", ~1 % of the data) appended to per-bin lists -- written straight into every peer's inbox
-//       as they are found (X2), flags raised by the last block.
-//   K5  one block per target bin selects its order statistics among the gathered candidates (sub-histogram,
-//       then a bitonic sort of <= 4096 keys); the last block to finish applies NumPy's _lerp, merges moments,
-//       tail and histogram over ranks in rank order and writes the result to the device AND to pinned host memory.
+//       ("candidates", ~1 % of the data) appended to per-bin lists in this rank's buffer.  The last block pushes
+//       the rank's header (moments, tail sums, list lengths) and fixed-bin counts to every peer and raises the
+//       flags of X2.
+//   K5  one block per target bin reads that bin's candidates from EVERY rank's list -- the peers' over NVLink --
+//       into shared memory and selects its order statistics there (4096-bin sub-histogram, then a bitonic sort of
+//       <= 1024 keys); the last block to finish applies NumPy's _lerp, merges moments, tail and histogram over
+//       ranks in rank order and writes the result to the device AND to pinned host memory.
 //
 // Every rank computes the same plan from the same summed histogram, so all ranks end with identical results.
 // A window that missed, a candidate list that overflowed or a peer that never arrived set a status the host
@@ -120,7 +122,7 @@ struct FusedPlan {
 // rank r's contributions land in slot r of every section of every rank's buffer (its own included)
 struct XchgLayout {
     unsigned int n_ranks;
-    unsigned int cand_bytes;                  // per rank
+    unsigned int cand_bytes;                  // of this rank's candidate lists
     size_t off_flags1, off_flags2, off_hist, off_hdr, off_nph, off_cand, total;
 };
 inline XchgLayout xchg_layout(unsigned int n_ranks, unsigned int cand_bytes) {
@@ -134,7 +136,7 @@ inline XchgLayout xchg_layout(unsigned int n_ranks, unsigned int cand_bytes) {
     L.off_hist = o; o += (size_t)n_ranks * FUSED_KB * 4;
     L.off_hdr = o; o += (size_t)n_ranks * FUSED_HDR_WORDS * 8;
     L.off_nph = o; o += (size_t)n_ranks * FUSED_MAX_NPH_BINS * 4;
-    L.off_cand = o; o += (size_t)n_ranks * cand_bytes;
+    L.off_cand = o; o += (size_t)cand_bytes;                 // this rank's own candidate lists; peers read them in place
     L.total = o;
     return L;
 }
