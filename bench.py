@@ -33,6 +33,8 @@ S0, MU, SIGMA, DT = 100.0, 0.05, 0.20, 1.0 / 252
 WORKLOADS = {
     "c2": dict(paths=10_000_000, steps=252, desc="single-asset GBM 10M paths x 252 steps fp32, terminal stats + "
                                                  "9 percentiles + CVaR + 2048-bin histogram (BASELINE configs[1])"),
+    "c2full": dict(paths=10_000_000, steps=252, desc="config-2 shape with full-resolution normals (MC_FLAG_FULL_RES_NORMALS: 4 per "
+                                                     "Philox call from 32-bit uniforms, MUFU sin/cos -- SURVEY 8d's own work definition)"),
     "c4": dict(paths=12_500_000, steps=2520, desc="single-asset GBM 2520 steps fp32, 12.5M paths per GPU "
                                                   "(= 100M over 8 GPUs, BASELINE configs[3])"),
     "c5": dict(paths=4_194_304, steps=1024, desc="GBM 4M paths x 1024 steps fp32, full paths stored to HBM + "
@@ -52,7 +54,7 @@ WORKLOADS = {
 FP64_WORKLOADS = ("ref64", "c1")
 # algorithmic work per path-step of the fused kernels -> path-steps per SM-clock
 # (fused GBM: 16 ALU lane-ops / 128 lanes = 2 MUFU / 16 lanes = 1/8 clk per path-step).  Kept as `survey_8d`.
-STEPS_PER_SM_CLK = {"c2": 8.0, "c4": 8.0, "ref": 7.5, "c3": 0.33, "ref64": 4.8, "c1": 4.8}
+STEPS_PER_SM_CLK = {"c2": 8.0, "c2full": 8.0, "c4": 8.0, "ref": 7.5, "c3": 0.33, "ref64": 4.8, "c1": 4.8}
 # The headline roofline: what the BINDING resource of the kernel AS BUILT allows, from the instruction mix of its
 # hot loop (tools/sass_loops.py -> profiles/r02/sass_hot_loops.txt) at the issue rates MEASURED on sm_100a
 # (tools/microbench*.cu, per SM per clock: IMAD.WIDE / IMAD.HI 31.6, IMAD 63, FFMA2 / FMUL2 62.3 -- all on the heavy
@@ -61,8 +63,10 @@ STEPS_PER_SM_CLK = {"c2": 8.0, "c4": 8.0, "ref": 7.5, "c3": 0.33, "ref64": 4.8, 
 #   Mode R fp32    per step:   3.40 IMAD.WIDE + 1.20 IMAD + 0.40 FFMA2 = 0.1330 clk;              17.6 instr = 0.1375 clk of issue
 #   portfolio d=16 per step:   76 FFMA2 + 8 FMUL2 + 36 IMAD.WIDE + 5 IMAD = 2.566 clk;             288 instr = 2.25 clk of issue
 #   Mode R fp64    per step:   13 DFMA/DMUL/DADD = 0.207 clk, 7.25 IMAD.WIDE/HI = 0.229 clk;      50.5 instr = 0.395 clk of issue
-BOUND_PER_SM_CLK = {"c2": 1 / 0.0940, "c4": 1 / 0.0940, "ref": 1 / 0.1375, "c3": 1 / 2.566, "ref64": 1 / 0.395, "c1": 1 / 0.395}
+#   GBM full-res   per normal: 2 MUFU + 0.5 I2F = 0.156 clk of the 16-lane XU pipe; 4.25 IMAD.WIDE = 0.134 clk; 19 instr = 0.148 clk
+BOUND_PER_SM_CLK = {"c2": 1 / 0.0940, "c2full": 1 / 0.156, "c4": 1 / 0.0940, "ref": 1 / 0.1375, "c3": 1 / 2.566, "ref64": 1 / 0.395, "c1": 1 / 0.395}
 BOUND_PIPE = {"c2": "heavy FMA pipe: 2.12 IMAD.WIDE + 0.94 IMAD + 0.75 FFMA2 per normal",
+              "c2full": "XU pipe: 2 MUFU (lg2 + sqrt per pair, sin, cos) + 0.5 I2F per normal at 16 lanes (issue and IMAD.WIDE within 15 %)",
               "c4": "heavy FMA pipe: 2.12 IMAD.WIDE + 0.94 IMAD + 0.75 FFMA2 per normal",
               "ref": "issue: 17.6 instructions per path-step (heavy FMA pipe close behind: 3.4 IMAD.WIDE + 1.2 IMAD)",
               "c3": "heavy FMA pipe: 76 FFMA2 + 8 FMUL2 + 36 IMAD.WIDE per 16-asset step",
@@ -148,8 +152,9 @@ def make_spec(workload, world):
     w = WORKLOADS[workload]
     n, t = w["paths"] * world, w["steps"]
     pool = None
-    if workload in ("c2", "c4"):
-        spec = SimSpec.gbm(n, t, S0, MU, SIGMA, DT, seed=SEED, hist_bins=2048, hist_range=hist_range(t))
+    if workload in ("c2", "c4", "c2full"):
+        spec = SimSpec.gbm(n, t, S0, MU, SIGMA, DT, seed=SEED, hist_bins=2048, hist_range=hist_range(t),
+                           full_res_normals=workload == "c2full")
     elif workload == "c5":
         spec = SimSpec.gbm(n, t, S0, MU, SIGMA, DT, seed=SEED, hist_bins=2048, hist_range=hist_range(t),
                            store_paths=True, fan_chart=True)
@@ -183,8 +188,9 @@ def api_call(workload, world, group):
     import montecarlo_b200 as mc
     w = WORKLOADS[workload]
     n, t = w["paths"] * world, w["steps"]
-    if workload in ("c2", "c4"):
-        return mc.simulate_gbm(n, t, S0, MU, SIGMA, dt=DT, seed=SEED, hist_bins=2048, group=group)
+    if workload in ("c2", "c4", "c2full"):
+        return mc.simulate_gbm(n, t, S0, MU, SIGMA, dt=DT, seed=SEED, hist_bins=2048, group=group,
+                               full_resolution=workload == "c2full")
     if workload == "c5":
         return mc.simulate_gbm(n, t, S0, MU, SIGMA, dt=DT, seed=SEED, hist_bins=2048, return_paths="device", group=group)
     if workload == "c4fan":
@@ -390,7 +396,7 @@ def callers_leg():
 
 # --------------------------------------------------------------------------- CPU arms
 # kind of loop the oracle port times for a workload that the reference itself cannot run (it has no GBM / portfolio)
-CPU_KIND = {"c2": "gbm", "c4": "gbm", "c5": "gbm", "c3": "gbm", "ref": "garch", "c4fan": "gbm"}
+CPU_KIND = {"c2": "gbm", "c2full": "gbm", "c4": "gbm", "c5": "gbm", "c3": "gbm", "ref": "garch", "c4fan": "gbm"}
 # workloads that ARE the reference's routine: timed with the unmodified function when it travelled (oracle/_ref)
 REFERENCE_WORKLOADS = ("c1", "ref64")
 
@@ -559,7 +565,7 @@ def main():
         # and without the per-step fan chart -- every rank runs them, rank 0 reports.
         if world == 1 and rank == 0:
             line["cpu_baseline"] = cpu_baseline_leg(args.workload)
-        names = ("c4", "c5", "c3", "ref", "ref64", "c1", "c4fan", "c2") if world == 1 else ("c4", "c4fan")
+        names = ("c4", "c5", "c3", "ref", "ref64", "c1", "c2full", "c4fan", "c2") if world == 1 else ("c4", "c4fan")
         extras = {}
         for wl in names:
             if wl == args.workload:

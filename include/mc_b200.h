@@ -66,6 +66,10 @@ enum {
                                    handle simulates the run again by itself, and only if the values it kept from
                                    pass 1 do not cover what the pass needs; mc_stage_reads_paths then reports 1
                                    only for the first pass. */
+    MC_FLAG_FULL_RES_NORMALS = 32u, /* fp32 normal shocks from full 32-bit uniforms, four per Philox call (|z| <= 6.66,
+                                   directions through MUFU.SIN/COS) instead of the default eight per call (20-bit radius:
+                                   |z| <= 5.27, P(|z| > 5) 27 % low; 4096 tabulated directions).  ~25 % slower; for callers
+                                   who look at single-step tails.  Single-asset fp32 kernels; fp64 always draws this way. */
     MC_FLAG_TERMINAL_GIVEN = 16u /* d_terminal already holds this rank's final prices (app.py:636): no simulation, only
                                    the reductions of app.py:638-640 and 652-656.  What mc_run itself falls back to when
                                    the fused closing reports mc_result.status = 1; the same call serves a caller who

@@ -17,6 +17,7 @@ SHOCK_BOOTSTRAP, SHOCK_NORMAL, SHOCK_INJECTED = 0, 1, 2
 VAR_GARCH, VAR_CONST = 0, 1
 F32, F64 = 0, 1
 FLAG_STORE_PATHS, FLAG_FAN_CHART, FLAG_NO_TERMINAL_SELECT, FLAG_PATHS_VOLATILE, FLAG_TERMINAL_GIVEN = 1, 2, 4, 8, 16
+FLAG_FULL_RES_NORMALS = 32
 
 EXPORTS = (
     "mc_abi_version", "mc_create", "mc_destroy", "mc_last_error", "mc_run",

@@ -22,6 +22,7 @@
 #include "mc_inputs.cuh"
 #include "mc_select.cuh"
 #include "mc_sim.cuh"
+#include "mc_small.cuh"
 
 using namespace mc;
 
@@ -263,6 +264,8 @@ int validate(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const voi
     if (p->n_pcts > MC_MAX_PCTS || p->n_path_pcts > MC_MAX_PATH_PCTS) return fail(h, MC_ERR_INVALID, "too many percentiles");
     if (p->hist_bins > (1u << 16)) return fail(h, MC_ERR_INVALID, "hist_bins > 65536");
     if (!(p->var0 >= 0.0) || !(p->s0 == p->s0)) return fail(h, MC_ERR_INVALID, "var0 must be >= 0");
+    if ((p->flags & MC_FLAG_FULL_RES_NORMALS) && p->n_assets > 1 && p->dtype == MC_F32 && p->shock == MC_SHOCK_NORMAL)
+        return fail(h, MC_ERR_INVALID, "MC_FLAG_FULL_RES_NORMALS: single-asset kernels only");
     if ((p->flags & MC_FLAG_TERMINAL_GIVEN) && (p->flags & (MC_FLAG_STORE_PATHS | MC_FLAG_FAN_CHART)))
         return fail(h, MC_ERR_INVALID, "MC_FLAG_TERMINAL_GIVEN reduces terminal values only");
     return MC_OK;
@@ -531,6 +534,87 @@ int fused_fetch(mc_handle* h, mc_result* r, uint64_t* h_hist, cudaStream_t s, in
     r->status = (uint32_t)*status;
     if (*status != FUSED_OK) { h->n_fused_fallback += 1; h->fused_dirty = true; }
     if (*status == FUSED_PEER_TIMEOUT) return fail(h, MC_ERR_STATE, "a peer rank never delivered its part of the exchange (20 s)");
+    return MC_OK;
+}
+
+// ------------------------------------------------------------------ the reference's own call sizes: two launches
+bool small_eligible(const mc_params& p) {
+    if (!(p.flags & MC_FLAG_FAN_CHART) || !(p.flags & MC_FLAG_STORE_PATHS) || p.n_path_pcts == 0) return false;
+    if (p.flags & (MC_FLAG_PATHS_VOLATILE | MC_FLAG_TERMINAL_GIVEN)) return false;
+    if (p.hist_bins || ranks_of(p) > 1 || p.n_paths != p.n_paths_global) return false;
+    if (p.n_paths == 0 || p.n_paths > (p.dtype == MC_F64 ? SMALL_MAX_PATHS_F64 : SMALL_MAX_PATHS_F32)) return false;
+    return (size_t)p.n_steps + 1 <= 65535;
+}
+
+// returns MC_OK with *done = false when the job turned out not to fit this path after all (nothing is lost: the
+// caller runs the general path)
+int small_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void* d_pool, const void* d_shocks,
+              void* d_paths, void* d_terminal, mc_result* r, double* h_fan, cudaStream_t s, bool* done) {
+    *done = false;
+    int rc = validate(h, p, pf, d_pool, d_shocks, d_paths, d_terminal);
+    if (rc) return rc;
+    MC_DEVICE(h);
+    h->active = false;
+    h->fused_pending = false;
+    h->p = *p;
+    h->launches = 0;
+    h->has_t = p->n_pcts > 0 && !(p->flags & MC_FLAG_NO_TERMINAL_SELECT);
+    h->has_f = true;
+    h->tail_idx = -1;
+    h->d_terminal = d_terminal;
+    h->prob_t = SelectProblem{};
+    h->prob_f = SelectProblem{};
+    if (h->has_t) {
+        if (!build_select_plan(p->pcts, (int)p->n_pcts, p->n_paths_global, p->dtype, &h->prob_t.plan))
+            return fail(h, MC_ERR_INVALID, "percentiles must be ascending and within [0, 100]");
+        if (p->tail_pct >= 0.0) {
+            for (unsigned k = 0; k < p->n_pcts; ++k) if (p->pcts[k] == p->tail_pct) h->tail_idx = (int)k;
+            if (h->tail_idx < 0) return fail(h, MC_ERR_INVALID, "tail_pct must be one of pcts");
+        }
+    } else {
+        build_select_plan(nullptr, 0, p->n_paths_global, p->dtype, &h->prob_t.plan);
+    }
+    if (!build_select_plan(p->path_pcts, (int)p->n_path_pcts, p->n_paths_global, p->dtype, &h->prob_f.plan))
+        return fail(h, MC_ERR_INVALID, "path percentiles must be ascending and within [0, 100]");
+    if ((rc = upload_plan(h, h->prob_t, 0, s))) return rc;
+    if ((rc = upload_plan(h, h->prob_f, 1, s))) return rc;
+    const size_t rows = (size_t)p->n_steps + 1, fan_n = rows * p->n_path_pcts;
+    MC_CUDA(h, h->fan.reserve(fan_n));
+    MC_CUDA(h, h->h_stage.reserve(sizeof(DeviceResult) + fan_n * 8));
+    MC_CUDA(h, cudaEventRecord(h->ev[0], s));
+    SimBuffers b{};
+    b.d_pool = d_pool; b.d_shocks = d_shocks; b.d_paths = d_paths; b.d_terminal = d_terminal;
+    b.d_partials = h->partials.p; b.d_lut = h->lut.p; b.sink = nullptr;
+    int grid = 0;
+    MC_CUDA(h, launch_simulation(*p, pf, b, h->dev, &grid, s));
+    MC_CUDA(h, cudaEventRecord(h->ev[1], s));
+    if (grid > SMALL_MAX_PARTIALS) return MC_OK;          // cannot happen at these sizes; the general path redoes the job
+    SmallArgs a{};
+    a.paths = d_paths; a.dtype = p->dtype; a.n = p->n_paths; a.ld = p->paths_ld ? p->paths_ld : p->n_paths;
+    a.rows = (unsigned int)rows;
+    a.plan_t = h->prob_t.d_plan; a.plan_f = h->prob_f.d_plan;
+    a.n_pcts = h->has_t ? (int)p->n_pcts : 0; a.n_path_pcts = (int)p->n_path_pcts; a.tail_idx = h->tail_idx;
+    a.partials = h->partials.p; a.n_partials = grid; a.center = p->s0;
+    a.res = h->res.p; a.fan = h->fan.p; a.host_out = h->h_stage.p;
+    MC_CUDA(h, launch_small_rows(a, s));
+    MC_CUDA(h, cudaEventRecord(h->ev[2], s));
+    MC_CUDA(h, cudaStreamSynchronize(s));
+    DeviceResult d;
+    memcpy(&d, h->h_stage.p, sizeof(d));
+    memset(r, 0, sizeof(*r));
+    r->n = d.n; r->n_above = d.n_above; r->mean = d.mean; r->std = d.std; r->min = d.vmin; r->max = d.vmax;
+    if (h->has_t) {
+        memcpy(r->pct, d.pct, sizeof(d.pct));
+        memcpy(r->pct_lo, d.pct_lo, sizeof(d.pct_lo));
+        memcpy(r->pct_hi, d.pct_hi, sizeof(d.pct_hi));
+    }
+    r->tail_count = d.tail_count; r->tail_sum = d.tail_sum;
+    if (h_fan) memcpy(h_fan, h->h_stage.p + sizeof(DeviceResult), fan_n * 8);       // already [pct][row]
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]) == cudaSuccess) r->sim_ms = ms;
+    if (cudaEventElapsedTime(&ms, h->ev[0], h->ev[2]) == cudaSuccess) r->total_ms = ms;
+    r->launches = 2;
+    *done = true;
     return MC_OK;
 }
 
@@ -1057,6 +1141,11 @@ int mc_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void*
     if (p->n_paths != p->n_paths_global || p->path_offset + p->n_paths < p->n_paths || p->n_ranks > 1)
         return fail(h, MC_ERR_INVALID, "mc_run is single-rank: n_paths must equal n_paths_global");
     MC_DEVICE(h);
+    if (small_eligible(*p) && small_rows_smem(p->dtype, p->n_paths) <= (size_t)h->dev.max_smem_optin - 2048 && h_result) {
+        bool done = false;
+        int rc = small_run(h, p, pf, d_pool, d_shocks, d_paths, d_terminal, h_result, h_fan, s, &done);
+        if (rc || done) return rc;
+    }
     mc_params generic = *p;
     if (fused_eligible(*p) && !(h->peers_attached && h->peers.n_ranks != 1)) {
         if (!h_result) return fail(h, MC_ERR_INVALID, "h_result is NULL");

@@ -456,7 +456,7 @@ __global__ void debug_shocks32_kernel(const Sim32Args a, float* out) {
         for (int i = threadIdx.x; i < DIR_COUNT; i += blockDim.x) s_lut[i] = a.lut[i];
     }
     __syncthreads();
-    constexpr int K = SHOCK == MC_SHOCK_NORMAL ? 8 : 5;
+    constexpr int K = SHOCK == MC_SHOCK_NORMAL ? 8 : (SHOCK == SHOCK_NORMAL_FULL ? 4 : 5);
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
     const uint32_t n_calls = (a.n_steps + K - 1) / K;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n_paths;
@@ -467,6 +467,8 @@ __global__ void debug_shocks32_kernel(const Sim32Args a, float* out) {
             float z[8];
             if (SHOCK == MC_SHOCK_NORMAL) {
                 normals8(w, lut_base, z);
+            } else if (SHOCK == SHOCK_NORMAL_FULL) {
+                normals4_full(w, z);
             } else {
                 const float gf[5] = {boot_g(w.x), boot_g(w.y), boot_g(w.z), boot_g(w.w), boot_g4(w)};
 #pragma unroll
@@ -676,8 +678,8 @@ static cudaError_t launch32_t(Sim32Args& a, const DeviceInfo& dev, int* grid, cu
     const unsigned long long items = (a.n_paths + V - 1) / V;      // threads' worth of work
     int block;
     size_t smem;
-    if (SHOCK == MC_SHOCK_NORMAL) {
-        smem = (size_t)DIR_COUNT * sizeof(float2);
+    if (SHOCK == MC_SHOCK_NORMAL || SHOCK == SHOCK_NORMAL_FULL) {
+        smem = SHOCK == MC_SHOCK_NORMAL ? (size_t)DIR_COUNT * sizeof(float2) : 0;
         block = items >= 512ull * dev.sm_count ? g_tune_nblock.load() : 128;
     } else {
         block = items >= 1024ull * dev.sm_count ? 1024 : 256;
@@ -730,6 +732,7 @@ static cudaError_t launch_sim32(const mc_params& p, const SimBuffers& b, const D
                                 cudaStream_t s) {
     Sim32Args a = make_args32(p, b);
     if (p.shock == MC_SHOCK_NORMAL) {
+        if (p.flags & MC_FLAG_FULL_RES_NORMALS) return launch32_var<SHOCK_NORMAL_FULL, TAB_GLOBAL>(a, p, dev, grid, s);
         if (!b.d_lut) return cudaErrorInvalidValue;
         return launch32_var<MC_SHOCK_NORMAL, TAB_SMEM>(a, p, dev, grid, s);
     }
@@ -860,7 +863,9 @@ cudaError_t launch_debug_shocks(const mc_params& p, const void* d_pool, const fl
     const Sim32Args a = make_args32(p, b);
     int grid = (int)((p.n_paths + 255) / 256 < 4096 ? (p.n_paths + 255) / 256 : 4096);
     if (grid < 1) grid = 1;
-    if (p.shock == MC_SHOCK_NORMAL) {
+    if (p.shock == MC_SHOCK_NORMAL && (p.flags & MC_FLAG_FULL_RES_NORMALS)) {
+        debug_shocks32_kernel<SHOCK_NORMAL_FULL><<<grid, 256, 0, stream>>>(a, static_cast<float*>(d_out));
+    } else if (p.shock == MC_SHOCK_NORMAL) {
         if (!d_lut) return cudaErrorInvalidValue;
         debug_shocks32_kernel<MC_SHOCK_NORMAL><<<grid, 256, DIR_COUNT * sizeof(float2), stream>>>(a, static_cast<float*>(d_out));
     } else if (p.shock == MC_SHOCK_BOOTSTRAP && boot32_eligible(p)) {

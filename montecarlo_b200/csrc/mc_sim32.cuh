@@ -43,14 +43,16 @@ enum { TAB_GLOBAL = 0, TAB_SMEM = 1, TAB_SMEM8 = 2 };     // where the bootstrap
 template <int SHOCK, int VAR, int TAB, bool TAIL, typename Emit>
 __device__ __forceinline__ void advance(const Sim32Args& a, const u32x4& w, uint32_t table_base, int table_shift,
                                         float sigr, int limit, float& y, float& v, Emit emit) {
-    if (SHOCK == MC_SHOCK_NORMAL) {
+    if (SHOCK == MC_SHOCK_NORMAL || SHOCK == SHOCK_NORMAL_FULL) {
         const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+        constexpr int PAIRS = SHOCK == MC_SHOCK_NORMAL ? 4 : 2;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < PAIRS; ++k) {
             if (TAIL && 2 * k >= limit) break;
-            float c, s;
-            direction_of(ww[k], table_base, c, s);
-            const float rs = rho20(ww[k]) * sigr;          // sigr = sqrt(2 ln 2) [* sigma]
+            float c, s, rho;
+            if (SHOCK == MC_SHOCK_NORMAL) { direction_of(ww[k], table_base, c, s); rho = rho20(ww[k]); }
+            else pair_full(ww[2 * k], ww[2 * k + 1], rho, c, s);
+            const float rs = rho * sigr;                   // sigr = sqrt(2 ln 2) [* sigma]
             if (VAR == MC_VAR_CONST) {
                 y = fmaf(rs, c, y);
                 emit(2 * k, y);
@@ -107,11 +109,11 @@ __device__ __forceinline__ void advance(const Sim32Args& a, const u32x4& w, uint
 // and, optionally, the caller's fixed-bin histogram, both in shared memory: one shared atomic per PATH each,
 // flushed once per block.  Moments are then taken by the closing pass, not here.
 template <int SHOCK, int VAR, bool STORE, int V, int TAB, bool SINK>
-__global__ void __launch_bounds__(SHOCK == MC_SHOCK_NORMAL ? 512 : 1024) sim32_kernel(const __grid_constant__ Sim32Args a) {
+__global__ void __launch_bounds__(SHOCK != MC_SHOCK_BOOTSTRAP ? 512 : 1024) sim32_kernel(const __grid_constant__ Sim32Args a) {
     static_assert(!SINK || (!STORE && V == 1), "the sink rides on the kernels that keep no paths");
     extern __shared__ __align__(16) unsigned char smem_dyn[];
     __shared__ BlockPartial s_warp[SINK ? 1 : 32];
-    constexpr int K = SHOCK == MC_SHOCK_NORMAL ? 8 : 5;
+    constexpr int K = SHOCK == MC_SHOCK_NORMAL ? 8 : (SHOCK == SHOCK_NORMAL_FULL ? 4 : 5);
     constexpr bool FUSED_SUM = SHOCK == MC_SHOCK_NORMAL && VAR == MC_VAR_CONST && !STORE;
 
     uint32_t table_base = (uint32_t)__cvta_generic_to_shared(smem_dyn);
@@ -119,6 +121,8 @@ __global__ void __launch_bounds__(SHOCK == MC_SHOCK_NORMAL ? 512 : 1024) sim32_k
     float2* s_tab = reinterpret_cast<float2*>(smem_dyn);
     if (SHOCK == MC_SHOCK_NORMAL) {
         for (int i = threadIdx.x; i < DIR_COUNT; i += blockDim.x) s_tab[i] = a.lut[i];
+    } else if (SHOCK == SHOCK_NORMAL_FULL) {
+        // no table: directions through MUFU
     } else if (TAB != TAB_GLOBAL) {
         const int lc = TAB == TAB_SMEM8 ? 3 : a.table_lc;
         for (uint32_t i = threadIdx.x; i < (a.pool_len << lc); i += blockDim.x) {

@@ -81,6 +81,8 @@ class SimSpec:
     hist_bins: int = 0
     hist_range: Optional[Tuple[float, float]] = None    # None -> (min, max) like np.histogram
     portfolio: Optional[PortfolioSpec] = None
+    full_res_normals: bool = False  # fp32 normal shocks from full 32-bit uniforms (4 per Philox call, |z| <= 6.66) instead of
+                                    # the default 8 per call (|z| <= 5.27, P(|z| > 5) 27 % low): MC_FLAG_FULL_RES_NORMALS
     pool_len: int = 0
     _pf_arrays: dict = field(default=None, repr=False, compare=False)
 
@@ -110,6 +112,8 @@ class SimSpec:
             raise ValueError("tail_pct must be one of pcts")
         if self.portfolio is not None and (self.shock == "bootstrap" or self.var_model != "const"):
             raise ValueError("portfolio mode needs normal/injected shocks and var_model='const'")
+        if self.full_res_normals and self.portfolio is not None and self.dtype == "float32":
+            raise ValueError("full_res_normals: single-asset kernels only (float64 portfolios already draw from 32-bit uniforms)")
 
 
 def shard_range(n_global: int, rank: int, world: int) -> Tuple[int, int]:
@@ -146,6 +150,8 @@ def make_params(spec: SimSpec, path_offset: int = 0, n_local: Optional[int] = No
         flags |= L.FLAG_NO_TERMINAL_SELECT
     if paths_volatile:
         flags |= L.FLAG_PATHS_VOLATILE
+    if spec.full_res_normals and spec.shock == "normal":
+        flags |= L.FLAG_FULL_RES_NORMALS
     p.flags = flags
     p.seed = spec.seed & 0xFFFFFFFFFFFFFFFF
     p.s0 = spec.s0

@@ -63,8 +63,8 @@ def mantissa_float(u):
     return ((u >> np.uint32(9)) | np.uint32(0x3F800000)).view(np.float32)
 
 
-def normals_per_call(dtype) -> int:
-    return 8 if np.dtype(dtype) == np.float32 else 4
+def normals_per_call(dtype, full_res: bool = False) -> int:
+    return 8 if (np.dtype(dtype) == np.float32 and not full_res) else 4
 
 
 DIR_BITS = 12
@@ -97,8 +97,25 @@ def _pair_f32(word):
     return r * _DIR[0][d], r * _DIR[1][d]
 
 
-def normals_from_words(w, dtype):
-    """All normals of one call (list of arrays): 8 for float32, 4 for float64."""
+TWO_PI_F = float(np.float32(6.28318530717958647692))
+THREE_PI_F = float(np.float32(9.42477796076937971538))
+
+
+def _pair_f32_full(wr, wd):
+    """MC_FLAG_FULL_RES_NORMALS (mc_rng.cuh: pair_full): radius from all 32 bits of one word -- v1 = fl32(fl32(u) 2^-32 +
+    2^-32), one fused rounding --, direction theta = fl32(m 2 pi - 3 pi) from the top 23 bits of the next word."""
+    f = np.asarray(wr, dtype=np.uint32).astype(np.float32).astype(np.float64)          # cvt.rn.f32.u32
+    v1 = (f * 2.0 ** -32 + 2.0 ** -32).astype(np.float32).astype(np.float64)           # exact in fp64, then one rounding
+    m = mantissa_float(wd).astype(np.float64)
+    th = (m * TWO_PI_F - THREE_PI_F).astype(np.float32).astype(np.float64)
+    r = np.sqrt(-2.0 * np.log(v1))
+    return r * np.cos(th), r * np.sin(th)
+
+
+def normals_from_words(w, dtype, full_res: bool = False):
+    """All normals of one call (list of arrays): 8 for float32 (4 at full resolution), 4 for float64."""
+    if np.dtype(dtype) == np.float32 and full_res:
+        return list(_pair_f32_full(w[0], w[1])) + list(_pair_f32_full(w[2], w[3]))
     if np.dtype(dtype) == np.float32:
         out = []
         for k in range(4):
@@ -114,16 +131,16 @@ def normals_from_words(w, dtype):
 
 
 def normal_shocks(seed: int, path_offset: int, n_paths: int, n_steps: int,
-                  dtype=np.float32, n_assets: int = 1):
+                  dtype=np.float32, n_assets: int = 1, full_res: bool = False):
     """Z[t, i] (single asset) or Z[t, a, i] (n_assets>1), float64 values, exactly the
     draws the device makes for global paths path_offset..path_offset+n_paths-1."""
     pid = np.arange(path_offset, path_offset + n_paths, dtype=np.uint64)
-    k = normals_per_call(dtype)
+    k = normals_per_call(dtype, full_res and n_assets == 1)
     if n_assets == 1:
         n_calls = (n_steps + k - 1) // k
         z = np.empty((n_calls * k, n_paths), dtype=np.float64)
         for j in range(n_calls):
-            z[k * j:k * (j + 1)] = normals_from_words(path_words(seed, pid, j), dtype)
+            z[k * j:k * (j + 1)] = normals_from_words(path_words(seed, pid, j), dtype, full_res)
         return z[:n_steps]
     q_per_step = (n_assets + k - 1) // k
     z = np.empty((n_steps, q_per_step * k, n_paths), dtype=np.float64)

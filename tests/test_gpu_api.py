@@ -55,8 +55,10 @@ def test_drop_in_contract():
 
 
 def test_statistical_parity_with_reference_c1(golden_dir):
-    """BASELINE config 1 (10k x 252): device RNG vs the reference run under np.random.seed(42);
-    agreement within 4 standard errors of the difference of two independent samples."""
+    """BASELINE config 1 (10k x 252): device RNG vs the reference run under np.random.seed(42).  north_star (b):
+    mean, std and percentiles within 3 standard errors (of the difference of two independent samples) -- the twelve
+    scalar comparisons below.  The fan chart adds 5 x 252 strongly correlated comparisons: at 3 SE each, three to four
+    would exceed the bound by chance alone, so its bound is on the maximum (4.5 SE) and on the rms (2 SE)."""
     import os
     g = np.load(os.path.join(golden_dir, "ref_c1_seed42.npz"))
     import pandas as pd
@@ -65,9 +67,9 @@ def test_statistical_parity_with_reference_c1(golden_dir):
     res = garch_monte_carlo(df, n, int(g["n_days"]), s0, seed=7, dtype="float32", return_paths="numpy")
     vol = float(g["expected_vol"])                       # std of terminal / s0 * 100
     se_mean = vol / math.sqrt(n) * math.sqrt(2)
-    assert abs(res["expected_return"] - float(g["expected_return"])) < 4 * se_mean
-    assert abs(res["expected_vol"] / vol - 1) < 4 * math.sqrt(2) * 1.5 / math.sqrt(n)      # heavy-ish tails
-    assert abs(res["prob_profit"] - float(g["prob_profit"])) < 4 * 100 * math.sqrt(0.5 / n)
+    assert abs(res["expected_return"] - float(g["expected_return"])) < 3 * se_mean
+    assert abs(res["expected_vol"] / vol - 1) < 3 * math.sqrt(2) * 1.5 / math.sqrt(n)      # heavy-ish tails
+    assert abs(res["prob_profit"] - float(g["prob_profit"])) < 3 * 100 * math.sqrt(0.5 / n)
     ref_p = g["percentiles"]
     final = np.sort(res["final_prices"])
     for i, p in enumerate(port.REF_TERMINAL_PCTS):
@@ -77,7 +79,7 @@ def test_statistical_parity_with_reference_c1(golden_dir):
         w = max(50, int(0.01 * n))
         dens = (2 * w / n) / (final[min(n - 1, k + w)] - final[max(0, k - w)])
         se = math.sqrt(q * (1 - q) / n) / dens * math.sqrt(2)
-        assert abs(res["percentiles"][f"p{p}"] - ref_p[i]) < 4 * se, p
+        assert abs(res["percentiles"][f"p{p}"] - ref_p[i]) < 3 * se, p
     # fan chart: every time step's five quantiles within 4 SE of the difference of two samples
     fan_ref = g["path_percentiles"]
     rows = np.sort(res["paths"][1:], axis=1)                 # [T, n]
