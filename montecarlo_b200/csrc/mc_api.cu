@@ -596,9 +596,12 @@ int small_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const vo
     a.n_pcts = h->has_t ? (int)p->n_pcts : 0; a.n_path_pcts = (int)p->n_path_pcts; a.tail_idx = h->tail_idx;
     a.partials = h->partials.p; a.n_partials = grid; a.center = p->s0;
     a.res = h->res.p; a.fan = h->fan.p; a.host_out = h->h_stage.p;
+    a.bad = h->h_pending.p;
+    *h->h_pending.p = 0u;
     MC_CUDA(h, launch_small_rows(a, s));
     MC_CUDA(h, cudaEventRecord(h->ev[2], s));
     MC_CUDA(h, cudaStreamSynchronize(s));
+    if (*h->h_pending.p != 0u) return MC_OK;               // never seen; the general path redoes the job
     DeviceResult d;
     memcpy(&d, h->h_stage.p, sizeof(d));
     memset(r, 0, sizeof(*r));

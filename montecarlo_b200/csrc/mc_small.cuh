@@ -21,6 +21,7 @@ struct SmallArgs {
     DeviceResult* res;            // device result block
     double* fan;                  // device [rows][n_path_pcts]
     unsigned char* host_out;      // pinned host: DeviceResult, then the fan chart as [n_path_pcts][rows] doubles
+    unsigned int* bad;            // pinned host flag: a row's selection found an inconsistency (the general path redoes the job)
 };
 size_t small_rows_smem(int dtype, unsigned long long n);
 cudaError_t launch_small_rows(const SmallArgs& a, cudaStream_t s);

@@ -169,6 +169,8 @@ class Engine:
                 return x
             return x.to(device=self.device, dtype=dtype).contiguous()
         host = torch.from_numpy(np.ascontiguousarray(x)).to(dtype)
+        if host.numel() * host.element_size() <= (1 << 16):
+            return host.to(self.device)                  # small (a bootstrap pool): pinning it costs more than the copy
         return host.pin_memory().to(self.device, non_blocking=True)
 
     # ------------------------------------------------------------------ main entry

@@ -217,3 +217,66 @@ def test_terminal_given_runs_the_staged_selection_without_a_simulation(engine):
     assert abs(res.mean - v.mean()) < 1e-12 * v.mean()
     assert np.array_equal(hist.astype(np.int64), np.histogram(v, bins=77, range=(30.0, 300.0))[0])
     assert torch.equal(term, torch.tensor(x, device=engine.device))          # untouched
+
+
+# ---------------------------------------------------------------- the reference's own call sizes: two launches
+@pytest.mark.parametrize("dtype", ["float64", "float32"])
+@pytest.mark.parametrize("n,t", [(1, 1), (2, 3), (3, 5), (1000, 20), (5000, 60), (10_000, 252), (16_384, 7), (777, 1)])
+def test_small_jobs_take_two_launches_and_equal_the_general_path(engine, dtype, n, t):
+    """app.py:1189 / 1195 (5..60 days, 500..5000 simulations) and BASELINE configs[0]: simulation kernel + one block per
+    row sorting in shared memory (csrc/mc_small.cu).  Asking for a histogram as well sends the same job down the
+    general staged path: order statistics, fan chart, counts, extremes AND mean / std must be bit-identical."""
+    pool = _pool()
+    kw = dict(n_paths=n, n_steps=t, s0=100.0, var0=port.initial_variance(0.02 * np.sqrt(252)), dtype=dtype, seed=77 + n,
+              store_paths=True, fan_chart=True)
+    small = engine.simulate(SimSpec(**kw), pool=pool)
+    general = engine.simulate(SimSpec(hist_bins=8, hist_range=(1.0, 1e4), **kw), pool=pool)
+    assert small.launches == 2 and general.launches > 10
+    assert torch.equal(small.paths, general.paths) and torch.equal(small.terminal, general.terminal)
+    assert small.pct == general.pct and small.pct_bounds == general.pct_bounds
+    for k in general.fan:
+        assert np.array_equal(small.fan[k], general.fan[k]), k
+    assert (small.n, small.n_above, small.min, small.max) == (general.n, general.n_above, general.min, general.max)
+    assert small.mean == general.mean and small.std == general.std
+    assert small.tail_count == general.tail_count
+    assert abs(small.tail_sum - general.tail_sum) <= 1e-13 * abs(general.tail_sum)
+    paths = small.paths.cpu().numpy().astype(np.float64)
+    assert np.array_equal(np.stack([small.fan[f"p{p}"] for p in port.REF_PATH_PCTS]),
+                          np.percentile(paths, port.REF_PATH_PCTS, axis=1))
+    exp = port.terminal_statistics(paths[-1], 100.0, PCTS)
+    assert list(small.pct.values()) == [exp["percentiles"][f"p{p}"] for p in PCTS]
+
+
+def test_small_path_other_models(engine):
+    """GBM with device normals and injected shocks, and the largest fp32 row (32768 paths)."""
+    for spec, shocks in ((SimSpec.gbm(32_768, 12, 100.0, 0.05, 0.2, 1 / 252, dtype="float32", seed=9, store_paths=True, fan_chart=True), None),
+                         (SimSpec.gbm(4_001, 9, 100.0, 0.05, 0.2, 1 / 252, dtype="float64", shock="injected", store_paths=True,
+                                      fan_chart=True), np.random.RandomState(1).standard_normal((9, 4_001)))):
+        out = engine.simulate(spec, shocks=shocks)
+        assert out.launches == 2
+        paths = out.paths.cpu().numpy().astype(np.float64)
+        assert np.array_equal(np.stack([out.fan[f"p{p}"] for p in port.REF_PATH_PCTS]),
+                              np.percentile(paths, port.REF_PATH_PCTS, axis=1))
+        exp = port.terminal_statistics(paths[-1], 100.0, PCTS)
+        assert list(out.pct.values()) == [exp["percentiles"][f"p{p}"] for p in PCTS]
+        s = out.summary()
+        for k in ("expected_return", "expected_vol", "prob_profit", "var_95", "cvar_95"):
+            assert abs(s[k] - exp[k]) <= 1e-9 * max(1.0, abs(exp[k])), k
+
+
+def test_small_path_rows_with_heavy_ties(engine):
+    """Three-value pool, constant variance: a handful of distinct prices per row, on both sides of the sort / narrowing split."""
+    pool = np.array([-1.0, 0.0, 1.0] * 40)
+    for n in (1500, 9000):
+        for dtype in ("float32", "float64"):
+            spec = SimSpec(n_paths=n, n_steps=6, s0=100.0, var0=1e-4, omega=0.0, alpha=0.0, beta=1.0, dtype=dtype, seed=n,
+                           store_paths=True, fan_chart=True)
+            out = engine.simulate(spec, pool=pool)
+            assert out.launches == 2
+            paths = out.paths.cpu().numpy().astype(np.float64)
+            assert np.array_equal(np.stack([out.fan[f"p{p}"] for p in port.REF_PATH_PCTS]),
+                                  np.percentile(paths, port.REF_PATH_PCTS, axis=1))
+            exp = port.terminal_statistics(paths[-1], 100.0, PCTS)
+            assert list(out.pct.values()) == [exp["percentiles"][f"p{p}"] for p in PCTS]
+            thr = np.percentile(paths[-1], 5.0)
+            assert out.tail_count == int((paths[-1] <= thr).sum())
