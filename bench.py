@@ -139,10 +139,25 @@ def hist_range(t):
     return (S0 * math.exp(-w), S0 * math.exp(w))
 
 
+_HISTORY = {}
+
+
 def synthetic_history():
-    import numpy as np
-    rs = np.random.RandomState(0)
-    return rs.normal(0.0, 0.02, 1250), 0.02 * math.sqrt(252)
+    """The caller's inputs as they sit in host memory before the call: returns, last rvol_20, and the DataFrame
+    app.py:1240 passes (built once: making it is the caller's business, not the path's)."""
+    if not _HISTORY:
+        import numpy as np
+        rs = np.random.RandomState(0)
+        _HISTORY["returns"], _HISTORY["rvol"] = rs.normal(0.0, 0.02, 1250), 0.02 * math.sqrt(252)
+    return _HISTORY["returns"], _HISTORY["rvol"]
+
+
+def synthetic_frame():
+    if "df" not in _HISTORY:
+        import pandas as pd
+        returns, rvol = synthetic_history()
+        _HISTORY["df"] = pd.DataFrame({"log_ret": returns, "rvol_20": rvol})
+    return _HISTORY["df"]
 
 
 def make_spec(workload, world):
@@ -201,9 +216,7 @@ def api_call(workload, world, group):
         corr = np.full((d, d), 0.3) + 0.7 * np.eye(d)
         return mc.simulate_portfolio(n, t, np.full(d, S0), MU, 0.15 + 0.01 * np.arange(d), np.full(d, 1 / d), corr,
                                      dt=DT, seed=SEED, group=group)
-    import pandas as pd
-    returns, rvol = synthetic_history()
-    df = pd.DataFrame({"log_ret": returns, "rvol_20": rvol})
+    df = synthetic_frame()
     if workload == "c1":        # the drop-in exactly as app.py:1240 calls it (host NumPy paths, fan chart, float64)
         return mc.garch_monte_carlo(df, n, t, S0, seed=SEED, group=group)
     if workload == "ref64":
@@ -414,8 +427,7 @@ def _reference_chunk(args):
     import numpy as np
     import pandas as pd
     fn, _ = _reference_function()
-    returns, rvol = synthetic_history()
-    df = pd.DataFrame({"log_ret": returns, "rvol_20": rvol})
+    df = synthetic_frame()
     np.random.seed(seed)
     return float(fn(df, n, t, S0)["expected_return"])
 

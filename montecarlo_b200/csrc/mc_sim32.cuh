@@ -196,7 +196,9 @@ __global__ void __launch_bounds__(SHOCK != MC_SHOCK_BOOTSTRAP ? 512 : 1024) sim3
             y[0] = a.sig * BM_RADIUS_SCALE_F * (s_cos + s_sin);
             t = n_full * K;
         } else {
-#pragma unroll 1
+            // two calls per trip when nothing is stored: the round keys and multipliers (uniform-register loads) are
+            // then fetched once per ten steps of the reference's model instead of once per five
+#pragma unroll (STORE ? 1 : 2)
             for (uint32_t j = 0; j < n_full; ++j) {
                 float px[STORE ? K : 1][V];
 #pragma unroll
