@@ -226,6 +226,15 @@ int mc_run_sharded(mc_handle* h, const mc_params* p, const mc_portfolio* pf,
  */
 int mc_stage_reads_paths(mc_handle* h);
 int mc_stage_resimulate(mc_handle* h, void* stream);
+/*
+ * The chunks of one GPU all consume the same gathered buffer, and what a handle derives from it -- brackets, narrowed
+ * intervals, the count of undecided rows -- does not depend on the handle.  One chunk (the leader) calls mc_stage_next;
+ * the others call mc_stage_adopt with the same arguments plus the leader: they copy its selection state (a few MB on
+ * the device) instead of scanning the buffers of all virtual ranks again, then enqueue their own next pass.  Same
+ * stream as the leader's call, after it.
+ */
+int mc_stage_adopt(mc_handle* h, mc_handle* leader, const void* d_gathered, uint32_t n_ranks,
+                   void* d_stage_out, int* done, void* stream);
 
 /*
  * Building blocks exposed for tests and for the callers either side of the path.
@@ -242,6 +251,8 @@ int mc_percentiles(mc_handle* h, const void* d_x, int32_t dtype, uint64_t rows, 
  * process-wide: waves of blocks per launch of the non-persistent simulation kernels (>= 1, 0: default 24) and threads
  * per block of the fused GBM kernel (128 / 256 / 512, 0: default).  Invalid values select the default. */
 int mc_debug_set_tuning(mc_handle* h, int side_cap, int no_side_lists, int waves, int nblock);
+/* pilot size (values per row) of single-rank selections, read in place from the rows; 0: default (131072).  Process-wide. */
+int mc_debug_set_pilot(uint32_t in_place_samples);
 /* counters: 0 fused runs, 1 fused runs that had to be redone by the staged selection, 2 status of the last fused
  * run, 3 re-simulations of MC_FLAG_PATHS_VOLATILE runs */
 int64_t mc_debug_counter(mc_handle* h, int which);

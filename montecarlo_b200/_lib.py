@@ -22,10 +22,10 @@ FLAG_FULL_RES_NORMALS = 32
 EXPORTS = (
     "mc_abi_version", "mc_create", "mc_destroy", "mc_last_error", "mc_run",
     "mc_stage_begin", "mc_stage_words", "mc_stage_max_words", "mc_stage_next", "mc_fetch_result",
-    "mc_stage_reads_paths", "mc_stage_resimulate",
+    "mc_stage_reads_paths", "mc_stage_resimulate", "mc_stage_adopt",
     "mc_debug_shocks", "mc_debug_philox", "mc_percentiles", "mc_histogram", "mc_prepare_inputs",
     "mc_run_batch", "mc_calibrate_garch",
-    "mc_peer_export", "mc_peer_attach", "mc_run_sharded", "mc_debug_set_tuning", "mc_debug_counter",
+    "mc_peer_export", "mc_peer_attach", "mc_run_sharded", "mc_debug_set_tuning", "mc_debug_counter", "mc_debug_set_pilot",
 )
 
 
@@ -129,6 +129,8 @@ def _declare(lib):
     lib.mc_stage_reads_paths.argtypes = [vp]
     lib.mc_stage_resimulate.restype = C.c_int
     lib.mc_stage_resimulate.argtypes = [vp, vp]
+    lib.mc_stage_adopt.restype = C.c_int
+    lib.mc_stage_adopt.argtypes = [vp, vp, vp, u32, vp, C.POINTER(C.c_int), vp]
     lib.mc_stage_words.restype = C.c_int64
     lib.mc_stage_words.argtypes = [vp]
     lib.mc_stage_max_words.restype = C.c_int64
@@ -159,6 +161,8 @@ def _declare(lib):
     lib.mc_run_sharded.argtypes = [vp, PP, PF, vp, vp, vp, vp, vp]
     lib.mc_debug_set_tuning.restype = C.c_int
     lib.mc_debug_set_tuning.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]
+    lib.mc_debug_set_pilot.restype = C.c_int
+    lib.mc_debug_set_pilot.argtypes = [u32]
     lib.mc_debug_counter.restype = C.c_int64
     lib.mc_debug_counter.argtypes = [vp, C.c_int]
 

@@ -230,9 +230,16 @@ void attach_side(mc_handle* h, SelectProblem& sp, SideBuf& buf) {
 }
 
 void setup_sampling(SelectProblem& sp, unsigned int n_ranks, bool contiguous) {
+    sp.sample_contiguous = contiguous ? 1 : 0;
+    sp.pilot_in_place = n_ranks <= 1 ? 1 : 0;
+    if (sp.pilot_in_place) {            // one rank: the brackets are taken from the rows themselves
+        const unsigned int m = pilot_in_place_size(contiguous);
+        sp.m_slot = 0;
+        sp.m_local = sp.n < m ? (unsigned int)sp.n : m;
+        return;
+    }
     sp.m_slot = sample_slot(sp.dtype, n_ranks);
     sp.m_local = sp.n < sp.m_slot ? (unsigned int)sp.n : sp.m_slot;
-    sp.sample_contiguous = contiguous ? 1 : 0;
 }
 
 int validate(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void* d_pool, const void* d_shocks,
@@ -689,7 +696,7 @@ int mc_destroy(mc_handle* h) {
 int64_t mc_stage_max_words(const mc_params* p) {
     if (!p) return -1;
     const unsigned int R = ranks_of(*p);
-    const size_t ku = (size_t)key_units(p->dtype), slot = sample_slot(p->dtype, R);
+    const size_t ku = (size_t)key_units(p->dtype), slot = R <= 1 ? 0 : sample_slot(p->dtype, R);      // one rank: pilot read in place
     const size_t rows_f = ((p->flags & MC_FLAG_FAN_CHART) && p->n_path_pcts) ? (size_t)p->n_steps + 1 : 0;
     const bool sel_t = p->n_pcts > 0 && !(p->flags & MC_FLAG_NO_TERMINAL_SELECT);
     const size_t nt_t = sel_t ? 2 * (size_t)p->n_pcts : 0, nt_f = 2 * (size_t)p->n_path_pcts;
@@ -869,8 +876,11 @@ static int enqueue_closing(mc_handle* h, unsigned long long* out, cudaStream_t s
     return MC_OK;
 }
 
+// `leader`: a handle of this process and device that has just consumed the SAME gathered buffer (fan chart by
+// regeneration: the chunks of one GPU are virtual ranks of one job).  Its merged selection state is what this handle
+// would compute from the buffer too, so it is copied instead of computed again.
 static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ranks, void* d_stage_out, int* done,
-                             cudaStream_t s) {
+                             cudaStream_t s, const mc_handle* leader = nullptr) {
     if (!h->active) return fail(h, MC_ERR_STATE, "mc_stage_next without mc_stage_begin");
     if (!d_gathered || !d_stage_out || n_ranks == 0 || !done) return fail(h, MC_ERR_INVALID, "bad stage arguments");
     if (n_ranks != ranks_of(h->p)) return fail(h, MC_ERR_INVALID, "n_ranks differs from mc_params.n_ranks");
@@ -906,13 +916,18 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
         h->launches += 1;
         if (!selecting) return enqueue_closing(h, out, s);
         const Stage0Layout L = layout_stage0(h);
-        if (h->has_t) {
-            MC_CUDA(h, launch_select_brackets(h->prob_t, g, L.off_t, 6, n_ranks, stride, h->dev.max_smem_optin, s));
-            h->launches += 1;
-        }
-        if (h->has_f) {
-            MC_CUDA(h, launch_select_brackets(h->prob_f, g, L.off_f, 7, n_ranks, stride, h->dev.max_smem_optin, s));
-            h->launches += 1;
+        if (leader) {
+            if (h->has_t) MC_CUDA(h, cudaMemcpyAsync(h->states_t.p, leader->states_t.p, sizeof(RowSel), cudaMemcpyDeviceToDevice, s));
+            if (h->has_f) MC_CUDA(h, cudaMemcpyAsync(h->states_f.p, leader->states_f.p, (size_t)h->prob_f.rows * sizeof(RowSel), cudaMemcpyDeviceToDevice, s));
+        } else {
+            if (h->has_t) {
+                MC_CUDA(h, launch_select_brackets(h->prob_t, g, L.off_t, 6, n_ranks, stride, h->dev.max_smem_optin, s));
+                h->launches += 1;
+            }
+            if (h->has_f) {
+                MC_CUDA(h, launch_select_brackets(h->prob_f, g, L.off_f, 7, n_ranks, stride, h->dev.max_smem_optin, s));
+                h->launches += 1;
+            }
         }
         h->phase = 1;
         return enqueue_pass(h, out, s);
@@ -920,14 +935,20 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
     // gathered = output of narrowing pass `pass_idx`
     const PassLayout L = layout_pass(h);
     // the counter is read only behind the second and later scans; the first one may add to whatever is there
-    if (h->pass_idx >= 2) MC_CUDA(h, cudaMemsetAsync(h->pending.p, 0, sizeof(unsigned int), s));
-    if (h->has_t) {
-        MC_CUDA(h, launch_select_scan(h->prob_t, g + L.off_t, n_ranks, stride, h->pending.p, s));
-        h->launches += 1;
-    }
-    if (h->has_f) {
-        MC_CUDA(h, launch_select_scan(h->prob_f, g + L.off_f, n_ranks, stride, h->pending.p, s));
-        h->launches += 1;
+    if (leader) {        // the leader's scan of this very buffer: its intervals and its count of undecided rows
+        if (h->has_t) MC_CUDA(h, cudaMemcpyAsync(h->states_t.p, leader->states_t.p, sizeof(RowSel), cudaMemcpyDeviceToDevice, s));
+        if (h->has_f) MC_CUDA(h, cudaMemcpyAsync(h->states_f.p, leader->states_f.p, (size_t)h->prob_f.rows * sizeof(RowSel), cudaMemcpyDeviceToDevice, s));
+        MC_CUDA(h, cudaMemcpyAsync(h->pending.p, leader->pending.p, sizeof(unsigned int), cudaMemcpyDeviceToDevice, s));
+    } else {
+        if (h->pass_idx >= 2) MC_CUDA(h, cudaMemsetAsync(h->pending.p, 0, sizeof(unsigned int), s));
+        if (h->has_t) {
+            MC_CUDA(h, launch_select_scan(h->prob_t, g + L.off_t, n_ranks, stride, h->pending.p, s));
+            h->launches += 1;
+        }
+        if (h->has_f) {
+            MC_CUDA(h, launch_select_scan(h->prob_f, g + L.off_f, n_ranks, stride, h->pending.p, s));
+            h->launches += 1;
+        }
     }
     if (h->pass_idx < 2) return enqueue_pass(h, out, s);
     // the second pass normally decides everything: go on to the closing stage and look at the counter later
@@ -1012,6 +1033,19 @@ int mc_stage_next(mc_handle* h, const void* d_gathered, uint32_t n_ranks, void* 
     if (!h) return MC_ERR_INVALID;
     std::lock_guard<std::mutex> lock(h->mu);
     return stage_next_locked(h, d_gathered, n_ranks, d_stage_out, done, static_cast<cudaStream_t>(stream));
+}
+
+int mc_stage_adopt(mc_handle* h, mc_handle* leader, const void* d_gathered, uint32_t n_ranks, void* d_stage_out, int* done,
+                   void* stream) {
+    if (!h || !leader || h == leader) return MC_ERR_INVALID;
+    std::scoped_lock lock(h->mu, leader->mu);
+    if (leader->device != h->device) return fail(h, MC_ERR_INVALID, "mc_stage_adopt: the leader lives on another device");
+    if (!h->active) return fail(h, MC_ERR_STATE, "mc_stage_adopt without mc_stage_begin");
+    // the leader has taken this step already: it is one step ahead, or finished
+    if (h->has_t != leader->has_t || h->has_f != leader->has_f || (h->has_f && h->prob_f.rows != leader->prob_f.rows) ||
+        h->prob_t.plan.n_targets != leader->prob_t.plan.n_targets)
+        return fail(h, MC_ERR_STATE, "mc_stage_adopt: the leader runs a different job");
+    return stage_next_locked(h, d_gathered, n_ranks, d_stage_out, done, static_cast<cudaStream_t>(stream), leader);
 }
 
 int mc_stage_reads_paths(mc_handle* h) {
@@ -1119,6 +1153,11 @@ int mc_debug_set_tuning(mc_handle* h, int side_cap, int no_side_lists, int waves
     h->side_cap_override = side_cap;
     h->no_side_lists = no_side_lists != 0;
     set_sim_tuning(waves, nblock);
+    return MC_OK;
+}
+
+int mc_debug_set_pilot(uint32_t in_place_samples) {
+    set_pilot_in_place_size(in_place_samples);
     return MC_OK;
 }
 

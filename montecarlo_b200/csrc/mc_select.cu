@@ -25,6 +25,8 @@
 // contraction so results are bit-identical to np.percentile on the same values.
 #include <math.h>
 
+#include <atomic>
+
 #include "mc_launch.cuh"
 #include "mc_select.cuh"
 
@@ -89,6 +91,14 @@ unsigned int sample_slot(int dtype, unsigned int n_ranks) {
     return s < 64 ? 64 : s;
 }
 
+// Single-rank problems read their pilot in place.  Contiguous (iid columns: the first m values of a row): 131072 --
+// the brackets come out half as wide as with the 32768 a stage buffer carries, pass 1 sets aside half as many values
+// (4.5 % of a row instead of 9 %: less queue / ring / side-list work, and pass 2 reads half as much).  Strided
+// (arbitrary data): 32768, one 32-byte sector per sample.
+static std::atomic<unsigned int> g_pilot_direct{131072u};
+unsigned int pilot_in_place_size(bool contiguous) { return contiguous ? g_pilot_direct.load() : (unsigned int)SEL_SAMPLE_MAX; }
+void set_pilot_in_place_size(unsigned int m) { g_pilot_direct.store(m >= 1024u && m <= (1u << 22) ? m : 131072u); }
+
 template <typename Key> __device__ __forceinline__ Key key_max();
 template <> __device__ __forceinline__ uint32_t key_max<uint32_t>() { return 0xFFFFFFFFu; }
 template <> __device__ __forceinline__ uint64_t key_max<uint64_t>() { return 0xFFFFFFFFFFFFFFFFull; }
@@ -108,7 +118,7 @@ __global__ void __launch_bounds__(256) select_sample_kernel(const Real* __restri
 }
 
 cudaError_t launch_select_sample(const SelectProblem& sp, void* d_out, cudaStream_t stream) {
-    if (sp.m_local == 0 || sp.rows == 0) return cudaSuccess;
+    if (sp.m_local == 0 || sp.rows == 0 || sp.pilot_in_place) return cudaSuccess;
     if (sp.rows > 65535) return cudaErrorInvalidValue;
     const unsigned long long stride = sp.sample_contiguous ? 1ull : (sp.n / sp.m_local ? sp.n / sp.m_local : 1ull);
     dim3 grid((sp.m_local + 255) / 256, (unsigned)sp.rows);
@@ -126,6 +136,78 @@ cudaError_t launch_select_sample(const SelectProblem& sp, void* d_out, cudaStrea
 // One block per row.  The sample (all ranks' contributions) is histogrammed over its own key
 // range (4096 linear bins: float keys are log-spaced, so this resolves ~0.1 % of a typical
 // row) and each percentile's bracket is rounded OUTWARD to bin edges.
+// brackets of one row from the (summed) 4096-bin histogram of its pilot: all 256 threads of the block
+template <typename Key>
+__device__ void brackets_from_pilot_hist(const SelectPlan* __restrict__ plan, unsigned int* s_hist, unsigned int* s_warp,
+                                         unsigned long long* s_lo, unsigned long long* s_hi, unsigned long long kmin,
+                                         int sh, unsigned int m_total, RowSel& st) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // inclusive scan of the 4096 bins, 16 per thread
+    unsigned int local[PILOT_BINS / 256], run = 0;
+#pragma unroll
+    for (int k = 0; k < PILOT_BINS / 256; ++k) { run += s_hist[tid * (PILOT_BINS / 256) + k]; local[k] = run; }
+    unsigned int incl = run;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned int o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    unsigned int off = incl - run;
+    for (int w = 0; w < warp; ++w) off += s_warp[w];
+#pragma unroll
+    for (int k = 0; k < PILOT_BINS / 256; ++k) s_hist[tid * (PILOT_BINS / 256) + k] = off + local[k];
+    __syncthreads();
+
+    const int np_ = plan->n_pcts;
+    const unsigned long long KMAX = (unsigned long long)key_max<Key>();
+    if (tid < np_) {
+        const double m = (double)m_total, ng = (double)plan->n_global;
+        const double qa = (double)plan->rank[plan->pct_lo_idx[tid]] / ng;
+        const double qb = ((double)plan->rank[plan->pct_hi_idx[tid]] + 1.0) / ng;
+        const double fa = floor(qa * m - SEL_Z * sqrt(m * qa * (1.0 - qa)) - 2.0);
+        const double fb = ceil(qb * m + SEL_Z * sqrt(m * qb * (1.0 - qb)) + 2.0);
+        unsigned long long lo = 0ull, hi = KMAX;
+        auto bin_of_rank = [&](unsigned int r) {       // first bin with cum > r
+            int a = 0, b = PILOT_BINS - 1;
+            while (a < b) { const int mid = (a + b) >> 1; if (s_hist[mid] > r) b = mid; else a = mid + 1; }
+            return a;
+        };
+        if (fa >= 0.0 && m_total) lo = kmin + ((unsigned long long)bin_of_rank((unsigned int)fa) << sh);
+        if (fb < m && m_total) {
+            const unsigned long long span = ((unsigned long long)(bin_of_rank((unsigned int)fb) + 1) << sh) - 1ull;
+            hi = span > KMAX - kmin ? KMAX : kmin + span;
+        }
+        s_lo[tid] = lo; s_hi[tid] = hi;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int iv_of_pct[MC_MAX_PCTS];
+        int n_iv = 0;
+        for (int k = 0; k < np_; ++k) {
+            if (n_iv && s_lo[k] <= st.hi[n_iv - 1]) {             // overlaps the previous bracket: merge
+                if (s_hi[k] > st.hi[n_iv - 1]) st.hi[n_iv - 1] = s_hi[k];
+            } else {
+                st.lo[n_iv] = s_lo[k]; st.hi[n_iv] = s_hi[k];
+                ++n_iv;
+            }
+            iv_of_pct[k] = n_iv - 1;
+        }
+        for (int gix = 0; gix < n_iv; ++gix) {
+            st.shift[gix] = max(0, bit_length(st.hi[gix] - st.lo[gix]) - SEL_BIN_BITS);
+            st.mode[gix] = IV_HIST;
+            st.below[gix] = 0ull;
+        }
+        for (int k = 0; k < np_; ++k) {
+            st.target_iv[plan->pct_lo_idx[k]] = iv_of_pct[k];
+            st.target_iv[plan->pct_hi_idx[k]] = iv_of_pct[k];
+        }
+        st.n_iv = n_iv;
+        st.below_known = 0;
+    }
+}
+
 template <typename Key>
 __global__ void __launch_bounds__(256) select_bracket_kernel(const SelectPlan* __restrict__ plan,
                                                              const unsigned long long* __restrict__ g,
@@ -171,77 +253,81 @@ __global__ void __launch_bounds__(256) select_bracket_kernel(const SelectPlan* _
         for (unsigned int i = tid; i < m_r; i += 256) atomicAdd(&s_hist[(unsigned int)(((unsigned long long)src[i] - kmin) >> sh)], 1u);
     }
     __syncthreads();
-    // inclusive scan of the 4096 bins, 16 per thread
-    unsigned int local[PILOT_BINS / 256], run = 0;
-#pragma unroll
-    for (int k = 0; k < PILOT_BINS / 256; ++k) { run += s_hist[tid * (PILOT_BINS / 256) + k]; local[k] = run; }
-    unsigned int incl = run;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const unsigned int o = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += o;
-    }
-    if (lane == 31) s_warp[warp] = incl;
-    __syncthreads();
-    unsigned int off = incl - run;
-    for (int w = 0; w < warp; ++w) off += s_warp[w];
-#pragma unroll
-    for (int k = 0; k < PILOT_BINS / 256; ++k) s_hist[tid * (PILOT_BINS / 256) + k] = off + local[k];
-    __syncthreads();
+    brackets_from_pilot_hist<Key>(plan, s_hist, s_warp, s_lo, s_hi, kmin, sh, m_total, states[row]);
+}
 
-    const int np_ = plan->n_pcts;
-    const unsigned long long KMAX = (unsigned long long)key_max<Key>();
-    if (tid < np_) {
-        const double m = (double)m_total, ng = (double)plan->n_global;
-        const double qa = (double)plan->rank[plan->pct_lo_idx[tid]] / ng;
-        const double qb = ((double)plan->rank[plan->pct_hi_idx[tid]] + 1.0) / ng;
-        const double fa = floor(qa * m - SEL_Z * sqrt(m * qa * (1.0 - qa)) - 2.0);
-        const double fb = ceil(qb * m + SEL_Z * sqrt(m * qb * (1.0 - qb)) + 2.0);
-        unsigned long long lo = 0ull, hi = KMAX;
-        auto bin_of_rank = [&](unsigned int r) {       // first bin with cum > r
-            int a = 0, b = PILOT_BINS - 1;
-            while (a < b) { const int mid = (a + b) >> 1; if (s_hist[mid] > r) b = mid; else a = mid + 1; }
-            return a;
-        };
-        if (fa >= 0.0 && m_total) lo = kmin + ((unsigned long long)bin_of_rank((unsigned int)fa) << sh);
-        if (fb < m && m_total) {
-            const unsigned long long span = ((unsigned long long)(bin_of_rank((unsigned int)fb) + 1) << sh) - 1ull;
-            hi = span > KMAX - kmin ? KMAX : kmin + span;
-        }
-        s_lo[tid] = lo; s_hi[tid] = hi;
+// the same from a pilot read IN PLACE: the first m values of the row (stride 1) or every stride-th value
+template <typename Real>
+__global__ void __launch_bounds__(256) select_bracket_in_place_kernel(const SelectPlan* __restrict__ plan,
+                                                                      const Real* __restrict__ x, unsigned long long ld,
+                                                                      unsigned int m, unsigned long long stride,
+                                                                      RowSel* __restrict__ states) {
+    using Key = typename KeyT<Real>::type;
+    __shared__ unsigned int s_hist[PILOT_BINS];
+    __shared__ unsigned long long s_min[8], s_max[8];
+    __shared__ unsigned int s_warp[8];
+    __shared__ unsigned long long s_lo[MC_MAX_PCTS], s_hi[MC_MAX_PCTS];
+    const unsigned long long row = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const Real* xr = x + row * ld;
+    unsigned long long kmin = ~0ull, kmax = 0ull;
+    unsigned int i = tid;
+    for (; i + 3 * 256 < m; i += 4 * 256) {              // four loads in flight
+        const Real v0 = xr[(unsigned long long)i * stride], v1 = xr[(unsigned long long)(i + 256) * stride],
+                   v2 = xr[(unsigned long long)(i + 512) * stride], v3 = xr[(unsigned long long)(i + 768) * stride];
+        const unsigned long long k0 = key_of(v0), k1 = key_of(v1), k2 = key_of(v2), k3 = key_of(v3);
+        const unsigned long long a = k0 < k1 ? k0 : k1, b = k2 < k3 ? k2 : k3, c = k0 > k1 ? k0 : k1, d = k2 > k3 ? k2 : k3;
+        const unsigned long long lo4 = a < b ? a : b, hi4 = c > d ? c : d;
+        kmin = lo4 < kmin ? lo4 : kmin;
+        kmax = hi4 > kmax ? hi4 : kmax;
     }
+    for (; i < m; i += 256) {
+        const unsigned long long k = key_of(xr[(unsigned long long)i * stride]);
+        kmin = k < kmin ? k : kmin;
+        kmax = k > kmax ? k : kmax;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        const unsigned long long a = __shfl_down_sync(0xffffffffu, kmin, d), b = __shfl_down_sync(0xffffffffu, kmax, d);
+        kmin = a < kmin ? a : kmin;
+        kmax = b > kmax ? b : kmax;
+    }
+    if (lane == 0) { s_min[warp] = kmin; s_max[warp] = kmax; }
+    for (int k = tid; k < PILOT_BINS; k += 256) s_hist[k] = 0u;
     __syncthreads();
-    if (tid == 0) {
-        RowSel& st = states[row];
-        int iv_of_pct[MC_MAX_PCTS];
-        int n_iv = 0;
-        for (int k = 0; k < np_; ++k) {
-            if (n_iv && s_lo[k] <= st.hi[n_iv - 1]) {             // overlaps the previous bracket: merge
-                if (s_hi[k] > st.hi[n_iv - 1]) st.hi[n_iv - 1] = s_hi[k];
-            } else {
-                st.lo[n_iv] = s_lo[k]; st.hi[n_iv] = s_hi[k];
-                ++n_iv;
-            }
-            iv_of_pct[k] = n_iv - 1;
-        }
-        for (int gix = 0; gix < n_iv; ++gix) {
-            st.shift[gix] = max(0, bit_length(st.hi[gix] - st.lo[gix]) - SEL_BIN_BITS);
-            st.mode[gix] = IV_HIST;
-            st.below[gix] = 0ull;
-        }
-        for (int k = 0; k < np_; ++k) {
-            st.target_iv[plan->pct_lo_idx[k]] = iv_of_pct[k];
-            st.target_iv[plan->pct_hi_idx[k]] = iv_of_pct[k];
-        }
-        st.n_iv = n_iv;
-        st.below_known = 0;
+    kmin = s_min[0]; kmax = s_max[0];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) { kmin = s_min[w] < kmin ? s_min[w] : kmin; kmax = s_max[w] > kmax ? s_max[w] : kmax; }
+    if (m == 0) { kmin = 0; kmax = 0; }
+    const int sh = max(0, bit_length(kmax - kmin) - PILOT_BIN_BITS);
+    i = tid;
+    for (; i + 3 * 256 < m; i += 4 * 256) {              // the second read of the pilot comes from L2
+        const Real v0 = xr[(unsigned long long)i * stride], v1 = xr[(unsigned long long)(i + 256) * stride],
+                   v2 = xr[(unsigned long long)(i + 512) * stride], v3 = xr[(unsigned long long)(i + 768) * stride];
+        atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(v0) - kmin) >> sh)], 1u);
+        atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(v1) - kmin) >> sh)], 1u);
+        atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(v2) - kmin) >> sh)], 1u);
+        atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(v3) - kmin) >> sh)], 1u);
     }
+    for (; i < m; i += 256) atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(xr[(unsigned long long)i * stride]) - kmin) >> sh)], 1u);
+    __syncthreads();
+    brackets_from_pilot_hist<Key>(plan, s_hist, s_warp, s_lo, s_hi, kmin, sh, m, states[row]);
 }
 
 cudaError_t launch_select_brackets(const SelectProblem& sp, const unsigned long long* d_gathered,
                                    size_t sample_off_words, int hdr_word, unsigned int n_ranks,
                                    size_t rank_stride_words, int /*max_smem_optin*/, cudaStream_t stream) {
     if (sp.plan.n_targets == 0 || sp.rows == 0) return cudaSuccess;
+    if (sp.pilot_in_place) {
+        const unsigned long long stride = sp.sample_contiguous ? 1ull : (sp.m_local && sp.n / sp.m_local ? sp.n / sp.m_local : 1ull);
+        if (sp.dtype == MC_F64)
+            select_bracket_in_place_kernel<double><<<(unsigned)sp.rows, 256, 0, stream>>>(
+                sp.d_plan, static_cast<const double*>(sp.x), sp.ld, sp.m_local, stride, sp.d_states);
+        else
+            select_bracket_in_place_kernel<float><<<(unsigned)sp.rows, 256, 0, stream>>>(
+                sp.d_plan, static_cast<const float*>(sp.x), sp.ld, sp.m_local, stride, sp.d_states);
+        return cudaGetLastError();
+    }
     if (sp.dtype == MC_F64)
         select_bracket_kernel<uint64_t><<<(unsigned)sp.rows, 256, 0, stream>>>(sp.d_plan, d_gathered, sample_off_words,
                                                                                hdr_word, n_ranks, rank_stride_words,

@@ -31,6 +31,8 @@ struct SelectProblem {
     unsigned int m_slot;      // pilot-sample slots per row in this rank's stage-0 buffer
     unsigned int m_local;     // pilot samples this rank contributes per row (<= m_slot, <= n)
     int sample_contiguous;    // 1: first m_local values of the row (iid columns), 0: strided
+    int pilot_in_place;       // 1 (single rank): the bracket kernel reads the pilot straight from the rows -- nothing is
+                              //   copied into a stage buffer (m_slot = 0), and the pilot can be four times larger
     SelectPlan plan;          // host copy
     SelectPlan* d_plan;       // device copy
     RowSel* d_states;         // [rows]
@@ -61,6 +63,9 @@ inline size_t sample_words(const SelectProblem& sp) {                           
 }
 // pilot-sample slots per row for one rank of n_ranks
 unsigned int sample_slot(int dtype, unsigned int n_ranks);
+// pilot size of a single-rank problem read in place; 0 restores the default
+unsigned int pilot_in_place_size(bool contiguous);
+void set_pilot_in_place_size(unsigned int m);
 
 // copy this rank's pilot sample (as keys) into its stage-0 buffer
 cudaError_t launch_select_sample(const SelectProblem& sp, void* d_sample_out, cudaStream_t stream);

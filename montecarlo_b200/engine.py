@@ -112,11 +112,17 @@ class _CudaStageBackend:
     def gather_view(self, total):
         return self.gathered[:total]
 
-    def next(self, gathered, n_ranks):
+    def next(self, gathered, n_ranks, leader=None):
+        """`leader`: another backend of this GPU that has already taken this step on the same gathered buffer -- its
+        selection state is copied instead of being derived again (`mc_stage_adopt`)."""
         done = C.c_int(0)
         e = self.e
-        e.check(e.lib.mc_stage_next(e.handle, C.c_void_p(gathered.data_ptr()), n_ranks, self._ptr(self.stage),
-                                    C.byref(done), e.stream_ptr()))
+        if leader is not None and leader is not self:
+            e.check(e.lib.mc_stage_adopt(e.handle, leader.e.handle, C.c_void_p(gathered.data_ptr()), n_ranks,
+                                         self._ptr(self.stage), C.byref(done), e.stream_ptr()))
+        else:
+            e.check(e.lib.mc_stage_next(e.handle, C.c_void_p(gathered.data_ptr()), n_ranks, self._ptr(self.stage),
+                                        C.byref(done), e.stream_ptr()))
         return bool(done.value)
 
 
@@ -329,7 +335,7 @@ class Engine:
                         e.check(reads)
                     if reads:
                         e.check(e.lib.mc_stage_resimulate(e.handle, e.stream_ptr()))
-                    flags.append(b.next(gathered, vworld))
+                    flags.append(b.next(gathered, vworld, leader=backs[0]))       # one scan per GPU, shared by its chunks
                 done = all(flags)
                 if any(flags) and not done:
                     raise RuntimeError("virtual ranks disagree on the stage count")

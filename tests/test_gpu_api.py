@@ -218,13 +218,18 @@ def test_full_size_c3_portfolio_properties():
 
 
 def test_full_size_c5_materialised_fan_chart():
-    """BASELINE config 5 shape at reduced N (the full 17 GB case runs in bench.py --workload c5):
-    1M x 1024 fp32 paths stored time-major; fan chart exact on sampled rows."""
-    n, t = 1_000_000, 1024
-    res = simulate_gbm(n, t, 100.0, 0.05, 0.2, seed=9, return_paths="device")
+    """BASELINE config 5 at its full size: 4,194,304 x 1024 fp32 paths stored time-major (17.2 GB); the fan chart is
+    np.percentile's, bit for bit, on rows sampled across the horizon (the first step, where a row is one draw; the
+    middle; the end), and the terminal statistics are NumPy's on the last row."""
+    n, t = 4_194_304, 1024
+    res = simulate_gbm(n, t, 100.0, 0.05, 0.2, seed=9, return_paths="device", hist_bins=2048)
     paths = res["paths"]
     assert paths.shape == (t + 1, n) and paths.dtype == torch.float32
-    for row in (0, 1, 511, 1024):
+    last = paths[-1].cpu().numpy().astype(np.float64)
+    for p, v in zip(port.REF_TERMINAL_PCTS, np.percentile(last, port.REF_TERMINAL_PCTS)):
+        assert res["percentiles"][f"p{p}"] == v
+    assert np.array_equal(res["histogram"]["counts"], np.histogram(last, bins=2048, range=res["histogram"]["range"])[0])
+    for row in (0, 1, 2, 17, 511, 800, 1023, 1024):
         ref = np.percentile(paths[row].cpu().numpy().astype(np.float64), port.REF_PATH_PCTS)
         got = [res["path_percentiles"][f"p{p}"][row] for p in port.REF_PATH_PCTS]
         assert list(ref) == got
