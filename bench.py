@@ -249,6 +249,10 @@ def run_workload(workload, steps, warmup, world, rank, group, device, sample_clo
     import torch.distributed as dist
     from montecarlo_b200.engine import get_engine
     eng = get_engine(device)
+    if os.environ.get("MC_BENCH_PILOT"):          # tuning sweeps only (tools/gpu_sweep.sh)
+        eng.lib.mc_debug_set_pilot(int(os.environ["MC_BENCH_PILOT"]))
+    if os.environ.get("MC_BENCH_WAVES") or os.environ.get("MC_BENCH_NBLOCK"):
+        eng.debug_set_tuning(waves=int(os.environ.get("MC_BENCH_WAVES", 0)), nblock=int(os.environ.get("MC_BENCH_NBLOCK", 0)))
     spec, pool = make_spec(workload, world)
     pool_dev = eng.to_device(pool, torch.float64 if spec.dtype == "float64" else torch.float32) if pool is not None else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=eng.device)       # > 126 MB L2
