@@ -261,6 +261,30 @@ int mc_histogram(mc_handle* h, const void* d_x, int32_t dtype, uint64_t n, uint3
                  double lo, double hi, uint64_t* h_counts, void* stream);
 
 /*
+ * np.histogram(x, bins, range=(lo, hi)) WITHOUT any allocation: mc_histogram for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  This entry point has no counterpart
+ * in the reference.
+ *
+ * It needs no handle and calls no cudaMalloc / cudaFree / allocating library routine: the scratch the kernels need
+ * (bin edges, running counts) lives in one file-scope __device__ array of 84 KB that every GPU loading the library
+ * holds until the process exits (csrc/mc_static.cu).  Hence:
+ *   - at most MC_STATIC_HIST_MAX_BINS bins; more is refused with MC_ERR_INVALID and a message in `err`;
+ *   - every call on a device shares that array, which still holds the previous call's contents; the call's first
+ *     kernel clears what must start at zero.  Calls that OVERLAP on the GPU (other streams, other threads, a graph
+ *     replayed next to itself) race on it and give wrong counts: serialise them (one stream, or events);
+ *   - the first call on a device asks the runtime for the array's device address (cudaGetSymbolAddress); make that
+ *     call once before starting a capture.
+ * Asynchronous: three small kernels on `stream`, no synchronisation, nothing copied to the host.
+ *   d_x       [n] values (dtype MC_F32 / MC_F64), device memory of `device_ordinal`
+ *   d_counts  [bins] uint64, device memory, overwritten
+ *   err       caller's buffer for the error text (may be NULL), err_cap its size
+ * Counts are those of mc_histogram on the same data, bit for bit.  The calling thread's current device is restored.
+ */
+#define MC_STATIC_HIST_MAX_BINS 4096u
+int mc_histogram_static(int device_ordinal, const void* d_x, int32_t dtype, uint64_t n, uint32_t bins,
+                        double lo, double hi, uint64_t* d_counts, void* stream, char* err, uint32_t err_cap);
+
+/*
  * Input producers: what the routine reads, from raw close prices, for n_series price histories
  * in one launch.  Replaces, per history, the pandas producers of the two columns the routine reads --
  * `log_ret` (app.py:224) and `rvol_20` (app.py:233, sample std of the last 20 log returns x sqrt(252)) --, the

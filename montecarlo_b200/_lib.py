@@ -12,6 +12,7 @@ MC_ABI_VERSION = 3
 MC_MAX_PCTS = 16
 MC_MAX_PATH_PCTS = 8
 MC_MAX_ASSETS = 32
+MC_STATIC_HIST_MAX_BINS = 4096
 
 SHOCK_BOOTSTRAP, SHOCK_NORMAL, SHOCK_INJECTED = 0, 1, 2
 VAR_GARCH, VAR_CONST = 0, 1
@@ -25,7 +26,7 @@ EXPORTS = (
     "mc_stage_reads_paths", "mc_stage_resimulate", "mc_stage_adopt",
     "mc_debug_shocks", "mc_debug_philox", "mc_percentiles", "mc_histogram", "mc_prepare_inputs",
     "mc_run_batch", "mc_calibrate_garch",
-    "mc_peer_export", "mc_peer_attach", "mc_run_sharded", "mc_debug_set_tuning", "mc_debug_counter", "mc_debug_set_pilot",
+    "mc_peer_export", "mc_peer_attach", "mc_run_sharded", "mc_debug_set_tuning", "mc_debug_counter", "mc_debug_set_pilot", "mc_histogram_static",
 )
 
 
@@ -163,6 +164,8 @@ def _declare(lib):
     lib.mc_debug_set_tuning.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]
     lib.mc_debug_set_pilot.restype = C.c_int
     lib.mc_debug_set_pilot.argtypes = [u32]
+    lib.mc_histogram_static.restype = C.c_int
+    lib.mc_histogram_static.argtypes = [C.c_int, vp, i32, u64, u32, dbl, dbl, vp, vp, C.c_char_p, u32]
     lib.mc_debug_counter.restype = C.c_int64
     lib.mc_debug_counter.argtypes = [vp, C.c_int]
 

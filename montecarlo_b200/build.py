@@ -10,7 +10,7 @@ from concurrent.futures import ThreadPoolExecutor
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libmc_b200.so")
-SOURCES = ("mc_api.cu", "mc_sim.cu", "mc_select.cu", "mc_fused.cu", "mc_small.cu", "mc_inputs.cu", "mc_batch.cu", "mc_calibrate.cu")
+SOURCES = ("mc_api.cu", "mc_sim.cu", "mc_select.cu", "mc_fused.cu", "mc_small.cu", "mc_static.cu", "mc_inputs.cu", "mc_batch.cu", "mc_calibrate.cu")
 HEADERS = ("mc_common.cuh", "mc_rng.cuh", "mc_sim.cuh", "mc_sim32.cuh", "mc_select.cuh", "mc_fused.cuh", "mc_small.cuh", "mc_launch.cuh", "mc_inputs.cuh",
            os.path.join("..", "..", "include", "mc_b200.h"))
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
