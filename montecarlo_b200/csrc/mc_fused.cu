@@ -372,21 +372,30 @@ __global__ void __launch_bounds__(CLOSE_THREADS, 4) fused_closing_kernel(const F
         unsigned long long beg = (unsigned long long)blockIdx.x * per;
         if (beg > a.n) beg = a.n;
         const unsigned long long end = beg + per < a.n ? beg + per : a.n;
-        for (unsigned long long t = beg; t < end; t += CLOSE_TILE) {
-            if (t + CLOSE_TILE <= end) {           // whole tile: four loads in flight, no bounds checks
-                Real v[4];
+        // whole tiles: the loads of the NEXT tile are issued before this one is worked on (a barrier closes every tile,
+        // so without this a block waits out a full L2 / HBM latency per 4 values a thread: issue 39 %, ncu)
+        const unsigned long long n_full = (end - beg) / CLOSE_TILE;
+        Real v[4], vn[4];
+        if (n_full) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) v[k] = x[t + tid + (unsigned long long)k * CLOSE_THREADS];
+            for (int k = 0; k < 4; ++k) v[k] = x[beg + tid + (unsigned long long)k * CLOSE_THREADS];
+        }
+        for (unsigned long long q = 0; q < n_full; ++q) {
+            const unsigned long long nxt = beg + (q + 1) * CLOSE_TILE;
+            if (q + 1 < n_full) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) visit(v[k]);
-                acc.n += 4u;
-            } else {
-                for (unsigned long long i = t + tid; i < end; i += CLOSE_THREADS) { visit(x[i]); acc.n += 1u; }
+                for (int k = 0; k < 4; ++k) vn[k] = x[nxt + tid + (unsigned long long)k * CLOSE_THREADS];
             }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) visit(v[k]);
+            acc.n += 4u;
             // every thread looks at the fill level BEFORE the barrier and the barrier ORs what they saw: the last
             // one to arrive sees the final level, and nobody appends again before all have looked
             if (__syncthreads_or(*reinterpret_cast<volatile unsigned int*>(&s_stg_n) > (unsigned int)(CLOSE_STG - CLOSE_TILE))) flush();
+#pragma unroll
+            for (int k = 0; k < 4; ++k) v[k] = vn[k];
         }
+        for (unsigned long long i = beg + n_full * CLOSE_TILE + tid; i < end; i += CLOSE_THREADS) { visit(x[i]); acc.n += 1u; }   // < one tile
         __syncthreads();
         flush();
     }
@@ -444,22 +453,27 @@ __global__ void __launch_bounds__(CLOSE_THREADS, 4) fused_closing_kernel(const F
 }
 
 cudaError_t launch_fused_closing(const FusedArgs& a, int sm_count, int* grid, cudaStream_t s) {
-    // several resident blocks per SM: a block waits for its own loads at every tile
-    unsigned long long nb = (a.n + 2ull * CLOSE_TILE - 1) / (2ull * CLOSE_TILE);
-    if (nb > 8ull * sm_count) nb = 8ull * sm_count;
-    const unsigned int blocks = (unsigned int)(nb < 1 ? 1 : nb);
-    *grid = (int)blocks;
     const unsigned int bins = (a.nph_bins && !a.nph_in_sim && a.nph_bins <= CLOSE_NPH_SMEM) ? a.nph_bins : 0u;
     const size_t esz = a.dtype == MC_F64 ? 8 : 4;
     const size_t smem = bins ? ((size_t)bins + 2) * esz + (size_t)bins * 4 : 0;
     cudaError_t e;
+    // ONE wave of blocks: as many as are resident at once (each starts by copying the 8 KB membership table)
+    int per_sm = 0;
     if (a.dtype == MC_F64) {
         if ((e = ensure_dynamic_smem(fused_closing_kernel<double>, smem)) != cudaSuccess) return e;
-        fused_closing_kernel<double><<<blocks, CLOSE_THREADS, smem, s>>>(a);
+        e = resident_blocks_per_sm(fused_closing_kernel<double>, CLOSE_THREADS, smem, &per_sm);
     } else {
         if ((e = ensure_dynamic_smem(fused_closing_kernel<float>, smem)) != cudaSuccess) return e;
-        fused_closing_kernel<float><<<blocks, CLOSE_THREADS, smem, s>>>(a);
+        e = resident_blocks_per_sm(fused_closing_kernel<float>, CLOSE_THREADS, smem, &per_sm);
     }
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) per_sm = 1;
+    unsigned long long nb = (a.n + 2ull * CLOSE_TILE - 1) / (2ull * CLOSE_TILE);
+    if (nb > (unsigned long long)per_sm * sm_count) nb = (unsigned long long)per_sm * sm_count;
+    const unsigned int blocks = (unsigned int)(nb < 1 ? 1 : nb);
+    *grid = (int)blocks;
+    if (a.dtype == MC_F64) fused_closing_kernel<double><<<blocks, CLOSE_THREADS, smem, s>>>(a);
+    else fused_closing_kernel<float><<<blocks, CLOSE_THREADS, smem, s>>>(a);
     return cudaGetLastError();
 }
 
@@ -558,17 +572,27 @@ __global__ void __launch_bounds__(SEL_THREADS) fused_select_kernel(const FusedAr
         const bool in_smem = (size_t)total * sizeof(Key) <= SEL_CAND_SMEM;
         // every candidate of the slot, four loads in flight per thread: from the ranks' lists, or -- after the
         // first such sweep has copied them -- from shared memory
+        // (one flat index space over all ranks' lists: the loads from every peer are in flight together -- rank after
+        // rank, each list cost its own NVLink round trip: 51 us instead of 23 at 8 GPUs)
         auto sweep_lists = [&](auto f) {
-            for (unsigned int r = 0; r < R; ++r) {
-                const Key* src = cand_of<Key>(a, r) + off;      // rank r's own list, in rank r's memory
-                const unsigned int cnt = s_cnt[r];
-                for (unsigned int j = tid; j < cnt; j += 4u * SEL_THREADS) {
-                    Key k[4];
+            const Key* base_r[FUSED_MAX_RANKS];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) k[u] = j + u * SEL_THREADS < cnt ? __ldcg(src + j + u * SEL_THREADS) : (Key)0;
+            for (int r = 0; r < FUSED_MAX_RANKS; ++r) base_r[r] = r < (int)R ? cand_of<Key>(a, r) + off : nullptr;
+            auto locate = [&](unsigned int g) -> const Key* {        // position g of the concatenation -> its address
+                unsigned int r = 0;
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) if (j + u * SEL_THREADS < cnt) f(k[u], s_base[r] + j + u * SEL_THREADS);
-                }
+                for (int q = 1; q < FUSED_MAX_RANKS; ++q) r += (q < (int)R && g >= s_base[q]) ? 1u : 0u;
+                const Key* b = base_r[0];
+#pragma unroll
+                for (int q = 1; q < FUSED_MAX_RANKS; ++q) b = r == (unsigned)q ? base_r[q] : b;
+                return b + (g - s_base[r]);
+            };
+            for (unsigned int g = tid; g < total; g += 4u * SEL_THREADS) {
+                Key k[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) k[u] = g + u * SEL_THREADS < total ? __ldcg(locate(g + u * SEL_THREADS)) : (Key)0;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) if (g + u * SEL_THREADS < total) f(k[u], g + u * SEL_THREADS);
             }
         };
         if (tid == 0) {                 // work list: key ranges of this bin that still hold undecided targets
