@@ -107,7 +107,9 @@ typedef struct mc_params {
     double path_pcts[MC_MAX_PATH_PCTS];
     double tail_pct;            /* CVaR level in percent (reference: 5, app.py:656); <0 = none */
     uint32_t n_ranks;           /* ranks sharing n_paths_global (0 or 1 = single GPU); sizes the per-rank pilot sample */
-    uint32_t reserved0;
+    uint32_t pass_group;        /* 0 / 1: none.  g > 1 (fan chart by regeneration): g handles of this GPU are virtual ranks of one
+                                   job and write their narrowing-pass outputs into ONE buffer (mc_stage_adopt); a gathered pass
+                                   stage then holds n_ranks / g buffers.  Must divide n_ranks. */
 } mc_params;
 
 /* Portfolio description (n_assets > 1); host arrays, copied at launch. */
@@ -235,6 +237,14 @@ int mc_stage_resimulate(mc_handle* h, void* stream);
  */
 int mc_stage_adopt(mc_handle* h, mc_handle* leader, const void* d_gathered, uint32_t n_ranks,
                    void* d_stage_out, int* done, void* stream);
+/*
+ * With mc_params.pass_group = g > 1 the adopting handles also ADD their narrowing-pass output to the leader's stage
+ * buffer instead of filling their own (counts, histogram bins and candidate lists are additive): the GPU then hands
+ * the other GPUs ONE buffer per pass -- 104 MB instead of g x 104 MB at 2521 rows.  mc_stage_shared(h) tells the host
+ * which kind of buffer was just written: 1 = a shared pass output (gather the LEADER's buffer only; the next
+ * mc_stage_next / mc_stage_adopt takes n_ranks / g), 0 = one buffer per virtual rank as before.
+ */
+int mc_stage_shared(mc_handle* h);
 
 /*
  * Building blocks exposed for tests and for the callers either side of the path.

@@ -23,7 +23,7 @@ FLAG_FULL_RES_NORMALS = 32
 EXPORTS = (
     "mc_abi_version", "mc_create", "mc_destroy", "mc_last_error", "mc_run",
     "mc_stage_begin", "mc_stage_words", "mc_stage_max_words", "mc_stage_next", "mc_fetch_result",
-    "mc_stage_reads_paths", "mc_stage_resimulate", "mc_stage_adopt",
+    "mc_stage_reads_paths", "mc_stage_resimulate", "mc_stage_adopt", "mc_stage_shared",
     "mc_debug_shocks", "mc_debug_philox", "mc_percentiles", "mc_histogram", "mc_prepare_inputs",
     "mc_run_batch", "mc_calibrate_garch",
     "mc_peer_export", "mc_peer_attach", "mc_run_sharded", "mc_debug_set_tuning", "mc_debug_counter", "mc_debug_set_pilot", "mc_histogram_static",
@@ -47,7 +47,7 @@ class McParams(C.Structure):
         ("pcts", C.c_double * MC_MAX_PCTS),
         ("path_pcts", C.c_double * MC_MAX_PATH_PCTS),
         ("tail_pct", C.c_double),
-        ("n_ranks", C.c_uint32), ("reserved0", C.c_uint32),
+        ("n_ranks", C.c_uint32), ("pass_group", C.c_uint32),
     ]
 
 
@@ -132,6 +132,8 @@ def _declare(lib):
     lib.mc_stage_resimulate.argtypes = [vp, vp]
     lib.mc_stage_adopt.restype = C.c_int
     lib.mc_stage_adopt.argtypes = [vp, vp, vp, u32, vp, C.POINTER(C.c_int), vp]
+    lib.mc_stage_shared.restype = C.c_int
+    lib.mc_stage_shared.argtypes = [vp]
     lib.mc_stage_words.restype = C.c_int64
     lib.mc_stage_words.argtypes = [vp]
     lib.mc_stage_max_words.restype = C.c_int64

@@ -141,6 +141,7 @@ struct mc_handle {
     DevBuf<unsigned char> member;       // [FUSED_KB]
     DevBuf<ClosePartial> close_partials;
     DevBuf<unsigned long long> claim;   // [1]
+    unsigned long long* last_pass_out = nullptr;   // where this handle's latest narrowing pass wrote (shared within a pass group)
     unsigned long long fused_seq = 0;   // sharded runs so far (the flags of a run carry its number)
     bool fused_pending = false;         // a fused run is enqueued; mc_fetch_result reads the pinned block
     bool fused_dirty = true;            // accumulators (own histogram slots, claim counter) need zeroing
@@ -271,6 +272,8 @@ int validate(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const voi
     if (p->n_pcts > MC_MAX_PCTS || p->n_path_pcts > MC_MAX_PATH_PCTS) return fail(h, MC_ERR_INVALID, "too many percentiles");
     if (p->hist_bins > (1u << 16)) return fail(h, MC_ERR_INVALID, "hist_bins > 65536");
     if (!(p->var0 >= 0.0) || !(p->s0 == p->s0)) return fail(h, MC_ERR_INVALID, "var0 must be >= 0");
+    if (p->pass_group > 1 && (ranks_of(*p) % p->pass_group) != 0)
+        return fail(h, MC_ERR_INVALID, "pass_group must divide n_ranks");
     if ((p->flags & MC_FLAG_FULL_RES_NORMALS) && p->n_assets > 1 && p->dtype == MC_F32 && p->shock == MC_SHOCK_NORMAL)
         return fail(h, MC_ERR_INVALID, "MC_FLAG_FULL_RES_NORMALS: single-asset kernels only");
     if ((p->flags & MC_FLAG_TERMINAL_GIVEN) && (p->flags & (MC_FLAG_STORE_PATHS | MC_FLAG_FAN_CHART)))
@@ -718,6 +721,7 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
     h->active = false;
     h->fused_pending = false;
     h->p = *p;
+    h->last_pass_out = nullptr;
     h->launches = 0;
     h->phase = 0;
     h->pass_idx = 0;
@@ -835,17 +839,29 @@ static int restore_rows_if_needed(mc_handle* h, cudaStream_t s) {
     return resimulate_locked(h, s);
 }
 
-static int enqueue_pass(mc_handle* h, unsigned long long* out, cudaStream_t s) {
+unsigned int pass_group_of(const mc_params& p) { return p.pass_group > 1 ? p.pass_group : 1u; }
+
+// mc_params.pass_group > 1: the handles of one GPU that share a job (chunks of a fan chart by regeneration) write their
+// pass outputs into ONE buffer -- the leader's, which the leader clears -- so that the GPU hands the other GPUs one
+// buffer per pass instead of one per chunk.
+static int enqueue_pass(mc_handle* h, unsigned long long* out, cudaStream_t s, const mc_handle* leader = nullptr) {
     const PassLayout L = layout_pass(h);
     const bool first = h->pass_idx == 0;
     int rc = restore_rows_if_needed(h, s);
     if (rc) return rc;
+    bool zero = true;
+    if (pass_group_of(h->p) > 1 && leader) {
+        if (!leader->last_pass_out) return fail(h, MC_ERR_STATE, "shared pass output: the leader has not enqueued its pass");
+        out = leader->last_pass_out;
+        zero = false;
+    }
+    h->last_pass_out = out;
     if (h->has_t) {
-        MC_CUDA(h, launch_select_pass(h->prob_t, first, out + L.off_t, h->dev.sm_count, s));
+        MC_CUDA(h, launch_select_pass(h->prob_t, first, out + L.off_t, h->dev.sm_count, s, zero));
         h->launches += h->prob_t.n ? 1 : 0;
     }
     if (h->has_f) {
-        MC_CUDA(h, launch_select_pass(h->prob_f, first, out + L.off_f, h->dev.sm_count, s));
+        MC_CUDA(h, launch_select_pass(h->prob_f, first, out + L.off_f, h->dev.sm_count, s, zero));
         h->launches += h->prob_f.n ? 1 : 0;
     }
     h->pass_idx += 1;
@@ -883,7 +899,10 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
                              cudaStream_t s, const mc_handle* leader = nullptr) {
     if (!h->active) return fail(h, MC_ERR_STATE, "mc_stage_next without mc_stage_begin");
     if (!d_gathered || !d_stage_out || n_ranks == 0 || !done) return fail(h, MC_ERR_INVALID, "bad stage arguments");
-    if (n_ranks != ranks_of(h->p)) return fail(h, MC_ERR_INVALID, "n_ranks differs from mc_params.n_ranks");
+    {   // a gathered pass output holds one buffer per pass GROUP, every other stage one per (virtual) rank
+        const unsigned int expect = h->phase == 1 ? ranks_of(h->p) / pass_group_of(h->p) : ranks_of(h->p);
+        if (n_ranks != expect) return fail(h, MC_ERR_INVALID, "n_ranks differs from what this stage gathers (mc_params.n_ranks, pass_group)");
+    }
     MC_DEVICE(h);
     const unsigned long long* g = static_cast<const unsigned long long*>(d_gathered);
     unsigned long long* out = static_cast<unsigned long long*>(d_stage_out);
@@ -901,7 +920,7 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
             if (*h->h_pending.p != 0) {       // a bracket missed or a heavy tie: narrow again, then close again
                 if (h->pass_idx >= SEL_MAX_PASSES) return fail(h, MC_ERR_STATE, "selection did not converge");
                 h->phase = 1;
-                return enqueue_pass(h, out, s);
+                return enqueue_pass(h, out, s, leader);
             }
         }
         MC_CUDA(h, launch_merge_final(g, n_ranks, stride, p.hist_bins, h->res.p, h->hist_total.p, s));
@@ -930,7 +949,7 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
             }
         }
         h->phase = 1;
-        return enqueue_pass(h, out, s);
+        return enqueue_pass(h, out, s, leader);
     }
     // gathered = output of narrowing pass `pass_idx`
     const PassLayout L = layout_pass(h);
@@ -950,7 +969,7 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
             h->launches += 1;
         }
     }
-    if (h->pass_idx < 2) return enqueue_pass(h, out, s);
+    if (h->pass_idx < 2) return enqueue_pass(h, out, s, leader);
     // the second pass normally decides everything: go on to the closing stage and look at the counter later
     u32_to_host_kernel<<<1, 1, 0, s>>>(h->h_pending.p, h->pending.p);
     MC_CUDA(h, cudaGetLastError());
@@ -1046,6 +1065,12 @@ int mc_stage_adopt(mc_handle* h, mc_handle* leader, const void* d_gathered, uint
         h->prob_t.plan.n_targets != leader->prob_t.plan.n_targets)
         return fail(h, MC_ERR_STATE, "mc_stage_adopt: the leader runs a different job");
     return stage_next_locked(h, d_gathered, n_ranks, d_stage_out, done, static_cast<cudaStream_t>(stream), leader);
+}
+
+int mc_stage_shared(mc_handle* h) {
+    if (!h) return MC_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(h->mu);
+    return (h->active && h->phase == 1 && pass_group_of(h->p) > 1) ? 1 : 0;
 }
 
 int mc_stage_reads_paths(mc_handle* h) {

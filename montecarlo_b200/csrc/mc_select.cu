@@ -1116,10 +1116,12 @@ static cudaError_t launch_pass_real(const SelectProblem& sp, bool first, void* d
 }
 
 cudaError_t launch_select_pass(const SelectProblem& sp, bool first_pass, void* d_out, int sm_count,
-                               cudaStream_t stream) {
+                               cudaStream_t stream, bool zero_out) {
     if (sp.plan.n_targets == 0 || sp.rows == 0) return cudaSuccess;
     if (sp.rows > 65535) return cudaErrorInvalidValue;
-    cudaError_t e = cudaMemsetAsync(d_out, 0, pass_words(sp) * sizeof(unsigned long long), stream);
+    // everything a pass writes is additive (counts, histogram bins, appended candidates): several problems of one
+    // GPU may accumulate into one buffer, which only the first of them clears
+    cudaError_t e = zero_out ? cudaMemsetAsync(d_out, 0, pass_words(sp) * sizeof(unsigned long long), stream) : cudaSuccess;
     if (e != cudaSuccess || sp.n == 0) return e;
     if (sp.dtype == MC_F32) return launch_pass_f32(sp, first_pass, d_out, sm_count, stream);
     unsigned long long chunks = ((unsigned long long)sm_count * 16 + sp.rows - 1) / sp.rows;

@@ -77,7 +77,7 @@ cudaError_t launch_select_brackets(const SelectProblem& sp, const unsigned long 
 // one narrowing pass over the local values: per row and interval, counts / histogram /
 // collected candidates into d_out (layout row_slot_u32; zeroed by the callee)
 cudaError_t launch_select_pass(const SelectProblem& sp, bool first_pass, void* d_out, int sm_count,
-                               cudaStream_t stream);
+                               cudaStream_t stream, bool zero_out = true);
 // adds to *d_blocks the number of (row, chunk) blocks of the next fp32 pass that cannot work from their side
 // lists (they would stream the rows); adds rows * chunks when the problem has no side lists at all
 cudaError_t launch_side_check(const SelectProblem& sp, int sm_count, unsigned int* d_blocks, cudaStream_t stream);

@@ -313,17 +313,24 @@ class Engine:
                 lo = min(c * chunk, n_local)
                 cnt = min(chunk, n_local - lo)
                 params = make_params(spec, path_offset=offset + lo, n_local=cnt, paths_ld=buf.shape[1], n_ranks=vworld,
-                                     paths_volatile=True)
+                                     paths_volatile=True, pass_group=n_chunks)
                 backs.append(_CudaStageBackend(engines[c], params, pf, pool_t, None, buf, terminal[lo:lo + cnt], 1))
             launches = 0
             for b in backs:                      # simulate + moments + pilot sample, chunk by chunk
                 b.begin()
             done = False
+            lead = backs[0].e
             while not done:
                 words = backs[0].stage_words()
-                local = torch.cat([b.stage_view(words) for b in backs])
+                # a narrowing pass of all chunks has gone into ONE buffer, the leader's (mc_params.pass_group): this
+                # GPU is one rank of that stage; every other stage has one buffer per chunk
+                shared = n_chunks > 1 and lead.lib.mc_stage_shared(lead.handle) == 1
+                local = backs[0].stage_view(words) if shared else torch.cat([b.stage_view(words) for b in backs])
+                n_gathered = world if shared else vworld
+                if n_chunks == 1:
+                    n_gathered = world
                 if world > 1:
-                    gathered = torch.empty(vworld * words, dtype=torch.int64, device=self.device)
+                    gathered = torch.empty(n_gathered * words, dtype=torch.int64, device=self.device)
                     dist.all_gather_into_tensor(gathered, local, group=group)
                 else:
                     gathered = local
@@ -335,7 +342,7 @@ class Engine:
                         e.check(reads)
                     if reads:
                         e.check(e.lib.mc_stage_resimulate(e.handle, e.stream_ptr()))
-                    flags.append(b.next(gathered, vworld, leader=backs[0]))       # one scan per GPU, shared by its chunks
+                    flags.append(b.next(gathered, n_gathered, leader=backs[0]))   # one scan per GPU, shared by its chunks
                 done = all(flags)
                 if any(flags) and not done:
                     raise RuntimeError("virtual ranks disagree on the stage count")

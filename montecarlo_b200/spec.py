@@ -126,7 +126,7 @@ def shard_range(n_global: int, rank: int, world: int) -> Tuple[int, int]:
 
 
 def make_params(spec: SimSpec, path_offset: int = 0, n_local: Optional[int] = None,
-                paths_ld: int = 0, n_ranks: int = 1, paths_volatile: bool = False) -> L.McParams:
+                paths_ld: int = 0, n_ranks: int = 1, paths_volatile: bool = False, pass_group: int = 0) -> L.McParams:
     spec.validate()
     p = L.McParams()
     p.struct_size = C.sizeof(L.McParams)
@@ -135,6 +135,7 @@ def make_params(spec: SimSpec, path_offset: int = 0, n_local: Optional[int] = No
     p.path_offset = path_offset
     p.n_paths_global = spec.n_paths
     p.n_ranks = int(n_ranks)
+    p.pass_group = int(pass_group)
     p.paths_ld = paths_ld
     p.n_steps = spec.n_steps
     p.n_assets = 1
