@@ -234,7 +234,8 @@ void setup_sampling(SelectProblem& sp, unsigned int n_ranks, bool contiguous) {
     sp.sample_contiguous = contiguous ? 1 : 0;
     sp.pilot_in_place = n_ranks <= 1 ? 1 : 0;
     if (sp.pilot_in_place) {            // one rank: the brackets are taken from the rows themselves
-        const unsigned int m = pilot_in_place_size(contiguous);
+        // one row (terminal values): a single block reads the pilot, and pass 1 over one row is cheap anyway
+        const unsigned int m = sp.rows == 1 ? (unsigned int)SEL_SAMPLE_MAX : pilot_in_place_size(contiguous);
         sp.m_slot = 0;
         sp.m_local = sp.n < m ? (unsigned int)sp.n : m;
         return;

@@ -272,14 +272,17 @@ __global__ void __launch_bounds__(256) select_bracket_in_place_kernel(const Sele
     const Real* xr = x + row * ld;
     unsigned long long kmin = ~0ull, kmax = 0ull;
     unsigned int i = tid;
-    for (; i + 3 * 256 < m; i += 4 * 256) {              // four loads in flight
-        const Real v0 = xr[(unsigned long long)i * stride], v1 = xr[(unsigned long long)(i + 256) * stride],
-                   v2 = xr[(unsigned long long)(i + 512) * stride], v3 = xr[(unsigned long long)(i + 768) * stride];
-        const unsigned long long k0 = key_of(v0), k1 = key_of(v1), k2 = key_of(v2), k3 = key_of(v3);
-        const unsigned long long a = k0 < k1 ? k0 : k1, b = k2 < k3 ? k2 : k3, c = k0 > k1 ? k0 : k1, d = k2 > k3 ? k2 : k3;
-        const unsigned long long lo4 = a < b ? a : b, hi4 = c > d ? c : d;
-        kmin = lo4 < kmin ? lo4 : kmin;
-        kmax = hi4 > kmax ? hi4 : kmax;
+    constexpr int PU = 16;                               // loads in flight per thread: the block is alone with its row's latency
+    for (; i + (PU - 1) * 256 < m; i += PU * 256) {
+        Real v[PU];
+#pragma unroll
+        for (int u = 0; u < PU; ++u) v[u] = xr[(unsigned long long)(i + u * 256) * stride];
+#pragma unroll
+        for (int u = 0; u < PU; ++u) {
+            const unsigned long long k = key_of(v[u]);
+            kmin = k < kmin ? k : kmin;
+            kmax = k > kmax ? k : kmax;
+        }
     }
     for (; i < m; i += 256) {
         const unsigned long long k = key_of(xr[(unsigned long long)i * stride]);
@@ -301,13 +304,16 @@ __global__ void __launch_bounds__(256) select_bracket_in_place_kernel(const Sele
     if (m == 0) { kmin = 0; kmax = 0; }
     const int sh = max(0, bit_length(kmax - kmin) - PILOT_BIN_BITS);
     i = tid;
-    for (; i + 3 * 256 < m; i += 4 * 256) {              // the second read of the pilot comes from L2
-        const Real v0 = xr[(unsigned long long)i * stride], v1 = xr[(unsigned long long)(i + 256) * stride],
-                   v2 = xr[(unsigned long long)(i + 512) * stride], v3 = xr[(unsigned long long)(i + 768) * stride];
-        atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(v0) - kmin) >> sh)], 1u);
-        atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(v1) - kmin) >> sh)], 1u);
-        atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(v2) - kmin) >> sh)], 1u);
-        atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(v3) - kmin) >> sh)], 1u);
+    if (kmin == kmax) {          // a constant row (row 0 of the paths is all s0, app.py:613): every sample in bin 0 -- without
+        if (tid == 0) s_hist[0] = m;      // 131072 atomics on one shared-memory word (230 us for that one block)
+        i = m;
+    }
+    for (; i + (PU - 1) * 256 < m; i += PU * 256) {      // the second read of the pilot comes from L2
+        Real v[PU];
+#pragma unroll
+        for (int u = 0; u < PU; ++u) v[u] = xr[(unsigned long long)(i + u * 256) * stride];
+#pragma unroll
+        for (int u = 0; u < PU; ++u) atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(v[u]) - kmin) >> sh)], 1u);
     }
     for (; i < m; i += 256) atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(xr[(unsigned long long)i * stride]) - kmin) >> sh)], 1u);
     __syncthreads();
@@ -1139,7 +1145,8 @@ cudaError_t launch_select_pass(const SelectProblem& sp, bool first_pass, void* d
 // to the bin that holds its rank, is decided outright (single-key bin, or position in the sorted
 // candidates), or -- when its bracket missed -- is flagged for the gap beside the interval.  (2) One thread
 // per row assembles the next RowSel: gaps get their exact population below from the neighbours' totals.
-constexpr int SCAN_THREADS = 1024;
+constexpr int SCAN_THREADS = 256;           // four bins per thread: eight blocks per SM instead of two (10250 blocks for the
+constexpr int SCAN_PER = SEL_BINS / SCAN_THREADS;   // 1025 rows x 10 intervals of a config-5 fan chart: 90 -> 35 us)
 constexpr unsigned long long POP_UNKNOWN = ~0ull;
 enum { SC_NONE = 0, SC_BIN = 1, SC_DONE = 2, SC_GAP_LOW = 3, SC_GAP_HIGH = 4 };
 
@@ -1171,9 +1178,19 @@ __global__ void __launch_bounds__(SCAN_THREADS) select_scan_iv_kernel(const Sele
     const unsigned int* slot0 = grow + 2 * (size_t)n_iv_cap + (size_t)gi * iv_slot;
     unsigned long long total;
     if (mode == IV_HIST) {
-        unsigned long long c = 0;
-        for (unsigned int r = 0; r < n_ranks; ++r) c += slot0[r * rank_stride_u32 + 2 + tid];
-        unsigned long long incl = c;
+        unsigned long long c[SCAN_PER], run = 0;
+#pragma unroll
+        for (int k = 0; k < SCAN_PER; ++k) c[k] = 0;
+        for (unsigned int r = 0; r < n_ranks; ++r) {
+            // bins tid * 4 .. tid * 4 + 3 of rank r: the slot starts 2 words into an 8-byte aligned row: 8-byte loads
+            const uint2* src = reinterpret_cast<const uint2*>(slot0 + r * rank_stride_u32 + 2 + tid * SCAN_PER);
+            static_assert(SCAN_PER == 4, "two 8-byte loads per thread and rank");
+            const uint2 a = src[0], b = src[1];
+            c[0] += a.x; c[1] += a.y; c[2] += b.x; c[3] += b.y;
+        }
+#pragma unroll
+        for (int k = 0; k < SCAN_PER; ++k) { run += c[k]; c[k] = run; }
+        unsigned long long incl = run;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
@@ -1181,9 +1198,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) select_scan_iv_kernel(const Sele
         }
         if (lane == 31) s_warp[warp] = incl;
         __syncthreads();
-        unsigned long long off = 0;
+        unsigned long long off = incl - run;
         for (int w = 0; w < warp; ++w) off += s_warp[w];
-        s_cum[tid] = off + incl;
+#pragma unroll
+        for (int k = 0; k < SCAN_PER; ++k) s_cum[tid * SCAN_PER + k] = off + c[k];
         __syncthreads();
         total = s_cum[SEL_BINS - 1];
     } else {
@@ -1192,22 +1210,24 @@ __global__ void __launch_bounds__(SCAN_THREADS) select_scan_iv_kernel(const Sele
             const unsigned int* slot = slot0 + r * rank_stride_u32;
             unsigned int cr = slot[0];
             if (cr > (unsigned int)SEL_CAND) cr = SEL_CAND;
-            if ((unsigned int)tid < cr && base + tid < (unsigned int)SEL_CAND)
-                s_keys[base + tid] = (unsigned long long)reinterpret_cast<const Key*>(slot + 2)[tid];
+            for (unsigned int t = tid; t < cr; t += SCAN_THREADS)
+                if (base + t < (unsigned int)SEL_CAND) s_keys[base + t] = (unsigned long long)reinterpret_cast<const Key*>(slot + 2)[t];
             base += cr;
         }
         const unsigned int cnt_all = base < (unsigned int)SEL_CAND ? base : SEL_CAND;
         int P = 1;
         while (P < (int)cnt_all) P <<= 1;
-        if (tid >= (int)cnt_all && tid < P) s_keys[tid] = ~0ull;
+        for (int t = (int)cnt_all + tid; t < P; t += SCAN_THREADS) s_keys[t] = ~0ull;
         __syncthreads();
         for (int k = 2; k <= P; k <<= 1) {
             for (int j = k >> 1; j > 0; j >>= 1) {
-                const int ixj = tid ^ j;
-                if (tid < P && ixj > tid) {
-                    const unsigned long long a = s_keys[tid], b2 = s_keys[ixj];
-                    const bool up = (tid & k) == 0;
-                    if ((a > b2) == up) { s_keys[tid] = b2; s_keys[ixj] = a; }
+                for (int t = tid; t < P; t += SCAN_THREADS) {
+                    const int ixj = t ^ j;
+                    if (ixj > t) {
+                        const unsigned long long a = s_keys[t], b2 = s_keys[ixj];
+                        const bool up = (t & k) == 0;
+                        if ((a > b2) == up) { s_keys[t] = b2; s_keys[ixj] = a; }
+                    }
                 }
                 __syncthreads();
             }
