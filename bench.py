@@ -288,9 +288,9 @@ def run_workload(workload, steps, warmup, world, rank, group, device, sample_clo
     for a, b in ev:
         flush.zero_()                     # L2 flush between timed iterations (untimed)
         torch.cuda.synchronize(eng.device)
-        if world > 1:                     # ranks enter the step together: a step ends at its (device-side) exchanges,
-            dist.barrier(group)           # so a rank that started late would bill its lateness to the others
-            torch.cuda.synchronize(eng.device)
+        if world > 1 and os.environ.get("MC_BENCH_STEP_BARRIER", "1") != "0":
+            dist.barrier(group)           # ranks enter the step together: a step ends at its (device-side) exchanges,
+            torch.cuda.synchronize(eng.device)      # so a rank that started late would bill its lateness to the others
         a.record()
         last = one_step()
         b.record()

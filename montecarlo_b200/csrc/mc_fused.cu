@@ -109,11 +109,15 @@ __global__ void __launch_bounds__(1024) fused_plan_kernel(const FusedArgs a) {
     if (tid == 0) s_status = FUSED_OK;
     __syncthreads();
     if (R > 1) {            // X1: my histogram into every peer's inbox, then wait for theirs
+        // read once, store to every peer (a load per peer would chain 2 (R - 1) L2 latencies in front of the stores)
         const uint4* src = reinterpret_cast<const uint4*>(hist_in(a, me, me));
+        static_assert(FUSED_KB / 4 == 2 * 1024, "two 16-byte pieces per thread");
+        const uint4 q0 = __ldcg(src + tid), q1 = __ldcg(src + tid + 1024);
         for (unsigned int r = 0; r < R; ++r) {
             if (r == me) continue;
             uint4* dst = reinterpret_cast<uint4*>(hist_in(a, r, me));
-            for (int i = tid; i < FUSED_KB / 4; i += 1024) dst[i] = src[i];
+            dst[tid] = q0;
+            dst[tid + 1024] = q1;
         }
         __threadfence_system();
         __syncthreads();
@@ -430,19 +434,30 @@ __global__ void __launch_bounds__(CLOSE_THREADS, 4) fused_closing_kernel(const F
     }
     __syncthreads();
     tot = block_reduce(tot, s_part);
+    const unsigned int my_overflow = *reinterpret_cast<volatile unsigned int*>(&P.overflow);
+    const unsigned int my_cand = tid < FUSED_MAX_SLOTS ? *reinterpret_cast<volatile unsigned int*>(&P.cand_count[tid]) : 0u;
+    const int my_status = P.status;
     for (unsigned int r = 0; r < R; ++r) {
         unsigned long long* h = hdr_in(a, r, me);
         if (tid == 0) {
             h[HW_N] = tot.n; h[HW_ABOVE] = tot.n_above; h[HW_SUM_D] = bits(tot.sum_d); h[HW_SUM_D2] = bits(tot.sum_d2);
             h[HW_MIN] = bits(tot.vmin); h[HW_MAX] = bits(tot.vmax); h[HW_TAIL_CNT] = tot.tail_cnt;
             h[HW_TAIL_SUM] = bits(tot.tail_sum);
-            h[HW_OVERFLOW] = *reinterpret_cast<volatile unsigned int*>(&P.overflow);
-            h[HW_STATUS] = (unsigned long long)P.status;
+            h[HW_OVERFLOW] = my_overflow;
+            h[HW_STATUS] = (unsigned long long)my_status;
         }
-        if (tid < FUSED_MAX_SLOTS) h[HW_CAND + tid] = *reinterpret_cast<volatile unsigned int*>(&P.cand_count[tid]);
-        if (r != me && a.nph_bins) {
+        if (tid < FUSED_MAX_SLOTS) h[HW_CAND + tid] = my_cand;
+    }
+    // this rank's fixed-bin counts to every peer: each piece is read once and stored R - 1 times
+    for (unsigned int i0 = 0; R > 1 && i0 < a.nph_bins; i0 += 8u * CLOSE_THREADS) {
+        unsigned int c[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { const unsigned int i = i0 + tid + k * CLOSE_THREADS; c[k] = i < a.nph_bins ? __ldcg(my_nph + i) : 0u; }
+        for (unsigned int r = 0; r < R; ++r) {
+            if (r == me) continue;
             unsigned int* dst = nph_in(a, r, me);
-            for (unsigned int i = tid; i < a.nph_bins; i += CLOSE_THREADS) dst[i] = __ldcg(my_nph + i);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { const unsigned int i = i0 + tid + k * CLOSE_THREADS; if (i < a.nph_bins) dst[i] = c[k]; }
         }
     }
     if (R > 1) {

@@ -151,7 +151,8 @@ def test_gbm_injected_and_device_normals(engine, dtype):
     paths = out.paths.cpu().numpy().astype(np.float64)
     assert np.abs(paths / ref - 1).max() < RTOL[dtype]
     _check_reductions(out, paths[-1], s0, spec)
-    # on-device normals: stored and fused-sum kernels agree with the bit model
+    # on-device normals: stored and fused-sum kernels agree with the bit model (2e-5 in fp32: MUFU lg2 / sqrt in the
+    # draws themselves; the injected case above holds the stepping to 1e-5)
     tol = 2e-5 if dtype == "float32" else 1e-11
     ref2 = port.gbm_paths(z, s0, mu, sigma, dt)
     for store in (True, False):
@@ -179,13 +180,16 @@ def test_portfolio_matches_port(engine, dtype, d):
     z = philox.normal_shocks(seed, 0, n, t, dtype=np.dtype(dtype), n_assets=d)
     v_ref, _ = port.portfolio_terminal(z, s0, 0.05, sigma, np.linalg.cholesky(corr), w, dt)
     v0 = float(w @ s0)
-    tol = 3e-5 if dtype == "float32" else 1e-11
     for shock, shocks in (("normal", None), ("injected", z.reshape(t * d, n))):
+        # identical injected shocks: BASELINE's 1e-5 (fp32) / 1e-12-class (fp64).  Device normals go through MUFU lg2 /
+        # sqrt (each draw within 5e-5 of the fp64 bit model, test_device_normals_match_bit_model), so the replayed
+        # fp32 path may differ by a few 1e-5: that bound is about the generator's approximation, not the stepping
+        tol = (1e-5 if shock == "injected" else 3e-5) if dtype == "float32" else 1e-11
         spec = SimSpec(n_paths=n, n_steps=t, s0=v0, shock=shock, var_model="const", dtype=dtype, seed=seed,
                        portfolio=pf, store_paths=True, fan_chart=True)
         out = engine.simulate(spec, shocks=shocks)
         v = out.terminal.cpu().numpy().astype(np.float64)
-        assert np.abs(v / v_ref - 1).max() < tol
+        assert np.abs(v / v_ref - 1).max() < tol, (shock, float(np.abs(v / v_ref - 1).max()))
         _check_reductions(out, v, v0, spec)
         paths = out.paths.cpu().numpy().astype(np.float64)
         assert np.allclose(paths[0], v0, rtol=1e-6) and np.array_equal(paths[-1], v)
