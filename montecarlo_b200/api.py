@@ -39,19 +39,41 @@ def _fan_plan(store: bool, want: bool, n_sims: int, n_days: int, dtype: str):
     return True, True, int(chunk)
 
 
+def _column(df, name):
+    """df[name] as an array.  pandas builds a Series for `df[name]` (25 us in pandas 3 -- more than the simulation of
+    the app's default call takes); the block manager hands out the column's array directly.  Anything unusual
+    (no such private accessor, duplicate labels, a non-DataFrame mapping) takes the public route."""
+    try:
+        return df._get_column_array(df.columns.get_loc(name))
+    except Exception:
+        return df[name]
+
+
 def _history_inputs(df):
     """The two DataFrame reads of the reference: app.py:592 and app.py:606."""
-    # NumPy from the column on: Series.dropna() / .iloc cost more than the whole simulation at the app's sizes
-    returns = np.asarray(df["log_ret"], dtype=np.float64)
+    returns = np.asarray(_column(df, "log_ret"), dtype=np.float64)
     nan = np.isnan(returns)
     if nan.any():
         returns = returns[~nan]                        # .dropna()
-    rvol_last = float(np.asarray(df["rvol_20"], dtype=np.float64)[-1])      # .iloc[-1]
+    rvol_last = float(np.asarray(_column(df, "rvol_20"), dtype=np.float64)[-1])      # .iloc[-1]
     return returns, rvol_last
+
+
+def _population_std(r: np.ndarray) -> float:
+    """np.std(r) for a 1-D float64 array, bit for bit, without its 20 us of dispatch: the very operations of
+    numpy/_core/_methods.py:_var (pairwise np.add.reduce, true divide, subtract, multiply in place, reduce, divide,
+    sqrt).  tests/test_host_boundary.py holds it to np.std."""
+    n = r.shape[0]
+    mean = np.add.reduce(r) / n
+    x = r - mean
+    np.multiply(x, x, out=x)
+    return float(np.sqrt(np.add.reduce(x) / n))
 
 
 def bootstrap_pool(returns: np.ndarray) -> np.ndarray:
     """std_returns (app.py:609): scaled by the population std, not demeaned."""
+    if isinstance(returns, np.ndarray) and returns.ndim == 1 and returns.dtype == np.float64 and returns.size:
+        return returns / (_population_std(returns) + 1e-10)
     return returns / (np.std(returns) + 1e-10)
 
 

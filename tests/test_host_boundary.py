@@ -136,3 +136,26 @@ def test_portfolio_spec_arrays():
     assert p.n_assets == d and abs(p.s0 - 100.0) < 1e-12
     chol = np.ctypeslib.as_array(c.h_chol, (d * d,)).reshape(d, d)
     assert np.allclose(chol @ chol.T, corr)
+
+
+def test_fast_host_paths_equal_the_reference_expressions():
+    """The drop-in's host side avoids pandas Series construction and np.std's dispatch overhead (they cost more than
+    the simulation of the app's default call): same numbers as `df['log_ret'].dropna().values`, `df['rvol_20'].iloc[-1]`
+    and `returns / (np.std(returns) + 1e-10)` (app.py:592, 606, 609), bit for bit."""
+    import pandas as pd
+    from montecarlo_b200 import api
+    rs = np.random.RandomState(3)
+    for n in (1, 2, 100, 1250, 4097, 100_003):
+        r = rs.standard_t(4, n) * 0.013
+        assert api._population_std(r) == float(np.std(r)), n
+        assert np.array_equal(api.bootstrap_pool(r), r / (np.std(r) + 1e-10))
+    assert np.array_equal(api.bootstrap_pool(np.arange(5, dtype=np.float32)), np.arange(5, dtype=np.float32) / (np.std(np.arange(5, dtype=np.float32)) + 1e-10))
+    x = rs.normal(0, 0.02, 500)
+    x[[0, 17, 499]] = np.nan
+    for df in (pd.DataFrame({"log_ret": x, "rvol_20": np.linspace(0.1, 0.4, 500), "other": "a"}),
+               pd.DataFrame({"rvol_20": np.linspace(0.1, 0.4, 500).astype(np.float32), "log_ret": x}),
+               {"log_ret": pd.Series(x), "rvol_20": pd.Series(np.linspace(0.1, 0.4, 500))}):
+        returns, rvol_last = api._history_inputs(df)
+        col = df["log_ret"]
+        assert np.array_equal(returns, col.dropna().values)
+        assert rvol_last == float(df["rvol_20"].iloc[-1])
