@@ -138,9 +138,11 @@ cudaError_t launch_select_sample(const SelectProblem& sp, void* d_out, cudaStrea
 // row) and each percentile's bracket is rounded OUTWARD to bin edges.
 // brackets of one row from the (summed) 4096-bin histogram of its pilot: all 256 threads of the block
 template <typename Key>
+// `clamp_top` >= 0: samples outside the binned key range were clamped into bin 0 / bin clamp_top, so a bracket that
+// starts in bin 0 opens down to key 0 and one that ends in bin clamp_top (or beyond) opens up to the largest key
 __device__ void brackets_from_pilot_hist(const SelectPlan* __restrict__ plan, unsigned int* s_hist, unsigned int* s_warp,
                                          unsigned long long* s_lo, unsigned long long* s_hi, unsigned long long kmin,
-                                         int sh, unsigned int m_total, RowSel& st) {
+                                         int sh, unsigned int m_total, RowSel& st, int clamp_top = -1) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // inclusive scan of the 4096 bins, 16 per thread
     unsigned int local[PILOT_BINS / 256], run = 0;
@@ -174,10 +176,16 @@ __device__ void brackets_from_pilot_hist(const SelectPlan* __restrict__ plan, un
             while (a < b) { const int mid = (a + b) >> 1; if (s_hist[mid] > r) b = mid; else a = mid + 1; }
             return a;
         };
-        if (fa >= 0.0 && m_total) lo = kmin + ((unsigned long long)bin_of_rank((unsigned int)fa) << sh);
+        if (fa >= 0.0 && m_total) {
+            const int b = bin_of_rank((unsigned int)fa);
+            if (!(clamp_top >= 0 && b == 0)) lo = kmin + ((unsigned long long)b << sh);
+        }
         if (fb < m && m_total) {
-            const unsigned long long span = ((unsigned long long)(bin_of_rank((unsigned int)fb) + 1) << sh) - 1ull;
-            hi = span > KMAX - kmin ? KMAX : kmin + span;
+            const int b = bin_of_rank((unsigned int)fb);
+            if (!(clamp_top >= 0 && b >= clamp_top)) {
+                const unsigned long long span = ((unsigned long long)(b + 1) << sh) - 1ull;
+                hi = span > KMAX - kmin ? KMAX : kmin + span;
+            }
         }
         s_lo[tid] = lo; s_hi[tid] = hi;
     }
@@ -256,42 +264,49 @@ __global__ void __launch_bounds__(256) select_bracket_kernel(const SelectPlan* _
     brackets_from_pilot_hist<Key>(plan, s_hist, s_warp, s_lo, s_hi, kmin, sh, m_total, states[row]);
 }
 
-// the same from a pilot read IN PLACE: the first m values of the row (stride 1) or every stride-th value
-template <typename Real>
+// the same from a pilot read IN PLACE: the first m values of the row (stride 1) or every stride-th value.
+// ONE_PASS (iid columns: the first values of a row are a random sample of it): the binned key range comes from the
+// first 8192 samples, widened by a quarter of its width on either side; the few samples beyond it are clamped into the
+// end bins, which then open to the ends of the key range.  The pilot is read once (131072 samples x 1025 rows do not
+// fit the L2: the two-pass form read 1.07 GB from DRAM and spent 225 us, ncu `profiles/r02/ncu_full_brc5.txt`).
+constexpr unsigned int PILOT_RANGE_SAMPLES = 8192;
+
+template <typename Real, bool ONE_PASS>
 __global__ void __launch_bounds__(256) select_bracket_in_place_kernel(const SelectPlan* __restrict__ plan,
                                                                       const Real* __restrict__ x, unsigned long long ld,
                                                                       unsigned int m, unsigned long long stride,
                                                                       RowSel* __restrict__ states) {
     using Key = typename KeyT<Real>::type;
     __shared__ unsigned int s_hist[PILOT_BINS];
-    __shared__ unsigned long long s_min[8], s_max[8];
+    __shared__ Key s_min[8], s_max[8];
     __shared__ unsigned int s_warp[8];
     __shared__ unsigned long long s_lo[MC_MAX_PCTS], s_hi[MC_MAX_PCTS];
     const unsigned long long row = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const Real* xr = x + row * ld;
-    unsigned long long kmin = ~0ull, kmax = 0ull;
-    unsigned int i = tid;
     constexpr int PU = 16;                               // loads in flight per thread: the block is alone with its row's latency
-    for (; i + (PU - 1) * 256 < m; i += PU * 256) {
+    const unsigned int m_range = ONE_PASS ? (m < PILOT_RANGE_SAMPLES ? m : PILOT_RANGE_SAMPLES) : m;
+    Key kmin = key_max<Key>(), kmax = 0;
+    unsigned int i = tid;
+    for (; i + (PU - 1) * 256 < m_range; i += PU * 256) {
         Real v[PU];
 #pragma unroll
         for (int u = 0; u < PU; ++u) v[u] = xr[(unsigned long long)(i + u * 256) * stride];
 #pragma unroll
         for (int u = 0; u < PU; ++u) {
-            const unsigned long long k = key_of(v[u]);
+            const Key k = key_of(v[u]);
             kmin = k < kmin ? k : kmin;
             kmax = k > kmax ? k : kmax;
         }
     }
-    for (; i < m; i += 256) {
-        const unsigned long long k = key_of(xr[(unsigned long long)i * stride]);
+    for (; i < m_range; i += 256) {
+        const Key k = key_of(xr[(unsigned long long)i * stride]);
         kmin = k < kmin ? k : kmin;
         kmax = k > kmax ? k : kmax;
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
-        const unsigned long long a = __shfl_down_sync(0xffffffffu, kmin, d), b = __shfl_down_sync(0xffffffffu, kmax, d);
+        const Key a = __shfl_down_sync(0xffffffffu, kmin, d), b = __shfl_down_sync(0xffffffffu, kmax, d);
         kmin = a < kmin ? a : kmin;
         kmax = b > kmax ? b : kmax;
     }
@@ -302,22 +317,35 @@ __global__ void __launch_bounds__(256) select_bracket_in_place_kernel(const Sele
 #pragma unroll
     for (int w = 1; w < 8; ++w) { kmin = s_min[w] < kmin ? s_min[w] : kmin; kmax = s_max[w] > kmax ? s_max[w] : kmax; }
     if (m == 0) { kmin = 0; kmax = 0; }
-    const int sh = max(0, bit_length(kmax - kmin) - PILOT_BIN_BITS);
-    i = tid;
-    if (kmin == kmax) {          // a constant row (row 0 of the paths is all s0, app.py:613): every sample in bin 0 -- without
-        if (tid == 0) s_hist[0] = m;      // 131072 atomics on one shared-memory word (230 us for that one block)
-        i = m;
+    int clamp_top = -1;
+    if (ONE_PASS && m > m_range) {       // widen, stay inside the key type
+        const Key quarter = (Key)((kmax - kmin) >> 2) + 1;
+        kmin = kmin > quarter ? kmin - quarter : 0;
+        kmax = key_max<Key>() - kmax > quarter ? kmax + quarter : key_max<Key>();
     }
-    for (; i + (PU - 1) * 256 < m; i += PU * 256) {      // the second read of the pilot comes from L2
+    const int sh = max(0, bit_length((unsigned long long)(kmax - kmin)) - PILOT_BIN_BITS);
+    if (ONE_PASS && m > m_range) clamp_top = (int)((unsigned long long)(kmax - kmin) >> sh);
+    auto bin_of = [&](Real v) {
+        Key k = key_of(v);
+        if (ONE_PASS) { k = k < kmin ? kmin : k; k = k > kmax ? kmax : k; }
+        return (unsigned int)((Key)(k - kmin) >> sh);
+    };
+    i = tid;
+    if (kmin == kmax) {          // a constant row (row 0 of the paths is all s0, app.py:613): every sample in bin 0
+        if (tid == 0) s_hist[0] = m;
+        i = m;
+        clamp_top = -1;
+    }
+    for (; i + (PU - 1) * 256 < m; i += PU * 256) {
         Real v[PU];
 #pragma unroll
         for (int u = 0; u < PU; ++u) v[u] = xr[(unsigned long long)(i + u * 256) * stride];
 #pragma unroll
-        for (int u = 0; u < PU; ++u) atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(v[u]) - kmin) >> sh)], 1u);
+        for (int u = 0; u < PU; ++u) atomicAdd(&s_hist[bin_of(v[u])], 1u);
     }
-    for (; i < m; i += 256) atomicAdd(&s_hist[(unsigned int)(((unsigned long long)key_of(xr[(unsigned long long)i * stride]) - kmin) >> sh)], 1u);
+    for (; i < m; i += 256) atomicAdd(&s_hist[bin_of(xr[(unsigned long long)i * stride])], 1u);
     __syncthreads();
-    brackets_from_pilot_hist<Key>(plan, s_hist, s_warp, s_lo, s_hi, kmin, sh, m, states[row]);
+    brackets_from_pilot_hist<Key>(plan, s_hist, s_warp, s_lo, s_hi, (unsigned long long)kmin, sh, m, states[row], clamp_top);
 }
 
 cudaError_t launch_select_brackets(const SelectProblem& sp, const unsigned long long* d_gathered,
@@ -326,12 +354,14 @@ cudaError_t launch_select_brackets(const SelectProblem& sp, const unsigned long 
     if (sp.plan.n_targets == 0 || sp.rows == 0) return cudaSuccess;
     if (sp.pilot_in_place) {
         const unsigned long long stride = sp.sample_contiguous ? 1ull : (sp.m_local && sp.n / sp.m_local ? sp.n / sp.m_local : 1ull);
-        if (sp.dtype == MC_F64)
-            select_bracket_in_place_kernel<double><<<(unsigned)sp.rows, 256, 0, stream>>>(
-                sp.d_plan, static_cast<const double*>(sp.x), sp.ld, sp.m_local, stride, sp.d_states);
-        else
-            select_bracket_in_place_kernel<float><<<(unsigned)sp.rows, 256, 0, stream>>>(
-                sp.d_plan, static_cast<const float*>(sp.x), sp.ld, sp.m_local, stride, sp.d_states);
+        const bool one_pass = sp.sample_contiguous != 0;
+        if (sp.dtype == MC_F64) {
+            auto k = one_pass ? select_bracket_in_place_kernel<double, true> : select_bracket_in_place_kernel<double, false>;
+            k<<<(unsigned)sp.rows, 256, 0, stream>>>(sp.d_plan, static_cast<const double*>(sp.x), sp.ld, sp.m_local, stride, sp.d_states);
+        } else {
+            auto k = one_pass ? select_bracket_in_place_kernel<float, true> : select_bracket_in_place_kernel<float, false>;
+            k<<<(unsigned)sp.rows, 256, 0, stream>>>(sp.d_plan, static_cast<const float*>(sp.x), sp.ld, sp.m_local, stride, sp.d_states);
+        }
         return cudaGetLastError();
     }
     if (sp.dtype == MC_F64)
@@ -1001,15 +1031,20 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass2_f32_kernel(const fl
         const int warp = tid >> 5, lane = tid & 31;
         const float* list = side.values + (side_slot + warp) * side.cap;
         const unsigned int cnt = side.counts[side_slot + warp];
+        // four 16-byte loads in flight per lane (the lists start on 128-byte boundaries): 512 values per warp and round
+        // (8 scalar loads per lane left the pass waiting on its own loads: long scoreboard 5.6, ncu ncu_full_p2c5.txt)
+        const float4* list4 = reinterpret_cast<const float4*>(list);
+        const unsigned int cnt4 = (reinterpret_cast<uintptr_t>(list) & 15u) == 0 ? cnt >> 2 : 0u;     // (a test knob may set an odd capacity)
         unsigned int i = lane;
-        for (; i + 224 < cnt; i += 256) {        // eight loads in flight per lane
-            float a[8];
+        for (; i + 96 < cnt4; i += 128) {
+            float4 a[4];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) a[u] = __ldcs(list + i + 32 * u);
+            for (int u = 0; u < 4; ++u) a[u] = __ldcs(list4 + i + 32 * u);
 #pragma unroll
-            for (int u = 0; u < 8; ++u) visit(a[u]);
+            for (int u = 0; u < 4; ++u) { visit(a[u].x); visit(a[u].y); visit(a[u].z); visit(a[u].w); }
         }
-        for (; i < cnt; i += 32) visit(__ldcs(list + i));
+        for (; i < cnt4; i += 32) { const float4 q = __ldcs(list4 + i); visit(q.x); visit(q.y); visit(q.z); visit(q.w); }
+        for (unsigned int k = (cnt4 << 2) + lane; k < cnt; k += 32) visit(__ldcs(list + k));
     } else {
         unsigned long long beg, end;
         fast_block_range(n, &beg, &end);
