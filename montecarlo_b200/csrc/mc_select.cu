@@ -695,27 +695,48 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass1_f32_kernel(const fl
 // predicated park -- against 3 instructions PER BRACKET before.
 constexpr int LUT_BINS = 2048;
 constexpr float LUT_TOP_F = (float)(LUT_BINS - 1);
-constexpr uint32_t LUT_MAGIC_BITS = 0x4B000000u;        // bits of 2^23: rn(t + 2^23) has the integer t in its mantissa
 
-__device__ __forceinline__ uint32_t lut_bits(float v, float qs, float qb) {
-    float t, u;
-    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(t) : "f"(v), "f"(qs), "f"(qb));          // NaN -> 0
-    asm("fma.rn.f32 %0, %1, %2, %3;" : "=f"(u) : "f"(t), "f"(LUT_TOP_F), "f"(8388608.0f));
-    return __float_as_uint(u);                                                             // LUT_MAGIC_BITS + bin
+// byte address of a value's table word, straight out of two FMAs: t = sat(v * qs + qb) in [0, 1] (NaN -> 0), then
+//     u = t * ((LUT_BINS - 1) * sizeof(Word)) + (2^23 + table address)
+// has  table address + rn(t * (LUT_BINS - 1) * sizeof(Word))  in its mantissa; one AND drops the exponent and the low
+// bits, which leaves the address of word floor(rn(.) / sizeof(Word)) -- monotone in v.  (The earlier form put the bin
+// number into the mantissa and needed a shift-add and an add per value to make an address of it: 20.8 -> 19.8
+// instructions per value.  The pass is bound by shared-memory wavefronts -- 3.4 per table lookup, 78 % of the pipe,
+// profiles/r02/ncu_full_p1c5.txt -- so the time did not move.)
+struct LutAddr {
+    float qs, qb, scale, kb;          // kb = 2^23 + shared-window address of the table (exact: the address is < 2^18)
+    uint32_t mask, base;
+};
+template <typename Word>
+__device__ __forceinline__ LutAddr make_lut_addr(float qs, float qb, uint32_t table_addr) {
+    LutAddr a;
+    a.qs = qs; a.qb = qb;
+    a.scale = LUT_TOP_F * (float)sizeof(Word);
+    a.kb = 8388608.0f + (float)table_addr;
+    a.mask = 0x007FFFFFu & ~(uint32_t)(sizeof(Word) - 1);
+    a.base = table_addr;
+    return a;
 }
-
+__device__ __forceinline__ uint32_t lut_addr(const LutAddr& a, float v) {
+    float t, u;
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(t) : "f"(v), "f"(a.qs), "f"(a.qb));
+    asm("fma.rn.f32 %0, %1, %2, %3;" : "=f"(u) : "f"(t), "f"(a.scale), "f"(a.kb));
+    return __float_as_uint(u) & a.mask;
+}
 // two values: the clamp FMAs stay scalar (no .sat on the packed form), the second FMA is one FFMA2 -- each half the
-// same correctly rounded FMA as in lut_bits, so the bins are the ones the table was built for
-__device__ __forceinline__ void lut_bits2(float v0, float v1, float qs, float qb, uint32_t& b0, uint32_t& b1) {
+// same correctly rounded FMA as in lut_addr, so the words are the ones the table was built for
+__device__ __forceinline__ void lut_addr2(const LutAddr& a, float v0, float v1, uint32_t& a0, uint32_t& a1) {
     float t0, t1;
-    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(t0) : "f"(v0), "f"(qs), "f"(qb));
-    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(t1) : "f"(v1), "f"(qs), "f"(qb));
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(t0) : "f"(v0), "f"(a.qs), "f"(a.qb));
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(t1) : "f"(v1), "f"(a.qs), "f"(a.qb));
     unsigned long long t2, m2, k2, u2;
     asm("mov.b64 %0, {%1, %2};" : "=l"(t2) : "f"(t0), "f"(t1));
-    asm("mov.b64 %0, {%1, %1};" : "=l"(m2) : "f"(LUT_TOP_F));
-    asm("mov.b64 %0, {%1, %1};" : "=l"(k2) : "f"(8388608.0f));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(m2) : "f"(a.scale));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(k2) : "f"(a.kb));
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(u2) : "l"(t2), "l"(m2), "l"(k2));
+    uint32_t b0, b1;
     asm("mov.b64 {%0, %1}, %2;" : "=r"(b0), "=r"(b1) : "l"(u2));
+    a0 = b0 & a.mask; a1 = b1 & a.mask;
 }
 
 template <int NB> struct LutWord { using type = uint32_t; };
@@ -818,12 +839,13 @@ __global__ void __launch_bounds__(FAST_THREADS, NB <= 5 ? 3 : 2) select_pass1_lu
         const float s = 1.0f / (w + 2.0f * m), b = -(fmin_ - m) * s;
         if (w > 0.0f && s > 0.0f && s < INFINITY && fabsf(b) < INFINITY) { qs = s; qb = b; }      // else: every bin parks
     }
+    const LutAddr la = make_lut_addr<Word>(qs, qb, (uint32_t)__cvta_generic_to_shared(s_lut));
     {
         uint32_t qlo[NB], qhi[NB];
 #pragma unroll
         for (int g = 0; g < NB; ++g) {
-            qlo[g] = lut_bits(lo_f[g], qs, qb) - LUT_MAGIC_BITS;
-            qhi[g] = lut_bits(hi_f[g], qs, qb) - LUT_MAGIC_BITS;
+            qlo[g] = (lut_addr(la, lo_f[g]) - la.base) >> WSHIFT;
+            qhi[g] = (lut_addr(la, hi_f[g]) - la.base) >> WSHIFT;
         }
         for (uint32_t k = tid; k < (uint32_t)LUT_BINS; k += FAST_THREADS) {
             int gap = 0;
@@ -842,9 +864,6 @@ __global__ void __launch_bounds__(FAST_THREADS, NB <= 5 ? 3 : 2) select_pass1_lu
 
     unsigned int* out_row = out + row * row_slot;
     unsigned int* out_iv = out_row + 2 * (size_t)n_iv_cap;
-    uint32_t lut_base;                       // table address minus the shifted magic, opaque to the compiler: the
-    asm volatile("mov.u32 %0, %1;"           // address of a value's word is then ONE LEA
-                 : "=r"(lut_base) : "r"((uint32_t)__cvta_generic_to_shared(s_lut) - (LUT_MAGIC_BITS << WSHIFT)));
     Word acc = 0;                            // the gap counters of the current batch: NB + 1 fields of FIELD bits
     unsigned int gapc[NB + 1];
 #pragma unroll
@@ -890,17 +909,17 @@ __global__ void __launch_bounds__(FAST_THREADS, NB <= 5 ? 3 : 2) select_pass1_lu
     fast_stream<true>(x + row * ld, beg, end, vec != 0,
         [&](auto v) {
             if constexpr (sizeof(v) == sizeof(float4)) {       // four values: one register for the queue top throughout
-                uint32_t b0, b1, b2, b3;
-                lut_bits2(v.x, v.y, qs, qb, b0, b1);
-                lut_bits2(v.z, v.w, qs, qb, b2, b3);
-                const Word w0 = lut_word<Word>((b0 << WSHIFT) + lut_base);
-                const Word w1 = lut_word<Word>((b1 << WSHIFT) + lut_base);
-                const Word w2 = lut_word<Word>((b2 << WSHIFT) + lut_base);
-                const Word w3 = lut_word<Word>((b3 << WSHIFT) + lut_base);
+                uint32_t a0, a1, a2, a3;
+                lut_addr2(la, v.x, v.y, a0, a1);
+                lut_addr2(la, v.z, v.w, a2, a3);
+                const Word w0 = lut_word<Word>(a0);
+                const Word w1 = lut_word<Word>(a1);
+                const Word w2 = lut_word<Word>(a2);
+                const Word w3 = lut_word<Word>(a3);
                 acc += (w0 + w1) + (w2 + w3);
                 park4(q_top, v, w0, w1, w2, w3);
             } else {
-                const Word w = lut_word<Word>((lut_bits(v, qs, qb) << WSHIFT) + lut_base);
+                const Word w = lut_word<Word>(lut_addr(la, v));
                 acc += w;
                 park1(q_top, v, w);
             }
