@@ -257,7 +257,9 @@ int mc_debug_philox(mc_handle* h, const uint32_t* d_ctr, uint32_t n, uint32_t ke
 /* np.percentile(x[r, :], pcts, method='linear') for r in rows of a [rows, ld] matrix */
 int mc_percentiles(mc_handle* h, const void* d_x, int32_t dtype, uint64_t rows, uint64_t n,
                    uint64_t ld, const double* pcts, uint32_t n_pcts, double* h_out, void* stream);
-/* Test knobs, per handle: capacity of the fp32 selection's side lists (< 0: automatic) and whether they are used;
+/* Test knobs, per handle: capacity of the fp32 selection's side lists (< 0: automatic); no_side_lists bit 0: the lists
+ * are not used, bit 1: mc_run keeps the terminal-value selection of a fan-chart request on the caller's stream instead
+ * of running it on an internal stream beside the fan chart's passes;
  * process-wide: waves of blocks per launch of the non-persistent simulation kernels (>= 1, 0: default 24) and threads
  * per block of the fused GBM kernel (128 / 256 / 512, 0: default).  Invalid values select the default. */
 int mc_debug_set_tuning(mc_handle* h, int side_cap, int no_side_lists, int waves, int nblock);

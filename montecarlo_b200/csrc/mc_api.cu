@@ -77,7 +77,9 @@ __global__ void words_to_host_kernel(unsigned long long* __restrict__ dst, const
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < na + nb + nc; i += stride)
         dst[i] = i < na ? a[i] : (i < na + nb ? b[i - na] : c[i - na - nb]);
 }
-__global__ void u32_to_host_kernel(unsigned int* dst, const unsigned int* src) { *dst = *src; }
+__global__ void u32_to_host_kernel(unsigned int* dst, const unsigned int* src, const unsigned int* src2) {
+    *dst = *src + (src2 ? *src2 : 0u);
+}
 constexpr size_t HOST_STORE_MAX_BYTES = 512 * 1024;     // beyond this the copy engine wins
 }  // namespace
 
@@ -97,6 +99,7 @@ struct mc_handle {
     DevBuf<RowSel> states_t, states_f;
     DevBuf<ScanScratch> scratch_t, scratch_f;
     DevBuf<unsigned int> pending;       // [1] rows with undecided targets after the latest scan
+    DevBuf<unsigned int> pending_t;     // [1] the same for the terminal problem while it runs on the side stream
     PinnedBuf<unsigned int> h_pending;
     DevBuf<double> pct_t;               // [3 * MC_MAX_PCTS]
     DevBuf<double> fan;                 // [rows * n_path_pcts]
@@ -149,9 +152,16 @@ struct mc_handle {
     double edges_lo = 0.0, edges_hi = 0.0;
     unsigned long long n_fused = 0, n_fused_fallback = 0;
     int last_fused_status = 0;
+    // mc_run of a single-rank request with BOTH a fan chart and terminal percentiles: the terminal problem (one row,
+    // ~0.2 ms of small kernels one behind the other) is enqueued on `side` and runs underneath the fan chart's passes
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool allow_overlap = false;         // set by mc_run around its stage calls (callers of the stage API own the stage buffers)
+    bool overlap_t = false;             // this run: terminal kernels go to `side`
     // test knobs (mc_debug_set_tuning)
     int side_cap_override = -1;
     bool no_side_lists = false;
+    bool no_overlap = false;
 };
 
 namespace {
@@ -210,6 +220,7 @@ PassLayout layout_pass(const mc_handle* h) {
 size_t final_stage_words(const mc_params& p) { return 2 + (size_t)p.hist_bins; }
 
 unsigned int ranks_of(const mc_params& p) { return p.n_ranks ? p.n_ranks : 1u; }
+unsigned int pass_group_of(const mc_params& p) { return p.pass_group > 1 ? p.pass_group : 1u; }
 
 // Side lists for an fp32 problem (mc_select.cuh: SideLists); a failed allocation just leaves them off.
 void attach_side(mc_handle* h, SelectProblem& sp, SideBuf& buf) {
@@ -666,12 +677,16 @@ int mc_create(int device_ordinal, mc_handle** out) {
               h->plans.reserve(2) == cudaSuccess && h->states_t.reserve(1) == cudaSuccess &&
               h->scratch_t.reserve(1) == cudaSuccess &&
               h->pct_t.reserve(3 * MC_MAX_PCTS) == cudaSuccess && h->tail_scratch.reserve(2 * 1024) == cudaSuccess &&
-              h->pending.reserve(1) == cudaSuccess && h->h_pending.reserve(1) == cudaSuccess &&
+              h->pending.reserve(1) == cudaSuccess && h->pending_t.reserve(1) == cudaSuccess && h->h_pending.reserve(1) == cudaSuccess &&
               h->side_blocks.reserve(1) == cudaSuccess && h->h_side_blocks.reserve(1) == cudaSuccess &&
               h->lut.reserve(4096) == cudaSuccess && launch_build_direction_table(h->lut.p, nullptr) == cudaSuccess &&
               cudaStreamSynchronize(nullptr) == cudaSuccess;
     for (int i = 0; i < 3 && ok; ++i) ok = cudaEventCreate(&h->ev[i]) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&h->ev_pending, cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking) == cudaSuccess &&
+         cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) == cudaSuccess &&
+         cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) == cudaSuccess &&
+         cudaMemset(h->pending_t.p, 0, sizeof(unsigned int)) == cudaSuccess;
     if (!ok) {
         e = cudaGetLastError();
         mc_destroy(h);
@@ -690,7 +705,10 @@ int mc_destroy(mc_handle* h) {
     h->side_blocks.release(); h->h_side_blocks.release();
     for (void* q : h->ipc_opened) cudaIpcCloseMemHandle(q);
     h->xchg.release(); h->fplan.release(); h->member.release(); h->close_partials.release(); h->claim.release();
-    h->stage.release(); h->h_stage.release(); h->pending.release(); h->h_pending.release();
+    h->stage.release(); h->h_stage.release(); h->pending.release(); h->pending_t.release(); h->h_pending.release();
+    if (h->side) { cudaStreamSynchronize(h->side); cudaStreamDestroy(h->side); }
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->ev_pending) cudaEventDestroy(h->ev_pending);
     delete h;
@@ -768,6 +786,12 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
     const Stage0Layout L = layout_stage0(h);
     if (!d_stage_out || cap_words < (uint64_t)mc_stage_max_words(p))
         return fail(h, MC_ERR_INVALID, "stage buffer smaller than mc_stage_max_words()");
+    // The terminal problem may run beside the fan chart's when nothing of what either touches in the stage buffer can
+    // meet: a pass writes [0, words_t) for the terminal row and [words_t, ...) for the fan chart, the final stage
+    // (tail + histogram, terminal side) [0, 2 + bins) -- which must stay inside the terminal part.
+    h->overlap_t = h->allow_overlap && !h->no_overlap && h->has_t && h->has_f && R == 1 && pass_group_of(*p) == 1 &&
+                   !(p->flags & MC_FLAG_PATHS_VOLATILE) && h->prob_t.pilot_in_place && h->prob_f.pilot_in_place &&
+                   final_stage_words(*p) <= pass_words(h->prob_t);
     unsigned long long* out = static_cast<unsigned long long*>(d_stage_out);
 
     MC_CUDA(h, cudaEventRecord(h->ev[0], s));
@@ -840,7 +864,6 @@ static int restore_rows_if_needed(mc_handle* h, cudaStream_t s) {
     return resimulate_locked(h, s);
 }
 
-unsigned int pass_group_of(const mc_params& p) { return p.pass_group > 1 ? p.pass_group : 1u; }
 
 // mc_params.pass_group > 1: the handles of one GPU that share a job (chunks of a fan chart by regeneration) write their
 // pass outputs into ONE buffer -- the leader's, which the leader clears -- so that the GPU hands the other GPUs one
@@ -858,7 +881,7 @@ static int enqueue_pass(mc_handle* h, unsigned long long* out, cudaStream_t s, c
     }
     h->last_pass_out = out;
     if (h->has_t) {
-        MC_CUDA(h, launch_select_pass(h->prob_t, first, out + L.off_t, h->dev.sm_count, s, zero));
+        MC_CUDA(h, launch_select_pass(h->prob_t, first, out + L.off_t, h->dev.sm_count, h->overlap_t ? h->side : s, zero));
         h->launches += h->prob_t.n ? 1 : 0;
     }
     if (h->has_f) {
@@ -873,11 +896,12 @@ static int enqueue_pass(mc_handle* h, unsigned long long* out, cudaStream_t s, c
 // percentiles from the decided keys, then the final stage: [tail count, tail sum, histogram counts...]
 static int enqueue_closing(mc_handle* h, unsigned long long* out, cudaStream_t s) {
     const mc_params& p = h->p;
+    cudaStream_t st = h->overlap_t ? h->side : s;      // everything about the terminal values
     if (h->has_t) {
         double* pct = h->pct_t.p;
-        MC_CUDA(h, launch_select_finish(h->prob_t, pct, pct + MC_MAX_PCTS, pct + 2 * MC_MAX_PCTS, s));
+        MC_CUDA(h, launch_select_finish(h->prob_t, pct, pct + MC_MAX_PCTS, pct + 2 * MC_MAX_PCTS, st));
         MC_CUDA(h, launch_publish_percentiles(pct, pct + MC_MAX_PCTS, pct + 2 * MC_MAX_PCTS, (int)p.n_pcts,
-                                              h->tail_idx, h->res.p, s));
+                                              h->tail_idx, h->res.p, st));
         h->launches += 2;
     }
     if (h->has_f) {
@@ -886,7 +910,11 @@ static int enqueue_closing(mc_handle* h, unsigned long long* out, cudaStream_t s
     }
     const bool want_tail = h->has_t && h->tail_idx >= 0;
     MC_CUDA(h, launch_tail_hist(h->d_terminal, p.dtype, p.n_paths, want_tail, p.hist_bins, p.hist_lo, p.hist_hi,
-                                h->res.p, h->edges.p, h->tail_scratch.p, out, h->dev.sm_count, s));
+                                h->res.p, h->edges.p, h->tail_scratch.p, out, h->dev.sm_count, st));
+    if (h->overlap_t) {       // the caller's stream takes the terminal side back in: the final merge reads both
+        MC_CUDA(h, cudaEventRecord(h->ev_join, h->side));
+        MC_CUDA(h, cudaStreamWaitEvent(s, h->ev_join, 0));
+    }
     h->launches += (p.hist_bins ? 1 : 0) + ((p.n_paths && (want_tail || p.hist_bins)) ? 1 : 0) + (want_tail && p.n_paths ? 1 : 0);
     h->next_words = final_stage_words(p);
     h->phase = 2;
@@ -940,12 +968,20 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
             if (h->has_t) MC_CUDA(h, cudaMemcpyAsync(h->states_t.p, leader->states_t.p, sizeof(RowSel), cudaMemcpyDeviceToDevice, s));
             if (h->has_f) MC_CUDA(h, cudaMemcpyAsync(h->states_f.p, leader->states_f.p, (size_t)h->prob_f.rows * sizeof(RowSel), cudaMemcpyDeviceToDevice, s));
         } else {
-            if (h->has_t) {
-                MC_CUDA(h, launch_select_brackets(h->prob_t, g, L.off_t, 6, n_ranks, stride, h->dev.max_smem_optin, s));
-                h->launches += 1;
-            }
             if (h->has_f) {
                 MC_CUDA(h, launch_select_brackets(h->prob_f, g, L.off_f, 7, n_ranks, stride, h->dev.max_smem_optin, s));
+                h->launches += 1;
+            }
+            if (h->overlap_t) {
+                // fork: from here on the terminal problem has its own stream.  Everything that reads the stage-0 header
+                // on the caller's stream is enqueued above; the first thing the side stream does to the buffer is to
+                // clear the terminal part of the pass layout, which lies over that header.
+                MC_CUDA(h, cudaEventRecord(h->ev_fork, s));
+                MC_CUDA(h, cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+            }
+            if (h->has_t) {
+                MC_CUDA(h, launch_select_brackets(h->prob_t, g, L.off_t, 6, n_ranks, stride, h->dev.max_smem_optin,
+                                                  h->overlap_t ? h->side : s));
                 h->launches += 1;
             }
         }
@@ -961,8 +997,10 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
         MC_CUDA(h, cudaMemcpyAsync(h->pending.p, leader->pending.p, sizeof(unsigned int), cudaMemcpyDeviceToDevice, s));
     } else {
         if (h->pass_idx >= 2) MC_CUDA(h, cudaMemsetAsync(h->pending.p, 0, sizeof(unsigned int), s));
+        if (h->pass_idx >= 2 && h->overlap_t) MC_CUDA(h, cudaMemsetAsync(h->pending_t.p, 0, sizeof(unsigned int), h->side));
         if (h->has_t) {
-            MC_CUDA(h, launch_select_scan(h->prob_t, g + L.off_t, n_ranks, stride, h->pending.p, s));
+            MC_CUDA(h, launch_select_scan(h->prob_t, g + L.off_t, n_ranks, stride, h->overlap_t ? h->pending_t.p : h->pending.p,
+                                          h->overlap_t ? h->side : s));
             h->launches += 1;
         }
         if (h->has_f) {
@@ -972,11 +1010,15 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
     }
     if (h->pass_idx < 2) return enqueue_pass(h, out, s, leader);
     // the second pass normally decides everything: go on to the closing stage and look at the counter later
-    u32_to_host_kernel<<<1, 1, 0, s>>>(h->h_pending.p, h->pending.p);
+    // (closing first: with the terminal problem on its own stream it ends with that stream joining this one, and the
+    // counter of that side is only final then)
+    int rc = enqueue_closing(h, out, s);
+    if (rc) return rc;
+    u32_to_host_kernel<<<1, 1, 0, s>>>(h->h_pending.p, h->pending.p, h->overlap_t ? h->pending_t.p : nullptr);
     MC_CUDA(h, cudaGetLastError());
     MC_CUDA(h, cudaEventRecord(h->ev_pending, s));
     h->pending_unchecked = true;
-    return enqueue_closing(h, out, s);
+    return MC_OK;
 }
 
 static int fetch_locked(mc_handle* h, mc_result* r, uint64_t* h_hist, double* h_fan, cudaStream_t s) {
@@ -1177,7 +1219,8 @@ int mc_debug_set_tuning(mc_handle* h, int side_cap, int no_side_lists, int waves
     if (!h) return MC_ERR_INVALID;
     std::lock_guard<std::mutex> lock(h->mu);
     h->side_cap_override = side_cap;
-    h->no_side_lists = no_side_lists != 0;
+    h->no_side_lists = (no_side_lists & 1) != 0;
+    h->no_overlap = (no_side_lists & 2) != 0;
     set_sim_tuning(waves, nblock);
     return MC_OK;
 }
@@ -1231,12 +1274,14 @@ int mc_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf, const void*
     const unsigned fused_launches = (generic.flags & MC_FLAG_TERMINAL_GIVEN) ? h->launches : 0u;
     const size_t cap = (size_t)mc_stage_max_words(p);
     MC_CUDA(h, h->stage.reserve(cap));
+    h->allow_overlap = true;             // this call owns the stage buffer from the first stage to the fetch
     int rc = stage_begin_locked(h, p, pf, d_pool, d_shocks, d_paths, d_terminal, h->stage.p, cap, s);
+    h->allow_overlap = false;
     if (rc) return rc;
     int done = 0;
     while (!done) {
         rc = stage_next_locked(h, h->stage.p, 1, h->stage.p, &done, s);
-        if (rc) return rc;
+        if (rc) { if (h->overlap_t) cudaStreamSynchronize(h->side); return rc; }
     }
     rc = fetch_locked(h, h_result, h_hist, h_fan, s);
     if (rc == MC_OK && (generic.flags & MC_FLAG_TERMINAL_GIVEN)) {

@@ -296,9 +296,10 @@ class Engine:
         self._peer_state = (key, bool(ok))
         return bool(ok)
 
-    def debug_set_tuning(self, side_cap: int = -1, no_side_lists: bool = False, waves: int = 0, nblock: int = 0):
+    def debug_set_tuning(self, side_cap: int = -1, no_side_lists: bool = False, waves: int = 0, nblock: int = 0,
+                         no_overlap: bool = False):
         """Test knobs (`mc_debug_set_tuning`), applied to this engine and the chunk engines it spawned."""
-        self._tuning = (int(side_cap), int(bool(no_side_lists)), int(waves), int(nblock))
+        self._tuning = (int(side_cap), int(bool(no_side_lists)) | (2 if no_overlap else 0), int(waves), int(nblock))
         for e in [self] + [x for x in getattr(self, "_chunk_engines", []) if x is not self]:
             e.check(e.lib.mc_debug_set_tuning(e.handle, *self._tuning))
 

@@ -266,6 +266,34 @@ def test_fan_chart_by_regeneration_equals_stored_paths(engine, mode, dtype):
     assert abs(a.tail_sum - b.tail_sum) < 1e-12 * abs(a.tail_sum)
 
 
+@pytest.mark.parametrize("dtype,n,t,tiny", [("float32", 300_007, 120, False), ("float64", 50_003, 64, False),
+                                              ("float32", 300_007, 120, True)])
+def test_terminal_selection_beside_the_fan_chart_changes_nothing(engine, dtype, n, t, tiny):
+    """mc_run enqueues the terminal-value problem of a fan-chart request (one row: brackets, two passes, scans, tail,
+    histogram) on a stream of its own, underneath the fan chart's passes over the whole matrix.  Every number must be
+    the one the single-stream order gives (mc_debug_set_tuning bit 1), also when tiny side lists force the passes
+    to stream the rows again and brackets to be revisited."""
+    spec = SimSpec.gbm(n, t, 100.0, 0.05, 0.2, 1 / 252, dtype=dtype, seed=77, store_paths=True, fan_chart=True,
+                       hist_bins=512, hist_range=(40.0, 260.0))
+    try:
+        engine.debug_set_tuning(side_cap=32 if tiny else -1, no_overlap=True)
+        a = engine.simulate(spec)
+        engine.debug_set_tuning(side_cap=32 if tiny else -1, no_overlap=False)
+        for _ in range(3):                      # back to back: nothing of one run may leak into the next
+            b = engine.simulate(spec)
+            assert a.pct == b.pct and a.pct_bounds == b.pct_bounds
+            assert (a.n, a.n_above, a.tail_count) == (b.n, b.n_above, b.tail_count)
+            assert (a.mean, a.std, a.tail_sum, a.min, a.max) == (b.mean, b.std, b.tail_sum, b.min, b.max)
+            assert np.array_equal(a.hist, b.hist)
+            for k in a.fan:
+                assert np.array_equal(a.fan[k], b.fan[k]), k
+    finally:
+        engine.debug_set_tuning()
+    last = b.paths[-1].cpu().numpy().astype(np.float64)
+    assert [b.pct[f"p{p}"] for p in port.REF_TERMINAL_PCTS] == list(np.percentile(last, port.REF_TERMINAL_PCTS))
+    assert np.array_equal(b.hist, np.histogram(last, bins=512, range=(40.0, 260.0))[0])
+
+
 def test_regeneration_restores_rows_when_the_side_lists_do_not_cover_a_pass(engine):
     """MC_FLAG_PATHS_VOLATILE: from the second narrowing pass on a chunk works from the values pass 1 kept; with
     32-entry lists they overflow, and the handle must simulate the chunk again by itself -- same fan chart."""
