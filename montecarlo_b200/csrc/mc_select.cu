@@ -1023,19 +1023,21 @@ __global__ void __launch_bounds__(FAST_THREADS) select_pass2_f32_kernel(const fl
     // the side lists of pass 1 hold every value of this chunk that lies in a pass-1 bracket: enough when each
     // interval of the row is inside one of those brackets and none of this block's eight lists overflowed
     const size_t side_slot = (row * gridDim.x + blockIdx.x) * SIDE_WARPS;
-    if (tid == 0) {
-        int ok = side.values != nullptr && side.chunks == gridDim.x;
-        if (ok) {
+    {
+        // one thread per interval and one per list, all at once (a single thread doing this alone was a chain of ~20
+        // dependent global loads, ~10 us per block with the other 255 threads at the barrier)
+        const bool have = side.values != nullptr && side.chunks == gridDim.x;
+        int ok = 1;
+        if (have && tid < n_iv) {
             const uint32_t* br = side.brackets + row * SIDE_BRACKET_WORDS;
             const int nb = (int)br[0];
-            for (int i = 0; i < n_iv && ok; ++i) {
-                int inside = 0;
-                for (int b = 0; b < nb; ++b) inside |= (br[1 + b] <= s_lo[i] && s_hi[i] <= br[1 + MAX_IV + b]) ? 1 : 0;
-                ok = inside;
-            }
-            for (int w = 0; w < SIDE_WARPS && ok; ++w) ok = side.counts[side_slot + w] <= side.cap;
+            int inside = 0;
+            for (int b = 0; b < nb; ++b) inside |= (br[1 + b] <= s_lo[tid] && s_hi[tid] <= br[1 + MAX_IV + b]) ? 1 : 0;
+            ok = inside;
         }
-        s_use_side = ok;
+        if (have && tid >= 32 && tid < 32 + SIDE_WARPS) ok = side.counts[side_slot + (tid - 32)] <= side.cap;
+        const int all_ok = __syncthreads_and(ok);
+        if (tid == 0) s_use_side = have && all_ok;
     }
     __syncthreads();
 

@@ -9,6 +9,8 @@ from montecarlo_b200.engine import get_engine
 
 wl = sys.argv[1] if len(sys.argv) > 1 else "c2"
 eng = get_engine(0)
+if os.environ.get("MC_SIDE_CAP"):          # experiments: capacity (values) of a warp's side list
+    eng.debug_set_tuning(side_cap=int(os.environ["MC_SIDE_CAP"]))
 spec, pool = bench.make_spec(wl, 1)
 pool_dev = eng.to_device(pool, torch.float32) if pool is not None else None
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=eng.device)
