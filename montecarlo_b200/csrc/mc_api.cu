@@ -330,7 +330,7 @@ int select_rows(mc_handle* h, const void* d_x, int dtype, uint64_t rows, uint64_
     MC_CUDA(h, launch_reduce_partials(h->partials.p, 0, st, 0, sp.m_local, s));
     MC_CUDA(h, launch_select_sample(sp, st + STAGE0_HEADER, s));
     MC_CUDA(h, launch_select_brackets(sp, st, STAGE0_HEADER, 7, 1, w0, h->dev.max_smem_optin, s));
-    count += 3;
+    count += sp.pilot_in_place ? 2 : 3;       // kernels only (the pilot is read in place: no sampling kernel)
     for (int pass = 0;; ++pass) {
         MC_CUDA(h, launch_select_pass(sp, pass == 0, st, h->dev.sm_count, s));
         MC_CUDA(h, cudaMemsetAsync(h->pending.p, 0, sizeof(unsigned int), s));
@@ -824,11 +824,11 @@ static int stage_begin_locked(mc_handle* h, const mc_params* p, const mc_portfol
     h->launches += 1;
     if (h->has_t && h->prob_t.m_local) {
         MC_CUDA(h, launch_select_sample(h->prob_t, out + L.off_t, s));
-        h->launches += 1;
+        h->launches += h->prob_t.pilot_in_place ? 0 : 1;       // read in place: no sampling kernel
     }
     if (h->has_f && h->prob_f.m_local) {
         MC_CUDA(h, launch_select_sample(h->prob_f, out + L.off_f, s));
-        h->launches += 1;
+        h->launches += h->prob_f.pilot_in_place ? 0 : 1;
     }
     h->next_words = L.words;
     h->active = true;
@@ -1001,11 +1001,11 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
         if (h->has_t) {
             MC_CUDA(h, launch_select_scan(h->prob_t, g + L.off_t, n_ranks, stride, h->overlap_t ? h->pending_t.p : h->pending.p,
                                           h->overlap_t ? h->side : s));
-            h->launches += 1;
+            h->launches += 2;                 // per interval, then per row
         }
         if (h->has_f) {
             MC_CUDA(h, launch_select_scan(h->prob_f, g + L.off_f, n_ranks, stride, h->pending.p, s));
-            h->launches += 1;
+            h->launches += 2;
         }
     }
     if (h->pass_idx < 2) return enqueue_pass(h, out, s, leader);
@@ -1016,6 +1016,7 @@ static int stage_next_locked(mc_handle* h, const void* d_gathered, uint32_t n_ra
     if (rc) return rc;
     u32_to_host_kernel<<<1, 1, 0, s>>>(h->h_pending.p, h->pending.p, h->overlap_t ? h->pending_t.p : nullptr);
     MC_CUDA(h, cudaGetLastError());
+    h->launches += 1;
     MC_CUDA(h, cudaEventRecord(h->ev_pending, s));
     h->pending_unchecked = true;
     return MC_OK;
@@ -1037,6 +1038,7 @@ static int fetch_locked(mc_handle* h, mc_result* r, uint64_t* h_hist, double* h_
         // the layout below keeps the histogram's slot even when it is not wanted
         unsigned long long* dst = reinterpret_cast<unsigned long long*>(hp);
         const unsigned int blocks = (unsigned int)((na + nb + nc + 255) / 256 < 64 ? (na + nb + nc + 255) / 256 : 64);
+        h->launches += (want_hist || !want_fan) ? 1 : 2;
         if (want_hist || !want_fan) {
             words_to_host_kernel<<<blocks, 256, 0, s>>>(dst, reinterpret_cast<const unsigned long long*>(h->res.p), na,
                                                         reinterpret_cast<const unsigned long long*>(h->hist_total.p), nb,
