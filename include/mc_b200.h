@@ -157,7 +157,9 @@ const char* mc_last_error(const mc_handle* h);   /* h may be NULL: last create()
  *   d_terminal : [n_paths] final prices (always written)
  *   h_result   : scalars;  h_hist: uint64[hist_bins] or NULL;
  *   h_fan      : double[n_path_pcts * (n_steps+1)] or NULL (MC_FLAG_FAN_CHART)
- * Synchronises `stream` before returning.
+ * Synchronises `stream` before returning.  A request with both a fan chart and terminal percentiles runs the (one-row)
+ * terminal selection on a stream the handle owns, forked from and joined back into `stream` by events: all of the
+ * call's work is ordered after what `stream` held before the call and complete when the call returns.
  */
 int mc_run(mc_handle* h, const mc_params* p, const mc_portfolio* pf,
            const void* d_pool, const void* d_shocks, void* d_paths, void* d_terminal,

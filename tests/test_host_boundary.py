@@ -159,3 +159,19 @@ def test_fast_host_paths_equal_the_reference_expressions():
         col = df["log_ret"]
         assert np.array_equal(returns, col.dropna().values)
         assert rvol_last == float(df["rvol_20"].iloc[-1])
+
+
+def test_fused_request_mirrors_what_mc_run_sharded_accepts():
+    """Engine.fused_request decides, identically on every rank and without a GPU, whether a sharded run goes through
+    `mc_run_sharded` (include/mc_b200.h: no fan chart, an explicit histogram range of <= 16384 bins, <= 16 ranks) or
+    through the staged protocol."""
+    from montecarlo_b200.engine import Engine
+    from montecarlo_b200.spec import SimSpec
+    gbm = lambda **kw: SimSpec.gbm(1000, 10, 100.0, 0.05, 0.2, 1 / 252, **kw)
+    assert Engine.fused_request(gbm(), 8)
+    assert Engine.fused_request(gbm(hist_bins=2048, hist_range=(50.0, 200.0)), 2)
+    assert Engine.fused_request(gbm(hist_bins=16384, hist_range=(50.0, 200.0)), 16)
+    assert not Engine.fused_request(gbm(hist_bins=2048), 2)                               # range from the data
+    assert not Engine.fused_request(gbm(hist_bins=16385, hist_range=(50.0, 200.0)), 2)
+    assert not Engine.fused_request(gbm(store_paths=True, fan_chart=True), 2)
+    assert not Engine.fused_request(gbm(), 17)
