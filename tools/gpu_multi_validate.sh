@@ -1,5 +1,5 @@
 # N-GPU validation (inside gpurun --gpus W): NCCL parity of the global jobs, default bench with the multi-rank extras
-# (c4, c4fan), device timeline of one sharded c2 job.   usage: bash tools/gpu_call13.sh W
+# (c4, c4fan), device timeline of one sharded c2 job.   usage: bash tools/gpu_multi_validate.sh W
 set -x
 W=${1:-8}
 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $W --master-addr 127.0.0.1 --master-port 29511 tools/nccl_parity.py > gpurun_out/nccl_parity_${W}gpu.txt 2> gpurun_out/nccl_parity_${W}gpu.err; echo parity rc=$?; tail -9 gpurun_out/nccl_parity_${W}gpu.txt; grep -c true gpurun_out/nccl_parity_${W}gpu.txt
