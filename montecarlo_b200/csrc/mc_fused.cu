@@ -549,7 +549,7 @@ __global__ void __launch_bounds__(SEL_THREADS) fused_select_kernel(const FusedAr
     unsigned int* s_sub = reinterpret_cast<unsigned int*>(smem_dyn);                  // [SUB_BINS]
     Key* s_keys = reinterpret_cast<Key*>(s_sub + SUB_BINS);                           // [SEL_SORT]
     Key* s_cand = s_keys + SEL_SORT;                                                  // [SEL_CAND_SMEM / sizeof(Key)]
-    __shared__ unsigned int s_cnt[FUSED_MAX_RANKS], s_base[FUSED_MAX_RANKS + 1];
+    __shared__ unsigned int s_cnt[FUSED_MAX_RANKS];
     __shared__ unsigned int s_warp[32];
     __shared__ unsigned int s_n;
     __shared__ SelItem s_items[SEL_ITEMS];
@@ -582,47 +582,54 @@ __global__ void __launch_bounds__(SEL_THREADS) fused_select_kernel(const FusedAr
     const bool active = status == FUSED_OK && slot < P.n_slots;
     if (active) {
         unsigned int total = 0;
-        for (unsigned int r = 0; r < R; ++r) { if (tid == 0) s_base[r] = total; total += s_cnt[r]; }
+        for (unsigned int r = 0; r < R; ++r) total += s_cnt[r];
         const size_t off = P.off[slot];
+        // The slot's candidates are copied into shared memory when they fit: whole keys, or -- fp32 keys of one bin of the
+        // window differ in their low bits only (a bin is ~4000 - 12000 consecutive keys) -- as 16-bit offsets from the
+        // bin's first key, which doubles what fits.  At 8 ranks x 10M paths a central bin holds ~50,000 values: beyond the
+        // 40,960 whole keys, and every later look at them was another sweep over NVLink (K5 65 us against 26 us on one GPU).
+        Key bin_lo, bin_hi;
+        bin_key_range<Key>(a.win, P.bin[slot], &bin_lo, &bin_hi);
         const bool in_smem = (size_t)total * sizeof(Key) <= SEL_CAND_SMEM;
-        // every candidate of the slot, four loads in flight per thread: from the ranks' lists, or -- after the
-        // first such sweep has copied them -- from shared memory
-        // (one flat index space over all ranks' lists: the loads from every peer are in flight together -- rank after
-        // rank, each list cost its own NVLink round trip: 51 us instead of 23 at 8 GPUs)
+        const bool in_smem16 = !in_smem && sizeof(Key) == 4 && (unsigned long long)(bin_hi - bin_lo) <= 0xFFFFull &&
+                               (size_t)total * 2 <= SEL_CAND_SMEM;
+        unsigned short* s_cand16 = reinterpret_cast<unsigned short*>(s_cand);
+        // every candidate of the slot, eight loads in flight per thread: from the ranks' lists, or -- after the
+        // first such sweep has copied them -- from shared memory.
+        // Warps are dealt out to the ranks (warp w reads rank w mod R's list), so the loads from every peer are in flight
+        // together -- rank after rank, each list cost its own NVLink round trip: 51 us instead of 23 at 8 GPUs -- and a
+        // candidate's address is its list plus an index.  (One flat index space over all lists did the same, but finding
+        // the list of position g took ~80 instructions per candidate: 16 us of K5 at 8 ranks x 10M paths.)
         auto sweep_lists = [&](auto f) {
-            const Key* base_r[FUSED_MAX_RANKS];
+            const unsigned int r = (unsigned int)warp % R, sub = (unsigned int)warp / R;
+            const unsigned int n_sub = ((unsigned int)(SEL_THREADS / 32) - 1u - r) / R + 1u;       // warps on rank r's list
+            const bool idle = R > (unsigned int)(SEL_THREADS / 32);                                 // (R <= 16: never)
+            const Key* list = cand_of<Key>(a, (int)r) + off;
+            unsigned int base = 0;                          // where this rank's candidates start in the concatenation
+            for (unsigned int q = 0; q < r; ++q) base += s_cnt[q];
+            const unsigned int cnt = idle ? 0u : s_cnt[r], step = 32u * n_sub;
+            constexpr int U = sizeof(Key) == 8 ? 4 : 8;       // (a block of 1024 threads has 64 registers a thread)
+            for (unsigned int j = sub * 32u + lane; j < cnt; j += (unsigned int)U * step) {
+                Key k[U];
 #pragma unroll
-            for (int r = 0; r < FUSED_MAX_RANKS; ++r) base_r[r] = r < (int)R ? cand_of<Key>(a, r) + off : nullptr;
-            auto locate = [&](unsigned int g) -> const Key* {        // position g of the concatenation -> its address
-                unsigned int r = 0;
+                for (int u = 0; u < U; ++u) k[u] = j + u * step < cnt ? __ldcg(list + j + u * step) : (Key)0;
 #pragma unroll
-                for (int q = 1; q < FUSED_MAX_RANKS; ++q) r += (q < (int)R && g >= s_base[q]) ? 1u : 0u;
-                const Key* b = base_r[0];
-#pragma unroll
-                for (int q = 1; q < FUSED_MAX_RANKS; ++q) b = r == (unsigned)q ? base_r[q] : b;
-                return b + (g - s_base[r]);
-            };
-            for (unsigned int g = tid; g < total; g += 4u * SEL_THREADS) {
-                Key k[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) k[u] = g + u * SEL_THREADS < total ? __ldcg(locate(g + u * SEL_THREADS)) : (Key)0;
-#pragma unroll
-                for (int u = 0; u < 4; ++u) if (g + u * SEL_THREADS < total) f(k[u], g + u * SEL_THREADS);
+                for (int u = 0; u < U; ++u) if (j + u * step < cnt) f(k[u], base + j + u * step);
             }
         };
         if (tid == 0) {                 // work list: key ranges of this bin that still hold undecided targets
             int m = 0;
             for (int t = 0; t < a.n_targets; ++t) if (P.target_slot[t] == slot) s_tl[m++] = t;
-            Key lo, hi;
-            bin_key_range<Key>(a.win, P.bin[slot], &lo, &hi);
-            s_items[0] = SelItem{(unsigned long long)lo, (unsigned long long)hi, 0ull, total, 0, m};
+            s_items[0] = SelItem{(unsigned long long)bin_lo, (unsigned long long)bin_hi, 0ull, total, 0, m};
             s_nitems = 1;
         }
-        __syncthreads();                // s_base
+        __syncthreads();
         if (in_smem) sweep_lists([&](Key k, unsigned int pos) { s_cand[pos] = k; });
+        else if (in_smem16) sweep_lists([&](Key k, unsigned int pos) { s_cand16[pos] = (unsigned short)(k - bin_lo); });
         __syncthreads();
         auto for_each = [&](auto f) {
             if (in_smem) { for (unsigned int j = tid; j < total; j += SEL_THREADS) f(s_cand[j]); }
+            else if (in_smem16) { for (unsigned int j = tid; j < total; j += SEL_THREADS) f((Key)(bin_lo + (Key)s_cand16[j])); }
             else sweep_lists([&](Key k, unsigned int) { f(k); });
         };
         if ((unsigned long long)total != P.pop[slot]) status = FUSED_INCONSISTENT;

@@ -190,6 +190,37 @@ def test_sharded_run_through_peer_memory_equals_one_gpu(engine, case, world):
         assert res.mean == first.mean and res.std == first.std and res.tail_sum == first.tail_sum
 
 
+@pytest.mark.parametrize("dtype,per_rank,steps", [("float32", 8_500_003, 8), ("float64", 6_000_001, 4),
+                                                   ("float32", 17_000_001, 4)])
+def test_sharded_run_with_bins_too_full_for_whole_keys_in_shared_memory(engine, dtype, per_rank, steps):
+    """Eight ranks at the bench's scale: the key-histogram bin of a central percentile then holds 40,000 - 90,000 values.
+    fp32, <= 81,920: the select kernel keeps them as 16-bit offsets from the bin's first key; beyond that, and for
+    fp64 keys beyond 20,480, it sweeps the ranks' lists (over NVLink on real GPUs) once per narrowing step.  Either way
+    the order statistics are NumPy's on the union of the ranks' values, and every rank holds them."""
+    world = 8
+    n = world * per_rank
+    mk = lambda: SimSpec.gbm(n, steps, 100.0, 0.05, 0.2, 1 / 252, dtype=dtype, seed=2024, hist_bins=1024,
+                             hist_range=(80.0, 125.0))
+    results, terminal = _sharded_emulated(mk(), None, world)
+    v = terminal.cpu().numpy().astype(np.float64)
+    del terminal
+    want = list(np.percentile(v, PCTS))
+    counts = np.histogram(v, bins=1024, range=(80.0, 125.0))[0]
+    thr = want[list(PCTS).index(5)]
+    tail = v[v <= thr]
+    first = results[0][0]
+    for res, hist in results:
+        assert res.status == 0 and res.n == n
+        assert [res.pct[i] for i in range(len(PCTS))] == want
+        assert np.array_equal(hist.astype(np.int64), counts)
+        assert res.tail_count == tail.size and abs(res.tail_sum - tail.sum()) <= 1e-9 * tail.sum()
+        assert (res.mean, res.std, res.tail_sum) == (first.mean, first.std, first.tail_sum)
+    assert abs(first.mean - v.mean()) <= 1e-9 * v.mean()
+    single = engine.simulate(mk())                          # the same job on one handle: its own (local) lists, same code
+    assert list(single.pct.values()) == want and single.tail_count == tail.size
+    assert np.array_equal(single.hist, counts)
+
+
 def test_sharded_run_more_ranks_than_paths(engine):
     spec = SimSpec.gbm(5, 9, 100.0, 0.05, 0.2, 1 / 252, dtype="float32", seed=4)
     results, terminal = _sharded_emulated(spec, None, 8)
