@@ -587,7 +587,7 @@ __global__ void __launch_bounds__(SEL_THREADS) fused_select_kernel(const FusedAr
         // The slot's candidates are copied into shared memory when they fit: whole keys, or -- fp32 keys of one bin of the
         // window differ in their low bits only (a bin is ~4000 - 12000 consecutive keys) -- as 16-bit offsets from the
         // bin's first key, which doubles what fits.  At 8 ranks x 10M paths a central bin holds ~50,000 values: beyond the
-        // 40,960 whole keys, and every later look at them was another sweep over NVLink (K5 65 us against 26 us on one GPU).
+        // 40,960 whole keys, and every later look at them was another sweep over NVLink (K5 was 64 us at 8 GPUs against 25 us on one; now 33 us).
         Key bin_lo, bin_hi;
         bin_key_range<Key>(a.win, P.bin[slot], &bin_lo, &bin_hi);
         const bool in_smem = (size_t)total * sizeof(Key) <= SEL_CAND_SMEM;
@@ -608,14 +608,29 @@ __global__ void __launch_bounds__(SEL_THREADS) fused_select_kernel(const FusedAr
             unsigned int base = 0;                          // where this rank's candidates start in the concatenation
             for (unsigned int q = 0; q < r; ++q) base += s_cnt[q];
             const unsigned int cnt = idle ? 0u : s_cnt[r], step = 32u * n_sub;
-            constexpr int U = sizeof(Key) == 8 ? 4 : 8;       // (a block of 1024 threads has 64 registers a thread)
-            for (unsigned int j = sub * 32u + lane; j < cnt; j += (unsigned int)U * step) {
-                Key k[U];
+            // 16-byte loads (the lists start on 16-byte boundaries: capacities are multiples of four entries), four in
+            // flight per lane: 64 KB per block on the wire instead of 32 KB in 4-byte pieces -- a sweep over 8 ranks'
+            // lists is a handful of NVLink round trips
+            constexpr unsigned int VEC = 16u / (unsigned int)sizeof(Key);
+            constexpr int U = 4;
+            const uint4* list4 = reinterpret_cast<const uint4*>(list);
+            const unsigned int n_vec = cnt / VEC;
+            auto give = [&](const uint4& q, unsigned int at) {       // at: index of the vector's first entry
+                if constexpr (sizeof(Key) == 4) {
+                    f((Key)q.x, base + at); f((Key)q.y, base + at + 1u); f((Key)q.z, base + at + 2u); f((Key)q.w, base + at + 3u);
+                } else {
+                    f((Key)(((unsigned long long)q.y << 32) | q.x), base + at);
+                    f((Key)(((unsigned long long)q.w << 32) | q.z), base + at + 1u);
+                }
+            };
+            for (unsigned int j = sub * 32u + lane; j < n_vec; j += (unsigned int)U * step) {
+                uint4 q[U];
 #pragma unroll
-                for (int u = 0; u < U; ++u) k[u] = j + u * step < cnt ? __ldcg(list + j + u * step) : (Key)0;
+                for (int u = 0; u < U; ++u) q[u] = j + u * step < n_vec ? __ldcg(list4 + j + u * step) : make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
-                for (int u = 0; u < U; ++u) if (j + u * step < cnt) f(k[u], base + j + u * step);
+                for (int u = 0; u < U; ++u) if (j + u * step < n_vec) give(q[u], (j + u * step) * VEC);
             }
+            for (unsigned int j = n_vec * VEC + sub * 32u + lane; j < cnt; j += step) f(__ldcg(list + j), base + j);
         };
         if (tid == 0) {                 // work list: key ranges of this bin that still hold undecided targets
             int m = 0;
