@@ -294,6 +294,28 @@ def test_terminal_selection_beside_the_fan_chart_changes_nothing(engine, dtype, 
     assert np.array_equal(b.hist, np.histogram(last, bins=512, range=(40.0, 260.0))[0])
 
 
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+def test_brackets_that_miss_are_revisited_also_with_the_terminal_selection_on_its_own_stream(engine, dtype):
+    """Injected shocks SORTED across the paths: every row of the path matrix is sorted, so the pilot (the first 131072
+    values of a row) holds the smallest ones and the brackets of the upper percentiles miss.  The selection then narrows
+    the gap beside the bracket in further passes -- after the closing stage has already been enqueued once -- while the
+    terminal-value problem runs on the handle's own stream.  Results: NumPy's, bit for bit."""
+    n, t = 300_007, 3
+    z = np.sort(np.random.RandomState(3).normal(size=(t, n)), axis=1)
+    spec = SimSpec.gbm(n, t, 100.0, 0.05, 0.2, 1 / 252, dtype=dtype, shock="injected", store_paths=True, fan_chart=True,
+                       hist_bins=128, hist_range=(90.0, 112.0))
+    out = engine.simulate(spec, shocks=z)
+    paths = out.paths.cpu().numpy().astype(np.float64)
+    assert np.all(np.diff(paths[-1]) >= 0)                                    # the premise: sorted rows
+    assert out.launches > 40                       # 26 launches when the brackets hold; measured here: 130 - 143
+    ref_fan = np.percentile(paths, port.REF_PATH_PCTS, axis=1)
+    assert np.array_equal(np.stack([out.fan[f"p{p}"] for p in port.REF_PATH_PCTS]), ref_fan)
+    assert [out.pct[f"p{p}"] for p in port.REF_TERMINAL_PCTS] == list(np.percentile(paths[-1], port.REF_TERMINAL_PCTS))
+    assert np.array_equal(out.hist, np.histogram(paths[-1], bins=128, range=(90.0, 112.0))[0])
+    thr = out.pct["p5"]
+    assert out.tail_count == int((paths[-1] <= thr).sum())
+
+
 def test_regeneration_restores_rows_when_the_side_lists_do_not_cover_a_pass(engine):
     """MC_FLAG_PATHS_VOLATILE: from the second narrowing pass on a chunk works from the values pass 1 kept; with
     32-entry lists they overflow, and the handle must simulate the chunk again by itself -- same fan chart."""
