@@ -8,6 +8,7 @@ gloo backend in tests."""
 from __future__ import annotations
 
 import ctypes as C
+import functools
 import threading
 from dataclasses import dataclass
 from typing import Optional
@@ -124,6 +125,11 @@ class _CudaStageBackend:
             e.check(e.lib.mc_stage_next(e.handle, C.c_void_p(gathered.data_ptr()), n_ranks, self._ptr(self.stage),
                                         C.byref(done), e.stream_ptr()))
         return bool(done.value)
+
+
+@functools.lru_cache(maxsize=64)
+def _pct_names(pcts) -> tuple:
+    return tuple(f"p{p:g}" for p in pcts)
 
 
 class Engine:
@@ -385,10 +391,11 @@ class Engine:
         return self._pack(spec, res, hist, fan, terminal, None, offset)
 
     def _pack(self, spec, res, hist, fan, terminal, paths, offset) -> RunOutput:
-        names = [f"p{p:g}" for p in spec.pcts]
-        pct = {k: float(res.pct[i]) for i, k in enumerate(names)}
-        bounds = {k: (float(res.pct_lo[i]), float(res.pct_hi[i])) for i, k in enumerate(names)}
-        fan_d = {f"p{p:g}": fan[i] for i, p in enumerate(spec.path_pcts)} if fan is not None else None
+        names = _pct_names(tuple(spec.pcts))
+        k = len(names)
+        pct = dict(zip(names, res.pct[:k]))                    # a slice of a ctypes array is one call, not one per element
+        bounds = dict(zip(names, zip(res.pct_lo[:k], res.pct_hi[:k])))
+        fan_d = dict(zip(_pct_names(tuple(spec.path_pcts)), fan)) if fan is not None else None
         return RunOutput(spec=spec, n=int(res.n), n_above=int(res.n_above), mean=float(res.mean), std=float(res.std),
                          min=float(res.min), max=float(res.max), pct=pct, pct_bounds=bounds,
                          tail_count=int(res.tail_count), tail_sum=float(res.tail_sum),
