@@ -9,6 +9,7 @@ same single progress callback (app.py:597-598), same nine result keys (app.py:64
 Everything new is keyword-only with reference-equivalent defaults."""
 from __future__ import annotations
 
+import functools
 import math
 import os
 from typing import Dict, Optional
@@ -100,6 +101,14 @@ def _to_host(t):
     return t.to("cpu").numpy()
 
 
+@functools.lru_cache(maxsize=16)
+def _hist_edges(lo: float, hi: float, bins: int) -> np.ndarray:
+    """np.histogram's edges for (lo, hi, bins): the same (read-only) array for repeated calls with the same range."""
+    e = np.linspace(lo, hi, bins + 1)
+    e.setflags(write=False)
+    return e
+
+
 def _result_dict(out, s0, return_paths: str) -> Dict:
     res = {}
     paths, final = out.paths, out.terminal
@@ -121,7 +130,7 @@ def _result_dict(out, s0, return_paths: str) -> Dict:
             res[k] = np.float64(v)
     if out.hist is not None:
         res["histogram"] = {"counts": out.hist, "range": out.hist_range,
-                            "edges": np.linspace(out.hist_range[0], out.hist_range[1], len(out.hist) + 1)}
+                            "edges": _hist_edges(out.hist_range[0], out.hist_range[1], len(out.hist))}
     res["timing"] = {"sim_ms": out.sim_ms, "total_ms": out.total_ms, "launches": out.launches}
     return res
 
