@@ -175,3 +175,28 @@ def test_fused_request_mirrors_what_mc_run_sharded_accepts():
     assert not Engine.fused_request(gbm(hist_bins=16385, hist_range=(50.0, 200.0)), 2)
     assert not Engine.fused_request(gbm(store_paths=True, fan_chart=True), 2)
     assert not Engine.fused_request(gbm(), 17)
+
+
+def test_make_params_cache_hands_out_independent_copies():
+    """The parameter struct of a job is cached by everything it is built from; callers get copies (the engine edits
+    `flags` for its staged fall-back), invalid specs never get in, portfolio specs are always rebuilt."""
+    import numpy as np
+    from montecarlo_b200 import PortfolioSpec
+    from montecarlo_b200.spec import SimSpec, make_params, _PARAMS_CACHE
+    mk = lambda **kw: SimSpec.gbm(1234, 7, 100.0, 0.05, 0.2, 1 / 252, seed=5, hist_bins=16, hist_range=(50.0, 200.0), **kw)
+    a = make_params(mk(), n_local=100, path_offset=7, n_ranks=3)
+    b = make_params(mk(), n_local=100, path_offset=7, n_ranks=3)            # another spec object, same job: the cached struct
+    assert bytes(a) == bytes(b) and a is not b
+    a.flags |= 16
+    assert make_params(mk(), n_local=100, path_offset=7, n_ranks=3).flags == b.flags
+    c = make_params(mk(), n_local=101, path_offset=7, n_ranks=3)
+    assert c.n_paths == 101 and b.n_paths == 100
+    assert make_params(mk(dtype="float64")).dtype != b.dtype
+    n_before = len(_PARAMS_CACHE)
+    with pytest.raises(ValueError):
+        make_params(SimSpec.gbm(10, 5, 100.0, 0.05, 0.2, pcts=(50.0, 5.0)))
+    assert len(_PARAMS_CACHE) == n_before
+    d = 2
+    pf = PortfolioSpec(s0=np.full(d, 100.0), mu=0.05, sigma=np.full(d, 0.2), weights=np.full(d, 0.5), corr=np.eye(d), dt=1 / 252)
+    sp = SimSpec(n_paths=10, n_steps=5, s0=100.0, shock="normal", var_model="const", portfolio=pf)
+    assert make_params(sp).n_assets == d and len(_PARAMS_CACHE) == n_before
