@@ -7,6 +7,7 @@ The orchestration is backend-agnostic so the same loop is exercised on CPU with 
 gloo backend in tests."""
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import functools
 import threading
@@ -234,13 +235,15 @@ class Engine:
             if shocks_t is not None:
                 raise ValueError("fan chart by regeneration needs device-generated shocks")
             return self._simulate_regenerating(spec, pool_t, group, world, rank, offset, n_local, dt)
-        with torch.cuda.device(self.device):
+        # every buffer below names its device and the C entry points guard their own: the context manager (~8 us) is only
+        # entered when the calling thread sits on another GPU
+        with (torch.cuda.device(self.device) if torch.cuda.current_device() != self.device_index else contextlib.nullcontext()):
             terminal = torch.empty(n_local, dtype=dt, device=self.device)
             paths = torch.empty((spec.n_steps + 1, n_local), dtype=dt, device=self.device) if spec.store_paths else None
             params = make_params(spec, path_offset=offset, n_local=n_local, n_ranks=world)
             pf = make_portfolio(spec)
             res = L.McResult()
-            hist = np.zeros(spec.hist_bins, dtype=np.uint64) if spec.hist_bins else None
+            hist = np.zeros(spec.hist_bins, dtype=np.int64) if spec.hist_bins else None     # the library writes uint64 counts
             fan = np.zeros((len(spec.path_pcts), spec.n_steps + 1)) if (spec.fan_chart and spec.path_pcts) else None
             hist_p = C.c_void_p(hist.ctypes.data) if hist is not None else C.c_void_p(0)
             fan_p = C.c_void_p(fan.ctypes.data) if fan is not None else C.c_void_p(0)
@@ -399,7 +402,7 @@ class Engine:
         return RunOutput(spec=spec, n=int(res.n), n_above=int(res.n_above), mean=float(res.mean), std=float(res.std),
                          min=float(res.min), max=float(res.max), pct=pct, pct_bounds=bounds,
                          tail_count=int(res.tail_count), tail_sum=float(res.tail_sum),
-                         hist=hist.astype(np.int64) if hist is not None else None,
+                         hist=(hist if hist.dtype == np.int64 else hist.astype(np.int64)) if hist is not None else None,
                          hist_range=(float(res.hist_lo), float(res.hist_hi)) if hist is not None else None,
                          fan=fan_d, terminal=terminal, paths=paths, sim_ms=float(res.sim_ms),
                          total_ms=float(res.total_ms), launches=int(res.launches), path_offset=offset)
