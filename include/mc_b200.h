@@ -207,6 +207,11 @@ int mc_fetch_result(mc_handle* h, mc_result* h_result, uint64_t* h_hist, double*
  * mc_run_sharded needs params->n_ranks == n_ranks of the attachment and a request the fused closing accepts (no
  * fan chart, an explicit histogram range, <= 16384 bins); otherwise MC_ERR_INVALID and the staged protocol above
  * applies.  A peer that does not arrive within 20 s fails the run (MC_ERR_STATE from mc_fetch_result).
+ *
+ * With params->n_ranks <= 1 on a handle without peers, mc_run_sharded + mc_fetch_result are the two halves of mc_run
+ * for the same requests: enqueue only, then wait and read.  A caller that alternates between two handles (each with
+ * its own stream) keeps the GPU busy while a result travels; mc_result.status != 0 means the key window missed and
+ * the reductions must be redone by mc_run with MC_FLAG_TERMINAL_GIVEN on the terminal values already there.
  */
 int mc_peer_export(mc_handle* h, uint32_t n_ranks, void* out_ipc_handle /* 64 bytes, may be NULL */,
                    void** out_local_ptr, uint64_t* out_bytes);

@@ -10,11 +10,11 @@ from .api import (garch_monte_carlo, garch_monte_carlo_from_close, calibrate_gar
 from .spec import PortfolioSpec, SimSpec, make_params, shard_range
 
 __all__ = ["garch_monte_carlo", "garch_monte_carlo_from_close", "calibrate_garch", "simulate_gbm", "simulate_portfolio", "bootstrap_pool",
-           "SimSpec", "PortfolioSpec", "make_params", "shard_range", "Engine", "get_engine"]
+           "SimSpec", "PortfolioSpec", "make_params", "shard_range", "Engine", "get_engine", "Pipeline"]
 
 
 def __getattr__(name):
-    if name in ("Engine", "get_engine", "run_stages", "RunOutput"):
+    if name in ("Engine", "get_engine", "run_stages", "RunOutput", "Pipeline"):
         from . import engine
         return getattr(engine, name)
     raise AttributeError(name)

@@ -1159,7 +1159,10 @@ int mc_run_sharded(mc_handle* h, const mc_params* p, const mc_portfolio* pf, con
     std::lock_guard<std::mutex> lock(h->mu);
     if (!p) return fail(h, MC_ERR_INVALID, "params is NULL");
     if (!fused_eligible(*p)) return fail(h, MC_ERR_INVALID, "mc_run_sharded: this request needs the staged protocol (fan chart, data-dependent histogram range)");
-    return fused_enqueue(h, p, pf, d_pool, d_shocks, d_paths, d_terminal, true, static_cast<cudaStream_t>(stream));
+    // one rank, no peers: the enqueue half of mc_run (a caller that keeps several jobs in flight on several handles)
+    const bool alone = ranks_of(*p) == 1 && !(h->peers_attached && h->peers.n_ranks != 1);
+    if (alone && p->n_paths != p->n_paths_global) return fail(h, MC_ERR_INVALID, "n_ranks = 1: n_paths must equal n_paths_global");
+    return fused_enqueue(h, p, pf, d_pool, d_shocks, d_paths, d_terminal, !alone, static_cast<cudaStream_t>(stream));
 }
 
 int mc_peer_export(mc_handle* h, uint32_t n_ranks, void* out_ipc_handle, void** out_local_ptr, uint64_t* out_bytes) {

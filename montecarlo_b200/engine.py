@@ -269,6 +269,57 @@ class Engine:
                     self.check(self.lib.mc_fetch_result(self.handle, C.byref(res), hist_p, fan_p, self.stream_ptr()))
         return self._pack(spec, res, hist, fan, terminal, paths if keep_paths else None, offset)
 
+    # ------------------------------------------------------------------ enqueue now, read later
+    def submit(self, spec: SimSpec, pool=None, shocks=None):
+        """Enqueue a single-GPU job on the current stream and return at once; `collect(ticket)` waits for it and returns
+        what `simulate` would have.  For requests whose reductions the fused closing takes (`fused_request`: no fan chart,
+        no stored paths, an explicit histogram range) -- `mc_run_sharded` + `mc_fetch_result` with one rank
+        (include/mc_b200.h).  One job in flight per engine: alternate between engines (`Pipeline`) to overlap the host
+        side and the closing of one job with the simulation of the next."""
+        if getattr(self, "_in_flight", False):
+            raise RuntimeError("this engine already has a job in flight: collect() it first, or use another engine")
+        if spec.store_paths or not self.fused_request(spec, 1):
+            raise ValueError("submit() takes jobs without stored paths / fan chart and with an explicit histogram range")
+        dt = self._torch_dtype(spec)
+        n = spec.n_paths
+        pool_t = None
+        if spec.shock == "bootstrap":
+            if pool is None:
+                raise ValueError("bootstrap shocks need a pool")
+            pool_t = self._stage_pool(pool, dt)
+            spec.pool_len = int(pool_t.numel())
+        shocks_t = self.to_device(shocks, dt) if spec.shock == "injected" else None
+        stream = torch.cuda.current_stream(self.device)
+        with torch.cuda.device(self.device):
+            terminal = torch.empty(n, dtype=dt, device=self.device)
+            params = make_params(spec, path_offset=0, n_local=n, n_ranks=1)
+            pf = make_portfolio(spec)
+            ptr = _CudaStageBackend._ptr
+            self.check(self.lib.mc_run_sharded(self.handle, C.byref(params), C.byref(pf) if pf else None, ptr(pool_t),
+                                               ptr(shocks_t), None, ptr(terminal), C.c_void_p(stream.cuda_stream)))
+        self._in_flight = True
+        return dict(spec=spec, params=params, pf=pf, pool=pool_t, shocks=shocks_t, terminal=terminal, stream=stream)
+
+    def collect(self, ticket) -> RunOutput:
+        """Wait for the job of `submit` and return its RunOutput."""
+        spec, params, pf = ticket["spec"], ticket["params"], ticket["pf"]
+        res = L.McResult()
+        hist = np.zeros(spec.hist_bins, dtype=np.int64) if spec.hist_bins else None
+        hist_p = C.c_void_p(hist.ctypes.data) if hist is not None else C.c_void_p(0)
+        sp = C.c_void_p(ticket["stream"].cuda_stream)
+        ptr = _CudaStageBackend._ptr
+        with torch.cuda.device(self.device):
+            try:
+                self.check(self.lib.mc_fetch_result(self.handle, C.byref(res), hist_p, None, sp))
+            finally:
+                self._in_flight = False
+            if res.status != 0:          # the key window missed: the terminal values are there, reduce them the general way
+                params.flags = (params.flags | L.FLAG_TERMINAL_GIVEN) & ~L.FLAG_STORE_PATHS
+                self.check(self.lib.mc_run(self.handle, C.byref(params), C.byref(pf) if pf else None, ptr(ticket["pool"]),
+                                           ptr(ticket["shocks"]), None, ptr(ticket["terminal"]), C.byref(res), hist_p,
+                                           None, sp))
+        return self._pack(spec, res, hist, None, ticket["terminal"], None, 0)
+
     # ------------------------------------------------------------------ peers (runs sharded without host round trips)
     @staticmethod
     def fused_request(spec: SimSpec, world: int) -> bool:
@@ -549,6 +600,53 @@ class Engine:
 
 
 _engines = threading.local()
+
+
+class Pipeline:
+    """`depth` engines, each on a stream of its own, taking jobs in turn: while one job's result is fetched and unpacked
+    by the host and its closing kernels run, the next job's simulation already fills the GPU.
+
+        pipe = Pipeline(2)
+        for out in pipe.map(specs): ...          # results in submission order
+    """
+
+    def __init__(self, depth: int = 2, device: Optional[int] = None):
+        if depth < 1:
+            raise ValueError("depth must be >= 1")
+        self.engines = [Engine(device) for _ in range(depth)]
+        self.streams = [torch.cuda.Stream(device=e.device) for e in self.engines]
+        self._queue = []
+        self._next = 0
+
+    def submit(self, spec: SimSpec, pool=None, shocks=None) -> None:
+        if len(self._queue) >= len(self.engines):
+            raise RuntimeError("every engine of the pipeline has a job in flight: collect() first")
+        i = self._next
+        self._next = (i + 1) % len(self.engines)
+        # the job starts after whatever the caller's stream holds now (inputs it has just produced)
+        self.streams[i].wait_stream(torch.cuda.current_stream(self.engines[i].device))
+        with torch.cuda.stream(self.streams[i]):
+            ticket = self.engines[i].submit(spec, pool=pool, shocks=shocks)
+        self._queue.append((i, ticket))
+
+    def collect(self) -> RunOutput:
+        i, ticket = self._queue.pop(0)
+        return self.engines[i].collect(ticket)
+
+    def map(self, specs, pool=None):
+        """RunOutputs of `specs` in order, `depth` jobs in flight."""
+        for spec in specs:
+            if len(self._queue) >= len(self.engines):
+                yield self.collect()
+            self.submit(spec, pool=pool)
+        while self._queue:
+            yield self.collect()
+
+    def close(self):
+        while self._queue:
+            self.collect()
+        for e in self.engines:
+            e.close()
 
 
 def get_engine(device: Optional[int] = None) -> Engine:

@@ -311,3 +311,44 @@ def test_small_path_rows_with_heavy_ties(engine):
             assert list(out.pct.values()) == [exp["percentiles"][f"p{p}"] for p in PCTS]
             thr = np.percentile(paths[-1], 5.0)
             assert out.tail_count == int((paths[-1] <= thr).sum())
+
+
+# ---------------------------------------------------------------- jobs in flight on several handles
+def test_pipeline_keeps_two_jobs_in_flight_and_returns_the_synchronous_results(engine):
+    """`Engine.submit` / `collect` are `mc_run_sharded` + `mc_fetch_result` with one rank: the enqueue and the read of
+    `mc_run` as two calls.  `Pipeline(2)` alternates between two handles on two streams; every result must be the one
+    the synchronous call gives, bit for bit -- including a job whose key window misses and is reduced again by the
+    staged selection inside `collect`."""
+    from montecarlo_b200.engine import Pipeline
+    pool = _pool()
+    jobs = []
+    for seed in range(3):
+        jobs.append((SimSpec.gbm(300_007 + seed, 30, 100.0, 0.05, 0.2, 1 / 252, seed=seed, hist_bins=256,
+                                 hist_range=(60.0, 160.0)), None, None))
+        jobs.append((SimSpec(n_paths=200_003, n_steps=25, s0=100.0, var0=2e-4, seed=10 + seed, dtype="float64",
+                             hist_bins=64, hist_range=(20.0, 400.0)), pool, None))
+    z = (5.0 * np.random.RandomState(3).standard_normal((8, 3_000_000))).astype("float32")       # the window misses
+    jobs.append((SimSpec.gbm(3_000_000, 8, 100.0, 0.0, 0.4, 1 / 252, dtype="float32", shock="injected", hist_bins=128,
+                             hist_range=(10.0, 1000.0)), None, z))
+    pipe = Pipeline(2)
+    try:
+        got = []
+        for spec, pl, sh in jobs:
+            if len(pipe._queue) == 2:
+                got.append(pipe.collect())
+            pipe.submit(spec, pool=pl, shocks=sh)
+        while pipe._queue:
+            got.append(pipe.collect())
+        with pytest.raises(ValueError):
+            pipe.submit(SimSpec.gbm(1000, 5, 100.0, 0.05, 0.2, 1 / 252, store_paths=True, fan_chart=True))
+        assert pipe.engines[0].debug_counter(1) + pipe.engines[1].debug_counter(1) == 1          # the one fall-back
+    finally:
+        pipe.close()
+    assert len(got) == len(jobs)
+    for (spec, pl, sh), out in zip(jobs, got):
+        ref = engine.simulate(spec, pool=pl, shocks=sh)
+        assert torch.equal(out.terminal, ref.terminal)
+        assert out.pct == ref.pct and out.pct_bounds == ref.pct_bounds
+        assert (out.n, out.n_above, out.tail_count) == (ref.n, ref.n_above, ref.tail_count)
+        assert (out.mean, out.std, out.tail_sum, out.min, out.max) == (ref.mean, ref.std, ref.tail_sum, ref.min, ref.max)
+        assert np.array_equal(out.hist, ref.hist)
